@@ -1,0 +1,57 @@
+// la_b200 — execution context: one CUDA stream plus a device workspace arena.
+//
+// The reference keeps LAPACK workspaces in a pooled host arena so that any number
+// of fibers can call LAPACK concurrently (src/linalg/workpool.cr:6-73,
+// spec/linalg_spec.cr:519-539).  The GPU backend has the same need on the device
+// side: every exported symbol checks a Context out of a mutex-protected pool,
+// runs on that context's stream and bump-allocates scratch from its arena.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+namespace la {
+
+struct Arena {
+  struct Block { char* base; size_t size; size_t used; };
+  std::vector<Block> blocks;
+  struct Mark { size_t nblocks; size_t used_last; };
+  void* alloc(size_t bytes);       // 256-byte aligned; grows with cudaMalloc on demand
+  Mark mark() const;
+  void release(Mark m);            // stack discipline
+  void free_all();
+  size_t total = 0;
+};
+
+struct Context {
+  int device = 0;
+  cudaStream_t stream = nullptr;   // compute stream of this context
+  bool owns_stream = false;
+  cudaStream_t copy_stream = nullptr;  // H2D/D2H overlap in the host-pointer shims
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  Arena arena;
+  int sm_count = 0;
+  int* d_info = nullptr;           // device-side LAPACK info word (in arena block 0)
+  void* pinned = nullptr;          // small pinned bounce buffer (info, ipiv)
+  size_t pinned_size = 0;
+  template <typename T> T* alloc(size_t n) { return (T*)arena.alloc(n * sizeof(T)); }
+};
+
+// Pool of contexts for the host-pointer (drop-in) symbols.
+Context* acquire_context();
+void release_context(Context* c);
+struct ContextLease {
+  Context* c;
+  ContextLease() : c(acquire_context()) {}
+  ~ContextLease() { release_context(c); }
+  Context* operator->() { return c; }
+  Context& operator*() { return *c; }
+};
+
+// Per-thread context for the device-pointer API, re-targeted at a caller stream.
+Context* thread_context(cudaStream_t stream);
+
+void* pinned_scratch(Context& c, size_t bytes);
+
+}  // namespace la

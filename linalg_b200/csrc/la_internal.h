@@ -1,0 +1,114 @@
+// la_b200 — internal device-level API (all pointers are DEVICE pointers, column-major).
+//
+// One function per library routine the reference reaches through its FFI
+// (SURVEY.md §8a).  Every routine only enqueues work on ctx.stream; LAPACK `info`
+// words live on the device (d_info) and are read back by the C-ABI layer.
+#pragma once
+#include "common.cuh"
+#include "context.h"
+
+namespace la {
+
+enum TriMask : int { TriFull = 0, TriLower = 1, TriUpper = 2 };
+
+// C = alpha*op(A)*op(B) + beta*C.  `tri` restricts the stored part of C to one
+// triangle (syrk/herk style); `herm_diag` forces Im(C_ii)=0 (herk).
+template <typename T>
+void gemm(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A,
+          int64_t lda, const T* B, int64_t ldb, T beta, T* C, int64_t ldc, int tri = TriFull,
+          bool herm_diag = false);
+
+// Which GEMM path the calling thread used last (0 = SIMT, 1 = DMMA f64, 2 = DMMA complex,
+// 3 = 3xTF32 tcgen05); written by the dispatcher, read by la_b200_last_gemm_path().
+int& last_gemm_path();
+
+// Generic SIMT implementation (any alignment / leading dimension / type).
+template <typename T>
+void gemm_simt(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A,
+               int64_t lda, const T* B, int64_t ldb, T beta, T* C, int64_t ldc, int tri,
+               bool herm_diag);
+
+// Fast paths; return false when the shape/alignment is not supported.
+bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
+                   const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
+                   double* C, int64_t ldc, int tri);
+bool gemm_dmma_z(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, zcomplex alpha,
+                 const zcomplex* A, int64_t lda, const zcomplex* B, int64_t ldb, zcomplex beta,
+                 zcomplex* C, int64_t ldc, int tri, bool herm_diag);
+bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, float alpha,
+                 const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
+                 int64_t ldc, int tri);
+
+// C = alpha*op(A)*op(A)^H + beta*C on one triangle (trans = OpN: A is n x k; else k x n).
+template <typename T>
+void herk(Context& ctx, Uplo uplo, Op trans, int64_t n, int64_t k, double alpha, const T* A,
+          int64_t lda, double beta, T* C, int64_t ldc);
+
+template <typename T>
+void trsm(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, int64_t n, T alpha,
+          const T* A, int64_t lda, T* B, int64_t ldb);
+
+template <typename T>
+void trmm(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, int64_t n, T alpha,
+          const T* A, int64_t lda, T* B, int64_t ldb);
+
+// symm (herm=false) / hemm (herm=true)
+template <typename T>
+void symm(Context& ctx, bool herm, Side side, Uplo uplo, int64_t m, int64_t n, T alpha,
+          const T* A, int64_t lda, const T* B, int64_t ldb, T beta, T* C, int64_t ldc);
+
+// elementwise helpers
+template <typename T>
+void copy_matrix(Context& ctx, int64_t m, int64_t n, const T* A, int64_t lda, T* B, int64_t ldb);
+template <typename T>  // B = op(A); A is m x n, B is n x m
+void transpose_matrix(Context& ctx, bool conj, int64_t m, int64_t n, const T* A, int64_t lda,
+                      T* B, int64_t ldb);
+template <typename T>
+void set_matrix(Context& ctx, int64_t m, int64_t n, T offdiag, T diag, T* A, int64_t lda);
+// copy the `uplo` triangle of A (n x n) to B, zero the other, optional unit diagonal
+template <typename T>
+void copy_triangle(Context& ctx, Uplo uplo, bool unit, int64_t m, int64_t n, const T* A,
+                   int64_t lda, T* B, int64_t ldb);
+// B = full symmetric/hermitian matrix from the `uplo` triangle of A
+template <typename T>
+void symmetrize(Context& ctx, bool herm, Uplo uplo, int64_t n, const T* A, int64_t lda, T* B,
+                int64_t ldb);
+
+// row interchanges: for k in [k1,k2) (or reversed) swap rows k and ipiv[k]-1 of the n columns
+template <typename T>
+void laswp(Context& ctx, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, const int* d_ipiv,
+           bool reverse);
+
+// factorizations / solves
+template <typename T>
+void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info);
+template <typename T>
+void potrs(Context& ctx, Uplo uplo, int64_t n, int64_t nrhs, const T* A, int64_t lda, T* B,
+           int64_t ldb);
+template <typename T>
+void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, int* d_info);
+template <typename T>
+void getrs(Context& ctx, Op trans, int64_t n, int64_t nrhs, const T* A, int64_t lda,
+           const int* d_ipiv, T* B, int64_t ldb);
+template <typename T>
+void trtrs(Context& ctx, Uplo uplo, Op trans, Diag diag, int64_t n, int64_t nrhs, const T* A,
+           int64_t lda, T* B, int64_t ldb, int* d_info);
+template <typename T>
+void geqrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau);
+template <typename T>  // multiply C by Q or Q^H from geqrf reflectors (ormqr / unmqr)
+void ormqr(Context& ctx, Side side, Op trans, int64_t m, int64_t n, int64_t k, const T* A,
+           int64_t lda, const T* d_tau, T* C, int64_t ldc);
+template <typename T>  // generate the leading n columns of Q (orgqr / ungqr)
+void orgqr(Context& ctx, int64_t m, int64_t n, int64_t k, T* A, int64_t lda, const T* d_tau);
+template <typename T>
+void gels(Context& ctx, Op trans, int64_t m, int64_t n, int64_t nrhs, T* A, int64_t lda, T* B,
+          int64_t ldb, int* d_info);
+// inverses built on the factors
+template <typename T>
+void trtri(Context& ctx, Uplo uplo, Diag diag, int64_t n, T* A, int64_t lda, int* d_info);
+template <typename T>
+void getri(Context& ctx, int64_t n, T* A, int64_t lda, const int* d_ipiv, int* d_info);
+template <typename T>
+void potri(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info);
+
+}  // namespace la

@@ -1,0 +1,466 @@
+// la_b200 — Householder QR (geqrf), application/generation of Q (ormqr/unmqr, orgqr/ungqr)
+// and the least-squares driver gels.
+//
+// Reference call sites replaced: ?geqrf_ (src/linalg/qr.cr:42-46), ?gels_
+// (src/linalg/linalg.cr:493-506, :541-543 -> geqrf + ormqr/unmqr + trtrs inside LAPACK),
+// ?orgqr_/zungqr_ (src/linalg/qr.cr:107).  Conventions follow LAPACK 3.12 ?geqr2/?larfg/
+// ?larft/?larfb: H(i) = I - tau_i v_i v_i^H, v_i(i) = 1, beta = -sign(Re alpha)*norm, R's
+// diagonal is real; Q = H(1) H(2) ... H(k).
+//
+// Panel kernel: one cooperative launch per panel (<= 32 columns).  Rows are spread over the
+// CTAs; each column costs ONE grid barrier: the partial sums  s_c = sum_r conj(a(r,j)) a(r,c)
+// for c = j..jb-1 give both the column norm (c = j) and, after scaling, v^H A for the
+// update, so the reflector and its application are derived redundantly by every CTA from
+// the same reduced vector.  The CTA's row slice is cached in shared memory when it fits,
+// otherwise streamed from global memory (tall-skinny panels).
+#include "la_internal.h"
+#include <cooperative_groups.h>
+
+namespace la {
+
+namespace {
+
+constexpr int QR_NT = 256;
+constexpr int QR_MAX_JB = 32;
+constexpr int QR_MAX_CTAS = 160;
+constexpr size_t QR_SMEM_BUDGET = 200 * 1024;
+
+template <typename T>
+struct QrExchange {
+  unsigned int barrier;
+  unsigned int pad[63];
+  T part[2][QR_MAX_CTAS][QR_MAX_JB];  // per-CTA partial sums s_c
+  T rowj[2][QR_MAX_JB];               // row j of the panel
+};
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    while (ld_acquire_u32(counter) < target) { }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+template <typename T> __device__ __forceinline__ void st_cg(T* p, T v) { __stcg(p, v); }
+template <> __device__ __forceinline__ void st_cg<zcomplex>(zcomplex* p, zcomplex v) {
+  __stcg(&p->x, v.x); __stcg(&p->y, v.y);
+}
+template <typename T> __device__ __forceinline__ T ld_cg(const T* p) { return __ldcg(p); }
+template <> __device__ __forceinline__ zcomplex ld_cg<zcomplex>(const zcomplex* p) {
+  zcomplex v; v.x = __ldcg(&p->x); v.y = __ldcg(&p->y); return v;
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+template <>
+__device__ __forceinline__ zcomplex warp_sum<zcomplex>(zcomplex v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+    v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+  }
+  return v;
+}
+
+// ?larfg from the reduced quantities: alpha = a(j,j), xnorm2 = sum |x|^2.
+// Returns beta (new a(j,j)), tau and the scale applied to x.
+template <typename T>
+__device__ __forceinline__ void householder(T alpha, double xnorm2, T& beta_out, T& tau, T& scale) {
+  if constexpr (Traits<T>::is_complex) {
+    if (xnorm2 == 0.0 && alpha.y == 0.0) {
+      tau = zero<T>(); scale = zero<T>(); beta_out = alpha;
+      return;
+    }
+    double nrm = sqrt(alpha.x * alpha.x + alpha.y * alpha.y + xnorm2);
+    double beta = -copysign(nrm, alpha.x);
+    tau = zcomplex{(beta - alpha.x) / beta, -alpha.y / beta};
+    scale = cdiv(zcomplex{1.0, 0.0}, zcomplex{alpha.x - beta, alpha.y});
+    beta_out = zcomplex{beta, 0.0};
+  } else {
+    if (xnorm2 == 0.0) {
+      tau = zero<T>(); scale = zero<T>(); beta_out = alpha;
+      return;
+    }
+    double a = (double)alpha;
+    double nrm = sqrt(a * a + xnorm2);
+    double beta = -copysign(nrm, a);
+    tau = (T)((beta - a) / beta);
+    scale = (T)(1.0 / (a - beta));
+    beta_out = (T)beta;
+  }
+}
+
+// QR of an mp x jb panel (mp >= 1, jb <= 32), reflectors left in place, tau[0..kmax).
+template <typename T>
+__global__ void __launch_bounds__(QR_NT)
+qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
+                QrExchange<T>* xch, int64_t rpc, int use_smem) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ T s_f[QR_MAX_JB];       // f_c = conj(tau) * w_c
+  __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
+  __shared__ T s_scale;
+  __shared__ T s_beta;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = gridDim.x;
+  const int64_t rs = (int64_t)blockIdx.x * rpc;
+  int64_t nr64 = mp - rs; if (nr64 > rpc) nr64 = rpc; if (nr64 < 0) nr64 = 0;
+  const int64_t nr = nr64;
+
+  T* base;
+  int64_t pitch;
+  if (use_smem) {
+    base = reinterpret_cast<T*>(smem_raw);
+    pitch = rpc;
+    for (int c = 0; c < jb; c++)
+      for (int64_t r = tid; r < nr; r += QR_NT) base[c * pitch + r] = A[rs + r + (int64_t)c * lda];
+    __syncthreads();
+  } else {
+    base = A + rs;
+    pitch = lda;
+  }
+
+  const int kmax = (int)(mp < jb ? mp : jb);
+  unsigned target = 0;
+  for (int j = 0; j < kmax; j++) {
+    const int par = j & 1;
+    // ---- partial sums s_c over owned rows r > j, one warp per column
+    for (int c = j + warp; c < jb; c += QR_NT / 32) {
+      T acc = zero<T>();
+      int64_t rbeg = j + 1 - rs; if (rbeg < 0) rbeg = 0;
+      for (int64_t r = rbeg + lane; r < nr; r += 32)
+        acc = fma_(conj_(base[j * pitch + r]), base[c * pitch + r], acc);
+      acc = warp_sum<T>(acc);
+      if (lane == 0) st_cg<T>(&xch->part[par][blockIdx.x][c], acc);
+    }
+    if (j >= rs && j < rs + nr && tid >= j && tid < jb)
+      st_cg<T>(&xch->rowj[par][tid], base[tid * pitch + (j - rs)]);
+    target += (unsigned)G;
+    grid_barrier(&xch->barrier, target);
+    // ---- reduce the partials: 8 groups x 32 columns
+    {
+      const int c = tid & 31, grp = tid >> 5;
+      T s = zero<T>();
+      if (c >= j && c < jb)
+        for (int g = grp; g < G; g += QR_NT / 32) s = add(s, ld_cg<T>(&xch->part[par][g][c]));
+      s_red[grp][c] = s;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      const int c = tid;
+      T s = zero<T>();
+      if (c >= j && c < jb)
+        for (int g = 0; g < QR_NT / 32; g++) s = add(s, s_red[g][c]);
+      // every lane needs alpha, s_j
+      T rj = (c >= j && c < jb) ? ld_cg<T>(&xch->rowj[par][c]) : zero<T>();
+      T alpha, sj;
+      if constexpr (Traits<T>::is_complex) {
+        alpha.x = __shfl_sync(0xffffffffu, rj.x, j); alpha.y = __shfl_sync(0xffffffffu, rj.y, j);
+        sj.x = __shfl_sync(0xffffffffu, s.x, j); sj.y = 0.0;
+      } else {
+        alpha = __shfl_sync(0xffffffffu, rj, j);
+        sj = __shfl_sync(0xffffffffu, s, j);
+      }
+      T beta, tj, scale;
+      householder<T>(alpha, (double)real_(sj), beta, tj, scale);
+      // w_c = a(j,c) + conj(scale) * s_c ;  f_c = conj(tau) * w_c
+      T w = fma_(conj_(scale), s, rj);
+      s_f[c] = mul(conj_(tj), w);
+      if (c == j) {
+        s_scale = scale;
+        s_beta = beta;
+        if (blockIdx.x == 0) tau[j] = tj;
+      }
+    }
+    __syncthreads();
+    // ---- apply: rows r > j: v_r = x_r*scale, a(r,c) -= v_r f_c; row j: a(j,j)=beta, a(j,c) -= f_c
+    {
+      const T scale = s_scale;
+      const bool identity = is_zero(scale) && is_zero(s_f[j]);  // tau == 0: H = I
+      if (!identity || true) {
+        int64_t rbeg = j + 1 - rs; if (rbeg < 0) rbeg = 0;
+        for (int64_t r = rbeg + tid; r < nr; r += QR_NT) {
+          T v = mul(base[j * pitch + r], scale);
+          base[j * pitch + r] = v;
+          for (int c = j + 1; c < jb; c++)
+            base[c * pitch + r] = fnma_(v, s_f[c], base[c * pitch + r]);
+        }
+        if (j >= rs && j < rs + nr) {
+          if (tid == j) base[j * pitch + (j - rs)] = s_beta;
+          else if (tid > j && tid < jb)
+            base[tid * pitch + (j - rs)] = sub(base[tid * pitch + (j - rs)], s_f[tid]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (use_smem) {
+    for (int c = 0; c < jb; c++)
+      for (int64_t r = tid; r < nr; r += QR_NT) A[rs + r + (int64_t)c * lda] = base[c * pitch + r];
+  }
+}
+
+// T factor of a block reflector from G = V^H V and tau (forward, columnwise ?larft):
+//   T(i,i) = tau_i,  T(0:i,i) = -tau_i * T(0:i,0:i) * G(0:i,i);  strictly lower part = 0.
+template <typename T>
+__global__ void __launch_bounds__(64)
+larft_kernel(int k, const T* __restrict__ Gm, int64_t ldg, const T* __restrict__ tau,
+             T* __restrict__ Tm, int64_t ldt) {
+  __shared__ T Ts[QR_MAX_JB][QR_MAX_JB + 1];
+  const int t = threadIdx.x;
+  for (int idx = t; idx < k * k; idx += blockDim.x) Ts[idx % k][idx / k] = zero<T>();
+  __syncthreads();
+  for (int i = 0; i < k; i++) {
+    const T ti = tau[i];
+    if (t < i) {
+      // row t of T(0:i,0:i) times G(0:i,i); T upper triangular -> columns c >= t
+      T s = zero<T>();
+      for (int c = t; c < i; c++) s = fma_(Ts[t][c], Gm[c + (int64_t)i * ldg], s);
+      Ts[t][i] = mul(neg(ti), s);
+    }
+    if (t == i) Ts[i][i] = ti;
+    __syncthreads();
+  }
+  for (int idx = t; idx < k * k; idx += blockDim.x) Tm[idx % k + (int64_t)(idx / k) * ldt] = Ts[idx % k][idx / k];
+}
+
+template <typename T>
+struct QrWork {
+  QrExchange<T>* xch;
+  T* V;     // mp x nb clean copy of the reflectors (unit diagonal, zeros above)
+  int64_t ldv;
+  T* Tm;    // nb x nb
+  T* Gm;    // nb x nb
+  T* W;     // nb x ncols  (Left)  or  mrows x nb (Right)
+  T* W2;
+  int64_t ldw;
+};
+
+template <typename T>
+void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch) {
+  int64_t G = ceil_div(mp, 512);
+  if (G > ctx.sm_count) G = ctx.sm_count;
+  if (G < 1) G = 1;
+  int64_t rpc = round_up(ceil_div(mp, G), 2);
+  G = ceil_div(mp, rpc);
+  size_t smem = (size_t)rpc * jb * sizeof(T);
+  int use_smem = 1;
+  if (smem > QR_SMEM_BUDGET) {
+    // try all SMs
+    G = ctx.sm_count;
+    rpc = round_up(ceil_div(mp, G), 2);
+    G = ceil_div(mp, rpc);
+    smem = (size_t)rpc * jb * sizeof(T);
+    if (smem > QR_SMEM_BUDGET) { use_smem = 0; smem = 0; }
+  }
+  LA_CUDA_CHECK(cudaMemsetAsync(&xch->barrier, 0, sizeof(unsigned), ctx.stream));
+  void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem};
+  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_kernel<T>, dim3((unsigned)G),
+                                            dim3(QR_NT), args, smem, ctx.stream));
+}
+
+template <typename T>
+void ensure_attrs() {
+  static bool done = false;
+  if (!done) {
+    LA_CUDA_CHECK(cudaFuncSetAttribute(qr_panel_kernel<T>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)QR_SMEM_BUDGET));
+    done = true;
+  }
+}
+
+// Build the clean V (mp x jb) and T (jb x jb) of one block of reflectors stored in A.
+template <typename T>
+void form_block_reflector(Context& ctx, int64_t mp, int jb, const T* A, int64_t lda, const T* tau,
+                          QrWork<T>& w) {
+  copy_triangle<T>(ctx, Lower, true, mp, jb, A, lda, w.V, w.ldv);
+  gemm<T>(ctx, OpC, OpN, jb, jb, mp, one<T>(), w.V, w.ldv, w.V, w.ldv, zero<T>(), w.Gm,
+          QR_MAX_JB);
+  larft_kernel<T><<<1, 64, 0, ctx.stream>>>(jb, w.Gm, QR_MAX_JB, tau, w.Tm, QR_MAX_JB);
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+
+// C <- op(H) C (Left) or C op(H) (Right), H = I - V T V^H, op = N or C.
+template <typename T>
+void apply_block_reflector(Context& ctx, Side side, Op trans, int64_t m, int64_t n, int jb,
+                           QrWork<T>& w, T* C, int64_t ldc) {
+  const T onev = one<T>(), zerov = zero<T>(), mone = from_real<T>(-1.0);
+  if (side == Left) {
+    // W = V^H C (jb x n); W2 = op(T) W; C -= V W2
+    gemm<T>(ctx, OpC, OpN, jb, n, m, onev, w.V, w.ldv, C, ldc, zerov, w.W, w.ldw);
+    gemm<T>(ctx, trans == OpN ? OpN : OpC, OpN, jb, n, jb, onev, w.Tm, QR_MAX_JB, w.W, w.ldw,
+            zerov, w.W2, w.ldw);
+    gemm<T>(ctx, OpN, OpN, m, n, jb, mone, w.V, w.ldv, w.W2, w.ldw, onev, C, ldc);
+  } else {
+    // W = C V (m x jb); W2 = W op(T); C -= W2 V^H
+    gemm<T>(ctx, OpN, OpN, m, jb, n, onev, C, ldc, w.V, w.ldv, zerov, w.W, w.ldw);
+    gemm<T>(ctx, OpN, trans == OpN ? OpN : OpC, m, jb, jb, onev, w.W, w.ldw, w.Tm, QR_MAX_JB,
+            zerov, w.W2, w.ldw);
+    gemm<T>(ctx, OpN, OpC, m, n, jb, mone, w.W2, w.ldw, w.V, w.ldv, onev, C, ldc);
+  }
+}
+
+template <typename T>
+QrWork<T> make_work(Context& ctx, int64_t vrows, int64_t w_rows, int64_t w_cols) {
+  QrWork<T> w;
+  w.xch = (QrExchange<T>*)ctx.arena.alloc(sizeof(QrExchange<T>));
+  w.ldv = round_up(vrows, 16);
+  w.V = ctx.alloc<T>(w.ldv * QR_MAX_JB);
+  w.Tm = ctx.alloc<T>(QR_MAX_JB * QR_MAX_JB);
+  w.Gm = ctx.alloc<T>(QR_MAX_JB * QR_MAX_JB);
+  w.ldw = round_up(w_rows, 16);
+  w.W = ctx.alloc<T>(w.ldw * (w_cols > 0 ? w_cols : 1));
+  w.W2 = ctx.alloc<T>(w.ldw * (w_cols > 0 ? w_cols : 1));
+  return w;
+}
+
+}  // namespace
+
+template <typename T>
+void geqrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau) {
+  const int64_t k = m < n ? m : n;
+  if (k <= 0) return;
+  ensure_attrs<T>();
+  Arena::Mark mk = ctx.arena.mark();
+  QrWork<T> w = make_work<T>(ctx, m, QR_MAX_JB, n);
+  for (int64_t j0 = 0; j0 < k; j0 += QR_MAX_JB) {
+    const int jb = (int)((k - j0) < QR_MAX_JB ? (k - j0) : QR_MAX_JB);
+    const int64_t mp = m - j0;
+    T* P = A + j0 + j0 * lda;
+    qr_panel<T>(ctx, mp, jb, P, lda, d_tau + j0, w.xch);
+    const int64_t nc = n - j0 - jb;
+    if (nc > 0) {
+      form_block_reflector<T>(ctx, mp, jb, P, lda, d_tau + j0, w);
+      apply_block_reflector<T>(ctx, Left, OpC, mp, nc, jb, w, A + j0 + (j0 + jb) * lda, lda);
+    }
+  }
+  ctx.arena.release(mk);
+}
+
+template <typename T>
+void ormqr(Context& ctx, Side side, Op trans, int64_t m, int64_t n, int64_t k, const T* A,
+           int64_t lda, const T* d_tau, T* C, int64_t ldc) {
+  if (m <= 0 || n <= 0 || k <= 0) return;
+  if (trans == OpT && !Traits<T>::is_complex) trans = OpC;
+  const int64_t nq = side == Left ? m : n;  // order of Q
+  Arena::Mark mk = ctx.arena.mark();
+  QrWork<T> w = side == Left ? make_work<T>(ctx, nq, QR_MAX_JB, n)
+                             : make_work<T>(ctx, nq, m, QR_MAX_JB);
+  // Q = Hb_1 ... Hb_p.  Left/N and Right/C apply the last block first.
+  const bool forward = (side == Left) == (trans != OpN);
+  const int64_t nblk = ceil_div(k, QR_MAX_JB);
+  for (int64_t b = 0; b < nblk; b++) {
+    const int64_t bi = forward ? b : nblk - 1 - b;
+    const int64_t j0 = bi * QR_MAX_JB;
+    const int jb = (int)((k - j0) < QR_MAX_JB ? (k - j0) : QR_MAX_JB);
+    const int64_t mp = nq - j0;
+    form_block_reflector<T>(ctx, mp, jb, A + j0 + j0 * lda, lda, d_tau + j0, w);
+    if (side == Left)
+      apply_block_reflector<T>(ctx, Left, trans, mp, n, jb, w, C + j0, ldc);
+    else
+      apply_block_reflector<T>(ctx, Right, trans, m, mp, jb, w, C + j0 * ldc, ldc);
+  }
+  ctx.arena.release(mk);
+}
+
+template <typename T>
+void orgqr(Context& ctx, int64_t m, int64_t n, int64_t k, T* A, int64_t lda, const T* d_tau) {
+  if (m <= 0 || n <= 0) return;
+  Arena::Mark mk = ctx.arena.mark();
+  const int64_t ldq = round_up(m, 16);
+  T* Q = ctx.alloc<T>(ldq * n);
+  set_matrix<T>(ctx, m, n, zero<T>(), one<T>(), Q, ldq);
+  ormqr<T>(ctx, Left, OpN, m, n, k, A, lda, d_tau, Q, ldq);
+  copy_matrix<T>(ctx, m, n, Q, ldq, A, lda);
+  ctx.arena.release(mk);
+}
+
+namespace {
+template <typename T>
+__global__ void zero_rows_kernel(int64_t r0, int64_t r1, int64_t n, T* B, int64_t ldb) {
+  int64_t i = r0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= r1) return;
+  for (int64_t j = blockIdx.y; j < n; j += gridDim.y) B[i + j * ldb] = zero<T>();
+}
+template <typename T>
+void zero_rows(Context& ctx, int64_t r0, int64_t r1, int64_t n, T* B, int64_t ldb) {
+  if (r1 <= r0 || n <= 0) return;
+  dim3 g((unsigned)ceil_div(r1 - r0, 256), (unsigned)(n < 1024 ? n : 1024));
+  zero_rows_kernel<T><<<g, 256, 0, ctx.stream>>>(r0, r1, n, B, ldb);
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+}  // namespace
+
+// ?gels: full-rank least squares / minimum norm.  The LQ branches are run as the QR of A^H
+// held in workspace; A is overwritten with the LQ factors in LAPACK's ?gelqf layout (the
+// conjugate transpose of the QR result).  The ?lascl rescaling of badly scaled inputs that
+// LAPACK performs first is not replicated.
+template <typename T>
+void gels(Context& ctx, Op trans, int64_t m, int64_t n, int64_t nrhs, T* A, int64_t lda, T* B,
+          int64_t ldb, int* d_info) {
+  LA_CUDA_CHECK(cudaMemsetAsync(d_info, 0, sizeof(int), ctx.stream));
+  const int64_t mn = m < n ? m : n;
+  if (mn <= 0 || nrhs < 0) {
+    if (nrhs > 0) zero_rows<T>(ctx, 0, m > n ? m : n, nrhs, B, ldb);
+    return;
+  }
+  const bool tpose = trans != OpN;
+  Arena::Mark mk = ctx.arena.mark();
+  T* tau = ctx.alloc<T>(mn);
+  if (m >= n) {
+    geqrf<T>(ctx, m, n, A, lda, tau);
+    if (!tpose) {
+      // least squares: B <- Q^H B, solve R X = B(0:n)
+      ormqr<T>(ctx, Left, OpC, m, nrhs, n, A, lda, tau, B, ldb);
+      trtrs<T>(ctx, Upper, OpN, NonUnit, n, nrhs, A, lda, B, ldb, d_info);
+    } else {
+      // minimum norm of A^H X = B: X = Q [R^-H B; 0]
+      trtrs<T>(ctx, Upper, OpC, NonUnit, n, nrhs, A, lda, B, ldb, d_info);
+      zero_rows<T>(ctx, n, m, nrhs, B, ldb);
+      ormqr<T>(ctx, Left, OpN, m, nrhs, n, A, lda, tau, B, ldb);
+    }
+  } else {
+    // A = L Q  <=>  A^H = Q' R with L = R^H
+    const int64_t ldt = round_up(n, 16);
+    T* At = ctx.alloc<T>(ldt * m);
+    transpose_matrix<T>(ctx, true, m, n, A, lda, At, ldt);  // At = A^H (n x m)
+    geqrf<T>(ctx, n, m, At, ldt, tau);
+    if (!tpose) {
+      // minimum norm: X = Q' [R^-H B; 0]   (L y = b with L = R^H)
+      trtrs<T>(ctx, Upper, OpC, NonUnit, m, nrhs, At, ldt, B, ldb, d_info);
+      zero_rows<T>(ctx, m, n, nrhs, B, ldb);
+      ormqr<T>(ctx, Left, OpN, n, nrhs, m, At, ldt, tau, B, ldb);
+    } else {
+      // least squares of A^H X = B (B is n x nrhs): B <- Q'^H B, solve R X = B(0:m)
+      ormqr<T>(ctx, Left, OpC, n, nrhs, m, At, ldt, tau, B, ldb);
+      trtrs<T>(ctx, Upper, OpN, NonUnit, m, nrhs, At, ldt, B, ldb, d_info);
+    }
+    transpose_matrix<T>(ctx, true, n, m, At, ldt, A, lda);  // LQ layout back into A
+  }
+  ctx.arena.release(mk);
+}
+
+#define LA_INST_QR(T)                                                                            \
+  template void geqrf<T>(Context&, int64_t, int64_t, T*, int64_t, T*);                           \
+  template void ormqr<T>(Context&, Side, Op, int64_t, int64_t, int64_t, const T*, int64_t,       \
+                         const T*, T*, int64_t);                                                 \
+  template void orgqr<T>(Context&, int64_t, int64_t, int64_t, T*, int64_t, const T*);            \
+  template void gels<T>(Context&, Op, int64_t, int64_t, int64_t, T*, int64_t, T*, int64_t, int*);
+LA_INST_QR(float)
+LA_INST_QR(double)
+LA_INST_QR(zcomplex)
+
+}  // namespace la

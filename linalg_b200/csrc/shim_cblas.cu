@@ -1,0 +1,243 @@
+// la_b200 — CBLAS drop-in symbols (host pointers).  See include/la_b200.h, Part 1.
+//
+// Replaces the `fun`s the reference binds in src/linalg/libCBLAS.cr:174-203 and calls from
+// src/linalg/mult.cr:6-15 (`blas` macro: always COL_MAJOR, NoTrans).  Row-major calls are
+// mapped onto the column-major kernels by the usual transposition identities.
+#include "shim_common.h"
+#include <utility>
+
+namespace la {
+
+static void cblas_error(const char* name, int arg) {
+  // CBLAS has no error return (cblas_xerbla is bound at libCBLAS.cr:206 and never called by
+  // the reference); report and leave the output untouched, as the reference BLAS does.
+  fprintf(stderr, "la_b200: %s: parameter %d had an illegal value\n", name, arg);
+}
+
+template <typename T>
+static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, int k, T alpha,
+                   const T* A, int lda, const T* B, int ldb, T beta, T* C, int ldc) {
+  if (order == LA_ROW_MAJOR_) {
+    // C^T = op(B)^T op(A)^T in column-major terms
+    std::swap(ta, tb); std::swap(m, n); std::swap(A, B); std::swap(lda, ldb);
+  } else if (order != LA_COL_MAJOR_) return cblas_error(name, 1);
+  if (!valid_op(ta)) return cblas_error(name, 2);
+  if (!valid_op(tb)) return cblas_error(name, 3);
+  if (m < 0) return cblas_error(name, 4);
+  if (n < 0) return cblas_error(name, 5);
+  if (k < 0) return cblas_error(name, 6);
+  const int64_t ar = ta == OpN ? m : k, ac = ta == OpN ? k : m;
+  const int64_t br = tb == OpN ? k : n, bc = tb == OpN ? n : k;
+  if (lda < (ar > 1 ? ar : 1)) return cblas_error(name, 9);
+  if (ldb < (br > 1 ? br : 1)) return cblas_error(name, 11);
+  if (ldc < (m > 1 ? m : 1)) return cblas_error(name, 14);
+  if (m == 0 || n == 0) return;
+  if ((is_zero(alpha) || k == 0) && is_one(beta)) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  const bool need_ab = !is_zero(alpha) && k > 0;
+  DevMat<T> dA, dB;
+  if (need_ab) {
+    dA = dev_from_host<T>(*ctx, ar, ac, A, lda);
+    dB = dev_from_host<T>(*ctx, br, bc, B, ldb);
+  }
+  DevMat<T> dC = dev_alloc<T>(*ctx, m, n);
+  if (!is_zero(beta)) upload<T>(*ctx, dC, C, ldc);
+  gemm<T>(*ctx, (Op)ta, (Op)tb, m, n, need_ab ? k : 0, alpha, dA.p, dA.ld, dB.p, dB.ld, beta, dC.p,
+          dC.ld);
+  download<T>(*ctx, dC, C, ldc);
+  sync(*ctx);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_symm(const char* name, bool herm, int order, int side, int uplo, int m, int n,
+                   T alpha, const T* A, int lda, const T* B, int ldb, T beta, T* C, int ldc) {
+  if (order == LA_ROW_MAJOR_) {
+    // row-major C (m x n) is column-major C^T (n x m): A on the other side, other triangle
+    side = side == Left ? Right : (side == Right ? Left : side);
+    uplo = uplo == Upper ? Lower : (uplo == Lower ? Upper : uplo);
+    std::swap(m, n);
+  } else if (order != LA_COL_MAJOR_) return cblas_error(name, 1);
+  if (!valid_side(side)) return cblas_error(name, 2);
+  if (!valid_uplo(uplo)) return cblas_error(name, 3);
+  if (m < 0) return cblas_error(name, 4);
+  if (n < 0) return cblas_error(name, 5);
+  const int64_t na = side == Left ? m : n;
+  if (lda < (na > 1 ? na : 1)) return cblas_error(name, 8);
+  if (ldb < (m > 1 ? m : 1)) return cblas_error(name, 10);
+  if (ldc < (m > 1 ? m : 1)) return cblas_error(name, 13);
+  if (m == 0 || n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  // Row-major note: the column-major view of a row-major symmetric/Hermitian operand is its
+  // transpose, which is exactly the factor the transposed product needs (C^T = B^T A^T), so
+  // swapping side and triangle above is the whole mapping, Hermitian included.
+  DevMat<T> dA = dev_from_host<T>(*ctx, na, na, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, m, n, B, ldb);
+  DevMat<T> dC = dev_alloc<T>(*ctx, m, n);
+  if (!is_zero(beta)) upload<T>(*ctx, dC, C, ldc);
+  symm<T>(*ctx, herm, (Side)side, (Uplo)uplo, m, n, alpha, dA.p, dA.ld, dB.p, dB.ld, beta, dC.p,
+          dC.ld);
+  download<T>(*ctx, dC, C, ldc);
+  sync(*ctx);
+  ctx->arena.release(mk);
+}
+
+// trmm (solve == false) and trsm (solve == true) share validation and staging
+template <typename T>
+static void h_trxm(const char* name, bool solve, int order, int side, int uplo, int ta, int diag,
+                   int m, int n, T alpha, const T* A, int lda, T* B, int ldb) {
+  if (order == LA_ROW_MAJOR_) {
+    side = side == Left ? Right : (side == Right ? Left : side);
+    uplo = uplo == Upper ? Lower : (uplo == Lower ? Upper : uplo);
+    std::swap(m, n);
+  } else if (order != LA_COL_MAJOR_) return cblas_error(name, 1);
+  if (!valid_side(side)) return cblas_error(name, 2);
+  if (!valid_uplo(uplo)) return cblas_error(name, 3);
+  if (!valid_op(ta)) return cblas_error(name, 4);
+  if (!valid_diag(diag)) return cblas_error(name, 5);
+  if (m < 0) return cblas_error(name, 6);
+  if (n < 0) return cblas_error(name, 7);
+  const int64_t na = side == Left ? m : n;
+  if (lda < (na > 1 ? na : 1)) return cblas_error(name, 10);
+  if (ldb < (m > 1 ? m : 1)) return cblas_error(name, 12);
+  if (m == 0 || n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, na, na, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, m, n, B, ldb);
+  if (solve)
+    trsm<T>(*ctx, (Side)side, (Uplo)uplo, (Op)ta, (Diag)diag, m, n, alpha, dA.p, dA.ld, dB.p, dB.ld);
+  else
+    trmm<T>(*ctx, (Side)side, (Uplo)uplo, (Op)ta, (Diag)diag, m, n, alpha, dA.p, dA.ld, dB.p, dB.ld);
+  download<T>(*ctx, dB, B, ldb);
+  sync(*ctx);
+  ctx->arena.release(mk);
+}
+
+// syrk (herm == false, real types) / herk (herm == true)
+template <typename T>
+static void h_herk(const char* name, int order, int uplo, int trans, int n, int k, double alpha,
+                   const T* A, int lda, double beta, T* C, int ldc) {
+  if (order == LA_ROW_MAJOR_) {
+    uplo = uplo == Upper ? Lower : (uplo == Lower ? Upper : uplo);
+    // row-major A (n x k, trans N) is column-major k x n: A A^H = (A_cm)^T conj(A_cm); for the
+    // real routines that is trans flipped; for herk the result is the conjugate, which on the
+    // transposed (swapped-triangle) storage is again the right Hermitian matrix.
+    trans = trans == OpN ? OpC : OpN;
+  } else if (order != LA_COL_MAJOR_) return cblas_error(name, 1);
+  if (!valid_uplo(uplo)) return cblas_error(name, 2);
+  if (!valid_op(trans)) return cblas_error(name, 3);
+  if (n < 0) return cblas_error(name, 4);
+  if (k < 0) return cblas_error(name, 5);
+  const int64_t ar = trans == OpN ? n : k, ac = trans == OpN ? k : n;
+  if (lda < (ar > 1 ? ar : 1)) return cblas_error(name, 8);
+  if (ldc < (n > 1 ? n : 1)) return cblas_error(name, 11);
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, ar, ac, A, lda);
+  DevMat<T> dC = dev_from_host<T>(*ctx, n, n, C, ldc);
+  herk<T>(*ctx, (Uplo)uplo, trans == OpN ? OpN : OpC, n, k, alpha, dA.p, dA.ld, beta, dC.p, dC.ld);
+  // the masked GEMM writes only the named triangle of dC; the rest still holds C's
+  // original values, so a full download leaves the other triangle unchanged on the host
+  download<T>(*ctx, dC, C, ldc);
+  sync(*ctx);
+  ctx->arena.release(mk);
+}
+
+}  // namespace la
+
+using namespace la;
+
+extern "C" {
+
+void cblas_sgemm(int order, int ta, int tb, int m, int n, int k, float alpha, const float* a,
+                 int lda, const float* b, int ldb, float beta, float* c, int ldc) {
+  h_gemm<float>("cblas_sgemm", order, ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc);
+}
+void cblas_dgemm(int order, int ta, int tb, int m, int n, int k, double alpha, const double* a,
+                 int lda, const double* b, int ldb, double beta, double* c, int ldc) {
+  h_gemm<double>("cblas_dgemm", order, ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc);
+}
+void cblas_zgemm(int order, int ta, int tb, int m, int n, int k, const void* alpha, const void* a,
+                 int lda, const void* b, int ldb, const void* beta, void* c, int ldc) {
+  h_gemm<zcomplex>("cblas_zgemm", order, ta, tb, m, n, k, *(const zcomplex*)alpha,
+                   (const zcomplex*)a, lda, (const zcomplex*)b, ldb, *(const zcomplex*)beta,
+                   (zcomplex*)c, ldc);
+}
+void cblas_ssymm(int order, int side, int uplo, int m, int n, float alpha, const float* a, int lda,
+                 const float* b, int ldb, float beta, float* c, int ldc) {
+  h_symm<float>("cblas_ssymm", false, order, side, uplo, m, n, alpha, a, lda, b, ldb, beta, c, ldc);
+}
+void cblas_dsymm(int order, int side, int uplo, int m, int n, double alpha, const double* a,
+                 int lda, const double* b, int ldb, double beta, double* c, int ldc) {
+  h_symm<double>("cblas_dsymm", false, order, side, uplo, m, n, alpha, a, lda, b, ldb, beta, c, ldc);
+}
+void cblas_zsymm(int order, int side, int uplo, int m, int n, const void* alpha, const void* a,
+                 int lda, const void* b, int ldb, const void* beta, void* c, int ldc) {
+  h_symm<zcomplex>("cblas_zsymm", false, order, side, uplo, m, n, *(const zcomplex*)alpha,
+                   (const zcomplex*)a, lda, (const zcomplex*)b, ldb, *(const zcomplex*)beta,
+                   (zcomplex*)c, ldc);
+}
+void cblas_zhemm(int order, int side, int uplo, int m, int n, const void* alpha, const void* a,
+                 int lda, const void* b, int ldb, const void* beta, void* c, int ldc) {
+  h_symm<zcomplex>("cblas_zhemm", true, order, side, uplo, m, n, *(const zcomplex*)alpha,
+                   (const zcomplex*)a, lda, (const zcomplex*)b, ldb, *(const zcomplex*)beta,
+                   (zcomplex*)c, ldc);
+}
+void cblas_strmm(int order, int side, int uplo, int ta, int diag, int m, int n, float alpha,
+                 const float* a, int lda, float* b, int ldb) {
+  h_trxm<float>("cblas_strmm", false, order, side, uplo, ta, diag, m, n, alpha, a, lda, b, ldb);
+}
+void cblas_dtrmm(int order, int side, int uplo, int ta, int diag, int m, int n, double alpha,
+                 const double* a, int lda, double* b, int ldb) {
+  h_trxm<double>("cblas_dtrmm", false, order, side, uplo, ta, diag, m, n, alpha, a, lda, b, ldb);
+}
+void cblas_ztrmm(int order, int side, int uplo, int ta, int diag, int m, int n, const void* alpha,
+                 const void* a, int lda, void* b, int ldb) {
+  h_trxm<zcomplex>("cblas_ztrmm", false, order, side, uplo, ta, diag, m, n,
+                   *(const zcomplex*)alpha, (const zcomplex*)a, lda, (zcomplex*)b, ldb);
+}
+void cblas_strsm(int order, int side, int uplo, int ta, int diag, int m, int n, float alpha,
+                 const float* a, int lda, float* b, int ldb) {
+  h_trxm<float>("cblas_strsm", true, order, side, uplo, ta, diag, m, n, alpha, a, lda, b, ldb);
+}
+void cblas_dtrsm(int order, int side, int uplo, int ta, int diag, int m, int n, double alpha,
+                 const double* a, int lda, double* b, int ldb) {
+  h_trxm<double>("cblas_dtrsm", true, order, side, uplo, ta, diag, m, n, alpha, a, lda, b, ldb);
+}
+void cblas_ztrsm(int order, int side, int uplo, int ta, int diag, int m, int n, const void* alpha,
+                 const void* a, int lda, void* b, int ldb) {
+  h_trxm<zcomplex>("cblas_ztrsm", true, order, side, uplo, ta, diag, m, n, *(const zcomplex*)alpha,
+                   (const zcomplex*)a, lda, (zcomplex*)b, ldb);
+}
+void cblas_ssyrk(int order, int uplo, int trans, int n, int k, float alpha, const float* a, int lda,
+                 float beta, float* c, int ldc) {
+  h_herk<float>("cblas_ssyrk", order, uplo, trans, n, k, alpha, a, lda, beta, c, ldc);
+}
+void cblas_dsyrk(int order, int uplo, int trans, int n, int k, double alpha, const double* a,
+                 int lda, double beta, double* c, int ldc) {
+  h_herk<double>("cblas_dsyrk", order, uplo, trans, n, k, alpha, a, lda, beta, c, ldc);
+}
+void cblas_zherk(int order, int uplo, int trans, int n, int k, double alpha, const void* a, int lda,
+                 double beta, void* c, int ldc) {
+  h_herk<zcomplex>("cblas_zherk", order, uplo, trans, n, k, alpha, (const zcomplex*)a, lda, beta,
+                   (zcomplex*)c, ldc);
+}
+
+void openblas_set_num_threads(int) {}
+int openblas_get_num_threads(void) { return 1; }
+int openblas_get_num_procs(void) { return 1; }
+char* openblas_get_config(void) {
+  static char cfg[] = "la_b200 0.1 CUDA sm_100a (B200) DMMA/tcgen05 backend";
+  return cfg;
+}
+char* openblas_get_corename(void) {
+  static char core[] = "B200";
+  return core;
+}
+int openblas_get_parallel(void) { return 0; }
+
+}  // extern "C"

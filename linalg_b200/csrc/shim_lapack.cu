@@ -1,0 +1,312 @@
+// la_b200 — LAPACK drop-in symbols (host pointers, Fortran-77 ABI).  See include/la_b200.h,
+// Part 2.  Replaces the `fun`s of src/linalg/libLAPACK_linux.cr cited there; the call
+// protocol (all-pointer arguments, lwork = -1 query, info) is the one the reference's
+// `lapack` macro drives (src/linalg/lapack_helper.cr:215-372).
+//
+// Error convention: info = -i for an illegal i-th argument (nothing is
+// touched), info > 0 with LAPACK's meaning (zero pivot / non-PD minor / zero R diagonal).
+// CUDA failures abort the process with a message; they never return success.
+#include "shim_common.h"
+
+namespace la {
+
+static inline int64_t imax(int64_t a, int64_t b) { return a > b ? a : b; }
+static inline int64_t imin(int64_t a, int64_t b) { return a < b ? a : b; }
+
+template <typename T>
+static void set_work(T* work, double v) {
+  if (work) work[0] = from_real<T>(v);
+}
+
+// ------------------------------------------------------------------ getrf / getrs / gesv
+template <typename T>
+static void h_getrf(const int* pm, const int* pn, T* A, const int* plda, int* ipiv, int* info) {
+  const int64_t m = *pm, n = *pn, lda = *plda;
+  *info = 0;
+  if (m < 0) { *info = -1; return; }
+  if (n < 0) { *info = -2; return; }
+  if (lda < imax(1, m)) { *info = -4; return; }
+  if (m == 0 || n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  const int64_t k = imin(m, n);
+  DevMat<T> dA = dev_from_host<T>(*ctx, m, n, A, lda);
+  int* d_ipiv = ctx->alloc<int>(k);
+  getrf<T>(*ctx, m, n, dA.p, dA.ld, d_ipiv, ctx->d_info);
+  download<T>(*ctx, dA, A, lda);
+  LA_CUDA_CHECK(cudaMemcpyAsync(ipiv, d_ipiv, k * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  *info = read_info(*ctx, ctx->d_info);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_getrs(const char* ptrans, const int* pn, const int* pnrhs, const T* A,
+                    const int* plda, const int* ipiv, T* B, const int* pldb, int* info) {
+  const int64_t n = *pn, nrhs = *pnrhs, lda = *plda, ldb = *pldb;
+  const int trans = op_from_char(*ptrans);
+  *info = 0;
+  if (!trans) { *info = -1; return; }
+  if (n < 0) { *info = -2; return; }
+  if (nrhs < 0) { *info = -3; return; }
+  if (lda < imax(1, n)) { *info = -5; return; }
+  if (ldb < imax(1, n)) { *info = -8; return; }
+  if (n == 0 || nrhs == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
+  int* d_ipiv = ctx->alloc<int>(n);
+  LA_CUDA_CHECK(cudaMemcpyAsync(d_ipiv, ipiv, n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  getrs<T>(*ctx, (Op)trans, n, nrhs, dA.p, dA.ld, d_ipiv, dB.p, dB.ld);
+  download<T>(*ctx, dB, B, ldb);
+  sync(*ctx);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_gesv(const int* pn, const int* pnrhs, T* A, const int* plda, int* ipiv, T* B,
+                   const int* pldb, int* info) {
+  const int64_t n = *pn, nrhs = *pnrhs, lda = *plda, ldb = *pldb;
+  *info = 0;
+  if (n < 0) { *info = -1; return; }
+  if (nrhs < 0) { *info = -2; return; }
+  if (lda < imax(1, n)) { *info = -4; return; }
+  if (ldb < imax(1, n)) { *info = -7; return; }
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
+  int* d_ipiv = ctx->alloc<int>(n);
+  getrf<T>(*ctx, n, n, dA.p, dA.ld, d_ipiv, ctx->d_info);
+  download<T>(*ctx, dA, A, lda);
+  LA_CUDA_CHECK(cudaMemcpyAsync(ipiv, d_ipiv, n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  const int inf = read_info(*ctx, ctx->d_info);
+  if (inf == 0 && nrhs > 0) {  // LAPACK solves only when U is non-singular
+    getrs<T>(*ctx, OpN, n, nrhs, dA.p, dA.ld, d_ipiv, dB.p, dB.ld);
+    download<T>(*ctx, dB, B, ldb);
+    sync(*ctx);
+  }
+  *info = inf;
+  ctx->arena.release(mk);
+}
+
+// ------------------------------------------------------------------ potrf / potrs / posv
+template <typename T>
+static void h_potrf(const char* puplo, const int* pn, T* A, const int* plda, int* info) {
+  const int64_t n = *pn, lda = *plda;
+  const int uplo = uplo_from_char(*puplo);
+  *info = 0;
+  if (!uplo) { *info = -1; return; }
+  if (n < 0) { *info = -2; return; }
+  if (lda < imax(1, n)) { *info = -4; return; }
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  potrf<T>(*ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx->d_info);
+  // the kernels touch only the named triangle, so the full download leaves the other one
+  // bit-identical on the host ("other triangle untouched", cholesky.cr:50-64 relies on it)
+  download<T>(*ctx, dA, A, lda);
+  *info = read_info(*ctx, ctx->d_info);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_potrs(const char* puplo, const int* pn, const int* pnrhs, const T* A,
+                    const int* plda, T* B, const int* pldb, int* info) {
+  const int64_t n = *pn, nrhs = *pnrhs, lda = *plda, ldb = *pldb;
+  const int uplo = uplo_from_char(*puplo);
+  *info = 0;
+  if (!uplo) { *info = -1; return; }
+  if (n < 0) { *info = -2; return; }
+  if (nrhs < 0) { *info = -3; return; }
+  if (lda < imax(1, n)) { *info = -5; return; }
+  if (ldb < imax(1, n)) { *info = -7; return; }
+  if (n == 0 || nrhs == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
+  potrs<T>(*ctx, (Uplo)uplo, n, nrhs, dA.p, dA.ld, dB.p, dB.ld);
+  download<T>(*ctx, dB, B, ldb);
+  sync(*ctx);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_posv(const char* puplo, const int* pn, const int* pnrhs, T* A, const int* plda,
+                   T* B, const int* pldb, int* info) {
+  const int64_t n = *pn, nrhs = *pnrhs, lda = *plda, ldb = *pldb;
+  const int uplo = uplo_from_char(*puplo);
+  *info = 0;
+  if (!uplo) { *info = -1; return; }
+  if (n < 0) { *info = -2; return; }
+  if (nrhs < 0) { *info = -3; return; }
+  if (lda < imax(1, n)) { *info = -5; return; }
+  if (ldb < imax(1, n)) { *info = -7; return; }
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
+  potrf<T>(*ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx->d_info);
+  download<T>(*ctx, dA, A, lda);
+  const int inf = read_info(*ctx, ctx->d_info);
+  if (inf == 0 && nrhs > 0) {
+    potrs<T>(*ctx, (Uplo)uplo, n, nrhs, dA.p, dA.ld, dB.p, dB.ld);
+    download<T>(*ctx, dB, B, ldb);
+    sync(*ctx);
+  }
+  *info = inf;
+  ctx->arena.release(mk);
+}
+
+// ------------------------------------------------------------------ trtrs
+template <typename T>
+static void h_trtrs(const char* puplo, const char* ptrans, const char* pdiag, const int* pn,
+                    const int* pnrhs, const T* A, const int* plda, T* B, const int* pldb,
+                    int* info) {
+  const int64_t n = *pn, nrhs = *pnrhs, lda = *plda, ldb = *pldb;
+  const int uplo = uplo_from_char(*puplo), trans = op_from_char(*ptrans),
+            diag = diag_from_char(*pdiag);
+  *info = 0;
+  if (!uplo) { *info = -1; return; }
+  if (!trans) { *info = -2; return; }
+  if (!diag) { *info = -3; return; }
+  if (n < 0) { *info = -4; return; }
+  if (nrhs < 0) { *info = -5; return; }
+  if (lda < imax(1, n)) { *info = -7; return; }
+  if (ldb < imax(1, n)) { *info = -9; return; }
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
+  trtrs<T>(*ctx, (Uplo)uplo, (Op)trans, (Diag)diag, n, nrhs, dA.p, dA.ld, dB.p, dB.ld,
+           ctx->d_info);
+  const int inf = read_info(*ctx, ctx->d_info);
+  if (inf == 0) {  // singular: LAPACK returns before solving, B stays as it was
+    download<T>(*ctx, dB, B, ldb);
+    sync(*ctx);
+  }
+  *info = inf;
+  ctx->arena.release(mk);
+}
+
+// ------------------------------------------------------------------ inverses
+template <typename T>
+static void h_getri(const int* pn, T* A, const int* plda, const int* ipiv, T* work,
+                    const int* plwork, int* info) {
+  const int64_t n = *pn, lda = *plda, lwork = *plwork;
+  *info = 0;
+  if (n < 0) { *info = -1; return; }
+  if (lda < imax(1, n)) { *info = -3; return; }
+  if (lwork != -1 && lwork < imax(1, n)) { *info = -6; return; }
+  if (lwork == -1) { set_work<T>(work, (double)imax(1, n)); return; }
+  set_work<T>(work, (double)imax(1, n));
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  int* d_ipiv = ctx->alloc<int>(n);
+  LA_CUDA_CHECK(cudaMemcpyAsync(d_ipiv, ipiv, n * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  getri<T>(*ctx, n, dA.p, dA.ld, d_ipiv, ctx->d_info);
+  download<T>(*ctx, dA, A, lda);
+  *info = read_info(*ctx, ctx->d_info);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_potri(const char* puplo, const int* pn, T* A, const int* plda, int* info) {
+  const int64_t n = *pn, lda = *plda;
+  const int uplo = uplo_from_char(*puplo);
+  *info = 0;
+  if (!uplo) { *info = -1; return; }
+  if (n < 0) { *info = -2; return; }
+  if (lda < imax(1, n)) { *info = -4; return; }
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  potri<T>(*ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx->d_info);
+  download<T>(*ctx, dA, A, lda);
+  *info = read_info(*ctx, ctx->d_info);
+  ctx->arena.release(mk);
+}
+
+template <typename T>
+static void h_trtri(const char* puplo, const char* pdiag, const int* pn, T* A, const int* plda,
+                    int* info) {
+  const int64_t n = *pn, lda = *plda;
+  const int uplo = uplo_from_char(*puplo), diag = diag_from_char(*pdiag);
+  *info = 0;
+  if (!uplo) { *info = -1; return; }
+  if (!diag) { *info = -2; return; }
+  if (n < 0) { *info = -3; return; }
+  if (lda < imax(1, n)) { *info = -5; return; }
+  if (n == 0) return;
+  ContextLease ctx;
+  Arena::Mark mk = ctx->arena.mark();
+  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  trtri<T>(*ctx, (Uplo)uplo, (Diag)diag, n, dA.p, dA.ld, ctx->d_info);
+  download<T>(*ctx, dA, A, lda);
+  *info = read_info(*ctx, ctx->d_info);
+  ctx->arena.release(mk);
+}
+
+}  // namespace la
+
+using namespace la;
+
+#define LA_LAPACK_FACTOR_SYMBOLS(X, T, VT)                                                        \
+  void X##getrf_(const int* m, const int* n, VT* a, const int* lda, int* ipiv, int* info) {       \
+    h_getrf<T>(m, n, (T*)a, lda, ipiv, info);                                                     \
+  }                                                                                               \
+  void X##getrs_(const char* trans, const int* n, const int* nrhs, const VT* a, const int* lda,   \
+                 const int* ipiv, VT* b, const int* ldb, int* info) {                             \
+    h_getrs<T>(trans, n, nrhs, (const T*)a, lda, ipiv, (T*)b, ldb, info);                         \
+  }                                                                                               \
+  void X##gesv_(const int* n, const int* nrhs, VT* a, const int* lda, int* ipiv, VT* b,           \
+                const int* ldb, int* info) {                                                      \
+    h_gesv<T>(n, nrhs, (T*)a, lda, ipiv, (T*)b, ldb, info);                                       \
+  }                                                                                               \
+  void X##potrf_(const char* uplo, const int* n, VT* a, const int* lda, int* info) {              \
+    h_potrf<T>(uplo, n, (T*)a, lda, info);                                                        \
+  }                                                                                               \
+  void X##potrs_(const char* uplo, const int* n, const int* nrhs, const VT* a, const int* lda,    \
+                 VT* b, const int* ldb, int* info) {                                              \
+    h_potrs<T>(uplo, n, nrhs, (const T*)a, lda, (T*)b, ldb, info);                                \
+  }                                                                                               \
+  void X##posv_(const char* uplo, const int* n, const int* nrhs, VT* a, const int* lda, VT* b,    \
+                const int* ldb, int* info) {                                                      \
+    h_posv<T>(uplo, n, nrhs, (T*)a, lda, (T*)b, ldb, info);                                       \
+  }                                                                                               \
+  void X##trtrs_(const char* uplo, const char* trans, const char* diag, const int* n,             \
+                 const int* nrhs, const VT* a, const int* lda, VT* b, const int* ldb,             \
+                 int* info) {                                                                     \
+    h_trtrs<T>(uplo, trans, diag, n, nrhs, (const T*)a, lda, (T*)b, ldb, info);                   \
+  }                                                                                               \
+  void X##getri_(const int* n, VT* a, const int* lda, const int* ipiv, VT* work,                  \
+                 const int* lwork, int* info) {                                                   \
+    h_getri<T>(n, (T*)a, lda, ipiv, (T*)work, lwork, info);                                       \
+  }                                                                                               \
+  void X##potri_(const char* uplo, const int* n, VT* a, const int* lda, int* info) {              \
+    h_potri<T>(uplo, n, (T*)a, lda, info);                                                        \
+  }                                                                                               \
+  void X##trtri_(const char* uplo, const char* diag, const int* n, VT* a, const int* lda,         \
+                 int* info) {                                                                     \
+    h_trtri<T>(uplo, diag, n, (T*)a, lda, info);                                                  \
+  }
+
+extern "C" {
+
+void ilaver_(int* major, int* minor, int* patch) {
+  *major = 3; *minor = 12; *patch = 0;
+}
+
+LA_LAPACK_FACTOR_SYMBOLS(s, float, float)
+LA_LAPACK_FACTOR_SYMBOLS(d, double, double)
+LA_LAPACK_FACTOR_SYMBOLS(z, zcomplex, void)
+
+}  // extern "C"

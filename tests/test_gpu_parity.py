@@ -1,0 +1,460 @@
+"""GPU parity tests (marked gpu): libla_b200.so, called through the reference's C ABI with
+HOST pointers, against the CPU oracles on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): relative residuals <= 1e-12 for float64/complex128 and
+<= 1e-5 for float32; pivot vectors identical to LAPACK's on random (well separated) inputs.
+Elementwise comparisons with the oracle use c*n*eps scaled bounds written next to each check.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from linalg_b200 import ffi, la
+from oracle import c_ref, checks
+from tests import spec_cases
+
+pytestmark = pytest.mark.gpu
+
+DTYPES = [np.float32, np.float64, np.complex128]
+IDS = ["s", "d", "z"]
+
+
+def _rand(rng, shape, dt, lo=0.0):
+    a = rng.random(shape) + lo
+    if np.dtype(dt) == np.complex128:
+        a = a + 1j * (rng.random(shape) + lo)
+    return np.asfortranarray(a.astype(dt))
+
+
+def _eps(dt):
+    return float(np.finfo(np.dtype(dt)).eps)
+
+
+def _both(fn, product_abi, oracle_abi):
+    with la.use_backend(product_abi):
+        got = fn()
+    with la.use_backend(oracle_abi):
+        ref = fn()
+    return got, ref
+
+
+# ----------------------------------------------------------------------------- reference specs
+@pytest.mark.parametrize("case", spec_cases.ALL_CASES, ids=lambda f: f.__name__)
+def test_reference_specs_on_gpu(case, product_abi):
+    with la.use_backend(product_abi):
+        case()
+
+
+def test_lapack_version(product_abi):
+    assert product_abi.ilaver() == (3, 12, 0)
+
+
+# ----------------------------------------------------------------------------- gemm
+def _gemm_call(abi, dt, ta, tb, m, n, k, alpha, A, B, beta, Cm, lda=None, ldb=None, ldc=None):
+    L = ffi.LETTER[np.dtype(dt)]
+    al, k1 = ffi.scalar_arg(L, alpha)
+    be, k2 = ffi.scalar_arg(L, beta)
+    Cm = Cm.copy(order="F")
+    abi.gemm(L)(ffi.COL_MAJOR, ta, tb, m, n, k, al, ffi.ptr(A), lda or A.shape[0], ffi.ptr(B),
+                ldb or B.shape[0], be, ffi.ptr(Cm), ldc or Cm.shape[0])
+    return Cm
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("ta", [ffi.NO_TRANS, ffi.TRANS, ffi.CONJ_TRANS])
+@pytest.mark.parametrize("tb", [ffi.NO_TRANS, ffi.TRANS, ffi.CONJ_TRANS])
+def test_gemm_all_transposes(rng, dt, ta, tb, product_abi, oracle_abi):
+    for (m, n, k) in [(3, 2, 4), (65, 33, 17), (130, 257, 100), (512, 384, 256)]:
+        A = _rand(rng, (m, k) if ta == ffi.NO_TRANS else (k, m), dt, -0.5)
+        B = _rand(rng, (k, n) if tb == ffi.NO_TRANS else (n, k), dt, -0.5)
+        C0 = _rand(rng, (m, n), dt, -0.5)
+        alpha, beta = (1.25, -0.75) if np.dtype(dt) != np.complex128 else (1.25 - 0.5j, 0.25 + 1j)
+        got = _gemm_call(product_abi, dt, ta, tb, m, n, k, alpha, A, B, beta, C0)
+        ref = _gemm_call(oracle_abi, dt, ta, tb, m, n, k, alpha, A, B, beta, C0)
+        assert checks.rel(got - ref, ref) < 8 * _eps(dt) * np.sqrt(k)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_gemm_reference_call_pattern_and_edges(rng, dt, product_abi, oracle_abi):
+    # Matrix#*: NoTrans/NoTrans, alpha = 1, beta = 1 on a zeroed C (mult.cr:26, :119-120)
+    for n in [1, 7, 64, 1000]:
+        A, B = _rand(rng, (n, n), dt), _rand(rng, (n, n), dt)
+        Z = np.zeros((n, n), dtype=dt, order="F")
+        got = _gemm_call(product_abi, dt, ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, 1.0, A, B, 1.0, Z)
+        ref = _gemm_call(oracle_abi, dt, ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, 1.0, A, B, 1.0, Z)
+        assert checks.rel(got - ref, ref) < 8 * _eps(dt) * np.sqrt(n)
+    # beta = 0 must not read C (NaN in C is overwritten); k = 0 scales C only
+    A, B = _rand(rng, (5, 3), dt), _rand(rng, (3, 4), dt)
+    Cn = np.full((5, 4), np.nan, dtype=dt, order="F")
+    got = _gemm_call(product_abi, dt, ffi.NO_TRANS, ffi.NO_TRANS, 5, 4, 3, 1.0, A, B, 0.0, Cn)
+    assert np.all(np.isfinite(got))
+    C0 = _rand(rng, (5, 4), dt)
+    got = _gemm_call(product_abi, dt, ffi.NO_TRANS, ffi.NO_TRANS, 5, 4, 0, 1.0, A, B, 2.0, C0)
+    assert checks.rel(got - 2 * C0, C0) < 2 * _eps(dt)
+    # leading dimensions larger than the matrices, odd values
+    A, B, C0 = _rand(rng, (11, 6), dt), _rand(rng, (9, 5), dt), _rand(rng, (13, 5), dt)
+    got = _gemm_call(product_abi, dt, ffi.NO_TRANS, ffi.NO_TRANS, 7, 5, 6, 1.0, A, B, 1.0, C0,
+                     lda=11, ldb=9, ldc=13)
+    ref = _gemm_call(oracle_abi, dt, ffi.NO_TRANS, ffi.NO_TRANS, 7, 5, 6, 1.0, A, B, 1.0, C0,
+                     lda=11, ldb=9, ldc=13)
+    assert checks.rel(got - ref, ref) < 16 * _eps(dt)
+    assert np.array_equal(got[7:], C0[7:])  # rows beyond m untouched
+    # row-major call
+    L = ffi.LETTER[np.dtype(dt)]
+    Ar, Br = np.ascontiguousarray(_rand(rng, (4, 6), dt)), np.ascontiguousarray(_rand(rng, (6, 3), dt))
+    Cr = np.zeros((4, 3), dtype=dt)
+    al, _k1 = ffi.scalar_arg(L, 1.0)
+    be, _k2 = ffi.scalar_arg(L, 0.0)
+    product_abi.gemm(L)(ffi.ROW_MAJOR, ffi.NO_TRANS, ffi.NO_TRANS, 4, 3, 6, al, ffi.ptr(Ar), 6,
+                        ffi.ptr(Br), 3, be, ffi.ptr(Cr), 3)
+    assert checks.rel(Cr - Ar @ Br, Ar @ Br) < 16 * _eps(dt)
+
+
+def test_f32_gemm_keeps_fp32_accuracy_on_ill_scaled_input(rng, product_abi):
+    # north_star: the Float32 path must hold FP32 accuracy (3xTF32 split), also when the
+    # operands span many binades and cancel
+    n = 768
+    A = (rng.standard_normal((n, n)) * np.exp2(rng.integers(-12, 12, (n, n)))).astype(np.float32)
+    B = (rng.standard_normal((n, n)) * np.exp2(rng.integers(-12, 12, (n, n)))).astype(np.float32)
+    A, B = np.asfortranarray(A), np.asfortranarray(B)
+    Z = np.zeros((n, n), dtype=np.float32, order="F")
+    got = _gemm_call(product_abi, np.float32, ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, 1.0, A, B, 0.0, Z)
+    exact = A.astype(np.float64) @ B.astype(np.float64)
+    bound = np.abs(A).astype(np.float64) @ np.abs(B).astype(np.float64)
+    # componentwise error bound of an FP32 dot product: gamma_n * |A||B|
+    assert np.max(np.abs(got - exact) / bound) < 1e-5
+
+
+# ----------------------------------------------------------------------------- symm/hemm/trmm/trsm/syrk
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_symm_hemm_trmm_trsm_syrk(rng, dt, product_abi, oracle_abi):
+    L = ffi.LETTER[np.dtype(dt)]
+    m, n = 70, 45
+    for side, na in ((ffi.LEFT, m), (ffi.RIGHT, n)):
+        for uplo in (ffi.UPPER, ffi.LOWER):
+            A = _rand(rng, (na, na), dt, -0.5)
+            B, C0 = _rand(rng, (m, n), dt, -0.5), _rand(rng, (m, n), dt, -0.5)
+            for herm in ([False, True] if L == "z" else [False]):
+                Ah = A.copy(order="F")
+                if herm:
+                    Ah[np.diag_indices(na)] = Ah.diagonal().real
+                outs = []
+                for abi in (product_abi, oracle_abi):
+                    Cc = C0.copy(order="F")
+                    al, _k1 = ffi.scalar_arg(L, 0.5)
+                    be, _k2 = ffi.scalar_arg(L, 2.0)
+                    abi.symm(L, herm)(ffi.COL_MAJOR, side, uplo, m, n, al, ffi.ptr(Ah), na,
+                                      ffi.ptr(B), m, be, ffi.ptr(Cc), m)
+                    outs.append(Cc)
+                assert checks.rel(outs[0] - outs[1], outs[1]) < 64 * _eps(dt)
+            for trans in (ffi.NO_TRANS, ffi.TRANS, ffi.CONJ_TRANS):
+                for diag in (ffi.NON_UNIT, ffi.UNIT):
+                    At = A + na * np.eye(na, dtype=dt)
+                    for which in ("trmm", "trsm"):
+                        outs = []
+                        for abi in (product_abi, oracle_abi):
+                            Bc = B.copy(order="F")
+                            al, _k = ffi.scalar_arg(L, 1.5)
+                            getattr(abi, which)(L)(ffi.COL_MAJOR, side, uplo, trans, diag, m, n, al,
+                                                   ffi.ptr(At), na, ffi.ptr(Bc), m)
+                            outs.append(Bc)
+                        assert checks.rel(outs[0] - outs[1], outs[1]) < 256 * _eps(dt), \
+                            (which, side, uplo, trans, diag)
+    # syrk / herk: only the named triangle changes
+    n, k = 60, 37
+    for uplo in (ffi.UPPER, ffi.LOWER):
+        for trans in (ffi.NO_TRANS, ffi.CONJ_TRANS if L == "z" else ffi.TRANS):
+            A = _rand(rng, (n, k) if trans == ffi.NO_TRANS else (k, n), dt, -0.5)
+            C0 = _rand(rng, (n, n), dt, -0.5)
+            outs = []
+            for abi in (product_abi, oracle_abi):
+                Cc = C0.copy(order="F")
+                abi.syrk(L)(ffi.COL_MAJOR, uplo, trans, n, k, 0.5, ffi.ptr(A), A.shape[0], 2.0,
+                            ffi.ptr(Cc), n)
+                outs.append(Cc)
+            tri = np.triu if uplo == ffi.UPPER else np.tril
+            assert checks.rel(tri(outs[0]) - tri(outs[1]), tri(outs[1])) < 64 * _eps(dt)
+            oth = (lambda x: np.tril(x, -1)) if uplo == ffi.UPPER else (lambda x: np.triu(x, 1))
+            assert np.array_equal(oth(outs[0]), oth(C0))
+
+
+# ----------------------------------------------------------------------------- LU
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("shape", [(1, 1), (5, 4), (4, 7), (100, 100), (257, 130), (130, 257),
+                                   (1000, 1000)])
+def test_getrf_matches_lapack(rng, dt, shape, product_abi, oracle_abi):
+    A = _rand(rng, shape, dt)
+
+    def run():
+        a = la.GeneralMatrix(A)
+        ipiv = np.zeros(min(shape), dtype=np.int32)
+        la._lapack("getrf", a.letter, shape[0], shape[1], a.raw, shape[0], ipiv)
+        return a.raw, ipiv
+
+    (lu, ipiv), (rlu, ripiv) = _both(run, product_abi, oracle_abi)
+    assert checks.pivots_equal(ipiv, ripiv)[0], checks.pivots_equal(ipiv, ripiv)
+    assert checks.lu_residual(A, lu, ipiv) < checks.tol(dt)
+    assert checks.rel(lu - rlu, rlu) < 50 * max(shape) * _eps(dt)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_getrf_singular_and_ties(dt, product_abi, oracle_abi):
+    # exactly singular: column 3 is zero after elimination -> info = 3, factorisation completes
+    A = np.asfortranarray(np.array([[2, 1, 3, 1], [4, 2, 6, 0], [1, 0, 1.5, 2], [0, 1, 0, 1]],
+                                   dtype=dt))
+    A[:, 2] = 1.5 * A[:, 0]
+
+    def run():
+        a = la.GeneralMatrix(A)
+        ipiv = np.zeros(4, dtype=np.int32)
+        info = C.c_int(0)
+        n = C.c_int(4)
+        la.backend().lapack("getrf", a.letter)(C.byref(n), C.byref(n), ffi.ptr(a.raw), C.byref(n),
+                                               ffi.ptr(ipiv), C.byref(info))
+        return info.value, ipiv
+
+    (info, ipiv), (rinfo, ripiv) = _both(run, product_abi, oracle_abi)
+    assert info == rinfo and info > 0
+    assert list(ipiv) == list(ripiv)
+    # ties: equal magnitudes in the pivot column -> first maximal index, as i?amax
+    T = np.asfortranarray(np.array([[1, 2, 3], [-1, 5, 1], [1, 7, 2]], dtype=dt))
+    LU, p, _ = c_ref.getrf(T)
+    with la.use_backend(product_abi):
+        a = la.GeneralMatrix(T)
+        ip = np.zeros(3, dtype=np.int32)
+        la._lapack("getrf", a.letter, 3, 3, a.raw, 3, ip)
+    assert list(ip) == list(p) and ip[0] == 1
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("n,nrhs", [(1, 1), (50, 3), (300, 1), (300, 40)])
+def test_gesv_getrs(rng, dt, n, nrhs, product_abi, oracle_abi):
+    A, B = _rand(rng, (n, n), dt), _rand(rng, (n, nrhs), dt)
+    with la.use_backend(product_abi):
+        x = la.solve(la.GeneralMatrix(A), la.GeneralMatrix(B))
+        lu = la.GeneralMatrix(A).lu_factor()
+        xs = {t: lu.solve(la.GeneralMatrix(B), t).raw for t in la.LUTranspose}
+    assert checks.solve_residual(A, x.raw, B) < checks.tol(dt)
+    assert checks.solve_residual(A, xs[la.LUTranspose.NONE], B) < checks.tol(dt)
+    assert checks.solve_residual(A.T, xs[la.LUTranspose.Transpose], B) < checks.tol(dt)
+    assert checks.solve_residual(A.conj().T, xs[la.LUTranspose.ConjTranspose], B) < checks.tol(dt)
+    with la.use_backend(oracle_abi):
+        xr = la.solve(la.GeneralMatrix(A), la.GeneralMatrix(B))
+    # forward error against LAPACK's answer, scaled by the condition number estimate
+    cond = np.linalg.cond(A.astype(np.complex128))
+    assert checks.rel(x.raw - xr.raw, xr.raw) < 50 * cond * _eps(dt)
+
+
+# ----------------------------------------------------------------------------- Cholesky
+def _spd(rng, n, dt):
+    G = _rand(rng, (n, n), dt, -0.5)
+    return np.asfortranarray((G @ G.conj().T / n + np.eye(n)).astype(dt))
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("n", [1, 2, 63, 64, 65, 200, 777])
+@pytest.mark.parametrize("lower", [True, False])
+def test_potrf_matches_lapack(rng, dt, n, lower, product_abi, oracle_abi):
+    A = _spd(rng, n, dt)
+
+    def run():
+        return la.GeneralMatrix(A).cholesky_(lower=lower, dont_clean=True).raw
+
+    f, rf = _both(run, product_abi, oracle_abi)
+    tri = np.tril if lower else np.triu
+    assert checks.chol_residual(A, f, "L" if lower else "U") < checks.tol(dt)
+    assert checks.rel(tri(f) - tri(rf), tri(rf)) < 50 * n * _eps(dt)
+    oth = (lambda x: np.triu(x, 1)) if lower else (lambda x: np.tril(x, -1))
+    assert np.array_equal(oth(f), oth(A)), "the other triangle must stay untouched"
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_potrf_not_positive_definite_info(rng, dt, product_abi, oracle_abi):
+    for n, bad in [(10, 3), (200, 150), (200, 64)]:
+        A = _spd(rng, n, dt)
+        A[bad, bad] = -5.0
+
+        def run():
+            a = la.GeneralMatrix(A)
+            info, nn = C.c_int(0), C.c_int(n)
+            la.backend().lapack("potrf", a.letter)(C.c_char_p(b"L"), C.byref(nn), ffi.ptr(a.raw),
+                                                   C.byref(nn), C.byref(info))
+            return info.value
+
+        info, rinfo = _both(run, product_abi, oracle_abi)
+        assert info == rinfo == bad + 1
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_posv_potrs_cho_solve(rng, dt, product_abi):
+    n, nrhs = 150, 7
+    A, B = _spd(rng, n, dt), _rand(rng, (n, nrhs), dt)
+    with la.use_backend(product_abi):
+        a = la.GeneralMatrix(A).assume_(la.MatrixFlags.PositiveDefinite)
+        x = a.solve(la.GeneralMatrix(B))
+        xl = la.GeneralMatrix(A).cholesky(lower=True).cho_solve(la.GeneralMatrix(B))
+        xu = la.GeneralMatrix(A).cholesky(lower=False).cho_solve(la.GeneralMatrix(B))
+    for sol in (x, xl, xu):
+        assert checks.solve_residual(A, sol.raw, B) < checks.tol(dt)
+
+
+# ----------------------------------------------------------------------------- QR / least squares
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("shape", [(1, 1), (6, 4), (4, 6), (100, 100), (300, 70), (70, 300),
+                                   (2000, 96)])
+def test_geqrf_matches_lapack_conventions(rng, dt, shape, product_abi, oracle_abi):
+    A = _rand(rng, shape, dt, -0.5)
+
+    def run():
+        a, tau = la.GeneralMatrix(A).qr_raw()
+        return a.raw, tau
+
+    (qr, tau), (rqr, rtau) = _both(run, product_abi, oracle_abi)
+    k = min(shape)
+    assert checks.rel(np.triu(qr) - np.triu(rqr), np.triu(rqr)) < 100 * max(shape) * _eps(dt)
+    assert checks.rel(qr - rqr, rqr) < 100 * max(shape) * _eps(dt)
+    assert checks.rel(tau[:k] - rtau[:k], rtau[:k]) < 100 * max(shape) * _eps(dt)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_qr_orgqr_ormqr(rng, dt, product_abi, oracle_abi):
+    m, n = 120, 50
+    A = _rand(rng, (m, n), dt, -0.5)
+    with la.use_backend(product_abi):
+        q, r = la.GeneralMatrix(A).qr()
+    assert checks.rel(q.raw @ r.raw[:n] - A, A) < checks.tol(dt)
+    assert checks.rel(q.raw.conj().T @ q.raw - np.eye(n), np.eye(n)) < checks.tol(dt)
+    # ormqr/unmqr all sides and transposes against the oracle, on LAPACK's own factors
+    with la.use_backend(oracle_abi):
+        fac, tau = la.GeneralMatrix(A).qr_raw()
+    L = ffi.LETTER[np.dtype(dt)]
+    tr = b"C" if L == "z" else b"T"
+    for side, shape in ((b"L", (m, 9)), (b"R", (9, m))):
+        for trans in (b"N", tr):
+            Cm = _rand(rng, shape, dt, -0.5)
+            outs = []
+            for abi in (product_abi, oracle_abi):
+                with la.use_backend(abi):
+                    c = la.GeneralMatrix(Cm)
+                    la._lapack("ormqr", L, side, trans, shape[0], shape[1], n, fac.raw, m, tau,
+                               c.raw, shape[0])
+                    outs.append(c.raw)
+            assert checks.rel(outs[0] - outs[1], outs[1]) < 100 * m * _eps(dt), (side, trans)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("shape", [(3, 3), (40, 12), (12, 40), (500, 64), (64, 500), (4096, 128)])
+def test_gels_matches_lapack(rng, dt, shape, product_abi, oracle_abi):
+    m, n = shape
+    A, B = _rand(rng, shape, dt), _rand(rng, (m, 3), dt)
+
+    def run():
+        return la.solvels(la.GeneralMatrix(A), la.GeneralMatrix(B)).raw
+
+    x, xr = _both(run, product_abi, oracle_abi)
+    cond = np.linalg.cond(A.astype(np.complex128))
+    assert checks.rel(x[:n] - xr[:n], xr[:n]) < 100 * cond * _eps(dt)
+    if m >= n:  # normal equations residual of the least-squares solution
+        r = A.astype(np.complex128) @ x[:n] - B
+        assert checks.rel(A.conj().T @ r, A.conj().T @ B) < 1e3 * cond * _eps(dt)
+    else:       # minimum-norm: exact solve
+        assert checks.solve_residual(A, x[:n], B) < checks.tol(dt)
+    # the transposed problems of ?gels (not used by the reference, part of the symbol's contract)
+    L = ffi.LETTER[np.dtype(dt)]
+    tr = b"C" if L == "z" else b"T"
+    Bt = _rand(rng, (n, 2), dt)
+    outs = []
+    for abi in (product_abi, oracle_abi):
+        with la.use_backend(abi):
+            a = la.GeneralMatrix(A)
+            xb = np.zeros((max(m, n), 2), dtype=dt, order="F")
+            xb[:n] = Bt
+            la._lapack("gels", L, tr, m, n, 2, a.raw, m, xb, max(m, n))
+            outs.append(xb[:m].copy())
+    assert checks.rel(outs[0] - outs[1], outs[1]) < 100 * cond * _eps(dt)
+
+
+# ----------------------------------------------------------------------------- triangular, inverses
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_trtrs_and_inverses(rng, dt, product_abi, oracle_abi):
+    n = 90
+    T = np.asfortranarray(np.triu(_rand(rng, (n, n), dt)) + n * np.eye(n, dtype=dt))
+    B = _rand(rng, (n, 4), dt)
+    with la.use_backend(product_abi):
+        t = la.GeneralMatrix(T).assume_(la.MatrixFlags.UpperTriangular)
+        x = t.solve(la.GeneralMatrix(B))
+        ti = t.inv()
+        gi = la.GeneralMatrix(_rand(rng, (n, n), dt) + n * np.eye(n, dtype=dt))
+        gi_inv = gi.inv()
+        S = _spd(rng, n, dt)
+        si = la.GeneralMatrix(S).assume_(la.MatrixFlags.PositiveDefinite).inv()
+    assert checks.solve_residual(T, x.raw, B) < checks.tol(dt)
+    eye = np.eye(n)
+    assert checks.rel(T @ ti.raw - eye, eye) < 100 * checks.tol(dt)
+    assert np.array_equal(np.tril(ti.raw, -1), np.tril(T, -1))
+    assert checks.rel(gi.raw @ gi_inv.raw - eye, eye) < 100 * checks.tol(dt)
+    assert checks.rel(S @ si.raw - eye, eye) < 100 * checks.tol(dt)
+    # singular triangular: info = first zero diagonal, B unchanged
+    T2 = T.copy(order="F")
+    T2[10, 10] = 0
+    T2[40, 40] = 0
+    for abi in (product_abi, oracle_abi):
+        with la.use_backend(abi):
+            b = la.GeneralMatrix(B)
+            with pytest.raises(la.LinAlgError, match="returned 11"):
+                la._lapack("trtrs", ffi.LETTER[np.dtype(dt)], b"U", b"N", b"N", n, 4, T2, n, b.raw, n)
+            assert np.array_equal(b.raw, B)
+
+
+# ----------------------------------------------------------------------------- argument checking
+def test_illegal_arguments_report_negative_info(product_abi, oracle_abi):
+    A = np.zeros((4, 4), order="F")
+    ipiv = np.zeros(4, dtype=np.int32)
+
+    def info_of(abi, name, *args):
+        info = C.c_int(0)
+        cargs = []
+        keep = []
+        for a in args:
+            if isinstance(a, np.ndarray):
+                cargs.append(ffi.ptr(a))
+            elif isinstance(a, bytes):
+                cargs.append(C.c_char_p(a))
+            else:
+                keep.append(C.c_int(a))
+                cargs.append(C.byref(keep[-1]))
+        abi.lapack(name, "d")(*cargs, C.byref(info))
+        return info.value
+
+    cases = [("getrf", (-1, 4, A, 4, ipiv)), ("getrf", (4, 4, A, 3, ipiv)),
+             ("potrf", (b"X", 4, A, 4)), ("potrf", (b"L", 4, A, 2)),
+             ("getrs", (b"Q", 4, 1, A, 4, ipiv, A, 4)), ("gesv", (4, -1, A, 4, ipiv, A, 4)),
+             ("trtrs", (b"U", b"N", b"X", 4, 1, A, 4, A, 4)),
+             ("posv", (b"U", 4, 1, A, 4, A, 3))]
+    for name, args in cases:
+        assert info_of(product_abi, name, *args) == info_of(oracle_abi, name, *args) < 0, name
+    # zero-sized problems are legal no-ops
+    assert info_of(product_abi, "getrf", 0, 0, A, 1, ipiv) == 0
+    assert info_of(product_abi, "potrf", b"U", 0, A, 1) == 0
+
+
+def test_concurrent_callers(product_abi):
+    """spec/linalg_spec.cr:519-539 — many concurrent callers; every symbol is re-entrant."""
+    import threading
+    rng = np.random.default_rng(5)
+    mats = [np.asfortranarray(rng.random((60, 60)) + 60 * np.eye(60)) for _ in range(16)]
+    errs = []
+
+    def work(a):
+        try:
+            m = la.GeneralMatrix(a)
+            assert (m * m.inv()).almost_eq(la.GeneralMatrix.identity(60), 1e-9)
+        except Exception as e:  # noqa
+            errs.append(e)
+
+    with la.use_backend(product_abi):
+        ts = [threading.Thread(target=work, args=(a,)) for a in mats]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+    assert not errs, errs
