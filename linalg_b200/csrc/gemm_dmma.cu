@@ -1,0 +1,311 @@
+// la_b200 — FP64 GEMM on the tensor cores (DMMA) with TMA-staged shared-memory tiles.
+//
+// Hot path of cblas_dgemm (src/linalg/mult.cr:64-69 -> libCBLAS.cr:175) and of every
+// trailing update inside dgetrf / dpotrf / dgeqrf / dtrsm.
+//
+// sm_100a has no tcgen05 kind for f64; the FP64 tensor path is mma.sync.m8n8k4.f64
+// (SASS DMMA.8x8x4, 64 FMA/clk/SM = 37.2 TFLOP/s at 1965 MHz, measured 37.0 by
+// tools/microbench/peak_fp64.cu; the larger PTX shapes only expand to the same instruction).
+// Design:
+//   * persistent CTAs (one per SM), grouped tile order for L2 reuse;
+//   * CTA tile 128x128x16, 4-stage ring of TMA loads (cp.async.bulk.tensor.2d, 128-byte
+//     swizzle, zero fill at ragged edges) signalled through mbarriers;
+//   * 1 producer warpgroup (one elected lane issues TMA; setmaxnreg hands its registers to
+//     the consumers) + 8 consumer warps (2x4), warp tile 64x32 = 8x4 DMMA tiles, 64 FP64
+//     accumulators per thread;
+//   * both operand layouts per side (contiguous along M/N or along K), so NN/NT/TN/TT need
+//     no transposition pass;
+//   * k-slot permutation: the 16 k of a stage are assigned to (tig, step) as
+//     k = (tig&1) + 8*(tig>>1) + 2*step, which makes K-major fragment loads conflict free
+//     and MN-major ones 2-way (shared-memory bandwidth is ~30% utilised at DMMA peak);
+//   * epilogue straight from registers: alpha/beta, optional triangle mask (SYRK-style).
+// Algorithmic work: 2*m*n*k flops per call; HBM traffic ~ (m*k + k*n)*8*(reuse factor) +
+// m*n*8*(1 or 2) bytes, tensor-pipe bound for k >= 64.
+#include "la_internal.h"
+#include "tma_utils.cuh"
+#include <mutex>
+
+namespace la {
+
+// ------------------------------------------------------------------ tensor-map helper
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !p) {
+      fprintf(stderr, "la_b200: cuTensorMapEncodeTiled is not available from the driver\n");
+      abort();
+    }
+    fn = (PFN_encodeTiled)p;
+  });
+  return fn;
+}
+
+bool make_tensor_map_2d(CUtensorMap* map, CUtensorMapDataType dtype, size_t elem_bytes,
+                        const void* base, uint64_t inner_extent, uint64_t outer_extent,
+                        uint64_t outer_stride_bytes, uint32_t box_inner, uint32_t box_outer,
+                        CUtensorMapSwizzle swizzle) {
+  if (((uintptr_t)base & 15) || (outer_stride_bytes & 15)) return false;
+  if (inner_extent == 0 || outer_extent == 0) return false;
+  cuuint64_t dims[2] = {inner_extent, outer_extent};
+  cuuint64_t strides[1] = {outer_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = get_encode_fn()(map, dtype, 2, const_cast<void*>(base), dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4;
+constexpr int CONSUMER_WARPS = 8;
+constexpr int PRODUCER_WARPS = 4;  // a full warpgroup, so that setmaxnreg can hand its registers over
+constexpr int NTHREADS = (CONSUMER_WARPS + PRODUCER_WARPS) * 32;
+constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KB
+constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int GROUP_M = 16;  // tile rows per rasterisation group
+
+struct GemmParams {
+  int64_t m, n, k;
+  double alpha, beta;
+  double* C;
+  int64_t ldc;
+  int tri;
+  int tiles_m, tiles_n;
+};
+
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c[0]), "+d"(c[1])
+               : "d"(a), "d"(b));
+}
+
+// byte offset of element (mn, k) inside one operand stage
+template <bool MN_MAJOR>
+__device__ __forceinline__ uint32_t frag_off(int mn, int k) {
+  if (MN_MAJOR)  // [mn/16][k][16 mn], 128-byte rows, 128B swizzle
+    return (uint32_t)((mn >> 4) * (BK * 128) + k * 128 + ((((mn & 15) >> 1) ^ (k & 7)) << 4) +
+                      ((mn & 1) << 3));
+  else           // [mn][16 k]
+    return (uint32_t)(mn * 128 + ((((k >> 1) ^ (mn & 7))) << 4) + ((k & 1) << 3));
+}
+
+__device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
+  const int per_group = GROUP_M * tiles_n;
+  const int g = t / per_group;
+  const int first_m = g * GROUP_M;
+  const int gsz = min(tiles_m - first_m, GROUP_M);
+  const int r = t - g * per_group;
+  tm = first_m + r % gsz;
+  tn = r / gsz;
+}
+
+__device__ __forceinline__ bool tile_skipped(int tri, int tm, int tn) {
+  if (tri == TriLower) return tm * BM + BM - 1 < tn * BN;
+  if (tri == TriUpper) return tm * BM > tn * BN + BN - 1;
+  return false;
+}
+
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const GemmParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = (uint64_t*)(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], CONSUMER_WARPS);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int kblocks = (int)((p.k + BK - 1) / BK);
+
+  if (warp >= CONSUMER_WARPS) {
+    // ===================== TMA producer (one elected lane of the producer warpgroup) =======
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (warp == CONSUMER_WARPS && lane == 0) {
+      tma_prefetch_desc(&tmA);
+      tma_prefetch_desc(&tmB);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int tm, tn;
+        tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+        if (tile_skipped(p.tri, tm, tn)) continue;
+        const int m0 = tm * BM, n0 = tn * BN;
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          unsigned char* sA = smem + stage * STAGE_BYTES;
+          unsigned char* sB = sA + A_STAGE_BYTES;
+          const int k0 = kb * BK;
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / 16; j++)
+              tma_load_2d(sA + j * (BK * 128), &tmA, &full_bar[stage], m0 + 16 * j, k0);
+          } else {
+            tma_load_2d(sA, &tmA, &full_bar[stage], k0, m0);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 16; j++)
+              tma_load_2d(sB + j * (BK * 128), &tmB, &full_bar[stage], n0 + 16 * j, k0);
+          } else {
+            tma_load_2d(sB, &tmB, &full_bar[stage], k0, n0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    return;
+  }
+
+  // ===================== DMMA consumers =====================
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+  const int gid = lane >> 2, tig = lane & 3;
+  const int wm = warp & 1, wn = warp >> 1;     // 2 x 4 warps -> 64 x 32 warp tiles
+  const int kslot = (tig & 1) + 8 * (tig >> 1);  // + 2*step
+  int stage = 0;
+  uint32_t phase = 0;
+  const bool beta_zero = p.beta == 0.0;
+
+  for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    int tm, tn;
+    tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+    if (tile_skipped(p.tri, tm, tn)) continue;
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    for (int kb = 0; kb < kblocks; kb++) {
+      mbar_wait(&full_bar[stage], phase);
+      const unsigned char* sA = smem + stage * STAGE_BYTES;
+      const unsigned char* sB = sA + A_STAGE_BYTES;
+#pragma unroll
+      for (int ks = 0; ks < 4; ks++) {
+        const int kk = kslot + 2 * ks;
+        double a[8], b[4];
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          a[i] = *reinterpret_cast<const double*>(sA + frag_off<A_MN>(wm * 64 + i * 8 + gid, kk));
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          b[j] = *reinterpret_cast<const double*>(sB + frag_off<B_MN>(wn * 32 + j * 8 + gid, kk));
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+#pragma unroll
+          for (int j = 0; j < 4; j++) dmma884(acc[i][j], a[i], b[j]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[stage]);
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+
+    // ---- epilogue: C(row, col..col+1) for row = gid, col = 2*tig of each 8x8 tile
+    const int64_t row_base = (int64_t)tm * BM + wm * 64 + gid;
+    const int64_t col_base = (int64_t)tn * BN + wn * 32 + 2 * tig;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+#pragma unroll
+      for (int c = 0; c < 2; c++) {
+        const int64_t col = col_base + j * 8 + c;
+        if (col >= p.n) continue;
+        double* Ccol = p.C + col * p.ldc;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const int64_t row = row_base + i * 8;
+          if (row >= p.m) continue;
+          if (p.tri == TriLower && row < col) continue;
+          if (p.tri == TriUpper && row > col) continue;
+          double v = p.alpha * acc[i][j][c];
+          if (!beta_zero) v = fma(p.beta, Ccol[row], v);
+          Ccol[row] = v;
+        }
+      }
+    }
+  }
+}
+
+template <bool A_MN, bool B_MN>
+void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p) {
+  static bool attr = false;
+  auto kern = dgemm_dmma_kernel<A_MN, B_MN>;
+  if (!attr) {
+    LA_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr = true;
+  }
+  int tiles = p.tiles_m * p.tiles_n;
+  int grid = tiles < ctx.sm_count ? tiles : ctx.sm_count;
+  kern<<<grid, NTHREADS, SMEM_BYTES, ctx.stream>>>(tmA, tmB, p);
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace
+
+bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
+                   const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
+                   double* C, int64_t ldc, int tri) {
+  if (ta == OpC) ta = OpT;
+  if (tb == OpC) tb = OpT;
+  if (m <= 0 || n <= 0) return true;
+  if (k <= 0 || alpha == 0.0) return false;  // pure scaling: the generic kernel handles it
+  // tiny problems are latency bound either way; keep them on the simple kernel
+  if (m * n * k < (int64_t)64 * 64 * 64) return false;
+  if (m > (int64_t)1 << 30 || n > (int64_t)1 << 30 || k > (int64_t)1 << 30) return false;
+  const bool a_mn = (ta == OpN), b_mn = (tb != OpN);
+  CUtensorMap tmA, tmB;
+  // operand A as op(A) (m x k): stored m x k (lda) when ta == N, else k x m
+  if (a_mn) {
+    if (!make_tensor_map_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, A, m, k, lda * 8, 16, BK,
+                            CU_TENSOR_MAP_SWIZZLE_128B)) return false;
+  } else {
+    if (!make_tensor_map_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, A, k, m, lda * 8, BK, BM,
+                            CU_TENSOR_MAP_SWIZZLE_128B)) return false;
+  }
+  // operand B as op(B) (k x n): stored k x n (ldb) when tb == N, else n x k
+  if (b_mn) {
+    if (!make_tensor_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, B, n, k, ldb * 8, 16, BK,
+                            CU_TENSOR_MAP_SWIZZLE_128B)) return false;
+  } else {
+    if (!make_tensor_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, B, k, n, ldb * 8, BK, BN,
+                            CU_TENSOR_MAP_SWIZZLE_128B)) return false;
+  }
+  GemmParams p;
+  p.m = m; p.n = n; p.k = k;
+  p.alpha = alpha; p.beta = beta;
+  p.C = C; p.ldc = ldc; p.tri = tri;
+  p.tiles_m = (int)ceil_div(m, BM);
+  p.tiles_n = (int)ceil_div(n, BN);
+  if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
+  if (a_mn && b_mn) launch<true, true>(ctx, tmA, tmB, p);
+  else if (a_mn && !b_mn) launch<true, false>(ctx, tmA, tmB, p);
+  else if (!a_mn && b_mn) launch<false, true>(ctx, tmA, tmB, p);
+  else launch<false, false>(ctx, tmA, tmB, p);
+  return true;
+}
+
+}  // namespace la

@@ -433,7 +433,13 @@ def test_illegal_arguments_report_negative_info(product_abi, oracle_abi):
              ("trtrs", (b"U", b"N", b"X", 4, 1, A, 4, A, 4)),
              ("posv", (b"U", 4, 1, A, 4, A, 3))]
     for name, args in cases:
-        assert info_of(product_abi, name, *args) == info_of(oracle_abi, name, *args) < 0, name
+        got, ref = info_of(product_abi, name, *args), info_of(oracle_abi, name, *args)
+        if name == "getrs":
+            # OpenBLAS's own getrs interface reports the bad argument through xerbla but
+            # leaves info = 0; LAPACK 3.12's dgetrs documents info = -1, which is what we return
+            assert got == -1, name
+        else:
+            assert got == ref < 0, name
     # zero-sized problems are legal no-ops
     assert info_of(product_abi, "getrf", 0, 0, A, 1, ipiv) == 0
     assert info_of(product_abi, "potrf", b"U", 0, A, 1) == 0
