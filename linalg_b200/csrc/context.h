@@ -35,6 +35,7 @@ struct Context {
   int* d_info = nullptr;           // device-side LAPACK info word (in arena block 0)
   void* pinned = nullptr;          // small pinned bounce buffer (info, ipiv)
   size_t pinned_size = 0;
+  void* lu_state = nullptr;        // LU panel exchange area + launch sequence (lu_panel.cu)
   template <typename T> T* alloc(size_t n) { return (T*)arena.alloc(n * sizeof(T)); }
 };
 

@@ -135,195 +135,16 @@ void potrs(Context& ctx, Uplo uplo, int64_t n, int64_t nrhs, const T* A, int64_t
 }
 
 // =========================================================================== LU
+template <typename T>
+void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
+                const int* d_ipiv);
+// lu_panel.cu
+template <typename T>
+void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
+              int* d_info);
+int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes);
+
 namespace {
-
-constexpr int LU_NT = 256;       // threads per CTA of the panel kernel
-constexpr int LU_MAX_JB = 32;    // widest leaf panel
-constexpr int LU_MAX_CTAS = 160; // slots reserved in the exchange buffer
-
-// Exchange area in global memory for one panel launch (double-buffered by column parity).
-template <typename T>
-struct LuExchange {
-  unsigned int barrier;              // monotonically increasing arrival counter
-  unsigned int pad[63];
-  struct Slot {
-    typename Traits<T>::real val;    // best |a(i,j)| of this CTA (-1: no candidate)
-    int idx;                         // its row (panel-relative)
-    int pad;
-    T row[LU_MAX_JB];                // the candidate row's current contents
-  } slot[2][LU_MAX_CTAS];
-  T rowj[2][LU_MAX_JB];              // current contents of row j (the row being swapped out)
-};
-
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-
-__device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned target) {
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(counter, 1u);
-    while (ld_acquire_u32(counter) < target) { }
-    __threadfence();
-  }
-  __syncthreads();
-}
-
-template <typename R>
-__device__ __forceinline__ void argmax_combine(R& v, int& i, R ov, int oi) {
-  if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
-}
-
-// Block-wide (value, index) arg-max with "first maximal element" tie-break (i?amax rule).
-template <typename R>
-__device__ __forceinline__ void block_argmax(R& v, int& i, R* sval, int* sidx) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    R ov = __shfl_xor_sync(0xffffffffu, v, o);
-    int oi = __shfl_xor_sync(0xffffffffu, i, o);
-    argmax_combine(v, i, ov, oi);
-  }
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  __syncthreads();  // protect sval/sidx reuse
-  if (l == 0) { sval[w] = v; sidx[w] = i; }
-  __syncthreads();
-  if (w == 0) {
-    const int nw = blockDim.x >> 5;
-    v = l < nw ? sval[l] : (R)-2;
-    i = l < nw ? sidx[l] : 0x7fffffff;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      R ov = __shfl_xor_sync(0xffffffffu, v, o);
-      int oi = __shfl_xor_sync(0xffffffffu, i, o);
-      argmax_combine(v, i, ov, oi);
-    }
-    if (l == 0) { sval[0] = v; sidx[0] = i; }
-  }
-  __syncthreads();
-  v = sval[0];
-  i = sidx[0];
-}
-
-// LU with partial pivoting of an m x jb panel (m >= jb, jb <= 32).
-//   A      : panel, column-major, leading dimension lda
-//   ipiv   : pivot entries of the panel's columns; written as row0 + p + 1 (1-based, global)
-//   rpc    : rows per CTA (contiguous ownership), pitch of the shared-memory panel
-template <typename T>
-__global__ void __launch_bounds__(LU_NT)
-lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__ ipiv, int row0,
-                int* info, int info_off, LuExchange<T>* xch, int rpc) {
-  using R = typename Traits<T>::real;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  T* S = reinterpret_cast<T*>(smem_raw);           // S[c * rpc + r]
-  __shared__ T prow[LU_MAX_JB];
-  __shared__ T rowj[LU_MAX_JB];
-  __shared__ R sval[LU_NT / 32];
-  __shared__ int sidx[LU_NT / 32];
-  __shared__ int s_pcta;
-
-  const int tid = threadIdx.x;
-  const int G = gridDim.x;
-  const int rs = blockIdx.x * rpc;                       // first owned row
-  const int nr = max(0, min(m - rs, rpc));               // owned rows
-
-  for (int c = 0; c < jb; c++)
-    for (int r = tid; r < nr; r += LU_NT) S[c * rpc + r] = A[(int64_t)(rs + r) + (int64_t)c * lda];
-  __syncthreads();
-
-  unsigned target = 0;
-  for (int j = 0; j < jb; j++) {
-    const int par = j & 1;
-    // ---- 1. local arg-max of |a(i,j)| over owned rows i >= j
-    R bv = (R)-1;
-    int bi = 0x7fffffff;
-    for (int r = tid; r < nr; r += LU_NT) {
-      int gr = rs + r;
-      if (gr >= j) {
-        R v = abs1(S[j * rpc + r]);
-        if (v > bv) { bv = v; bi = gr; }
-      }
-    }
-    block_argmax<R>(bv, bi, sval, sidx);
-    // ---- 2. publish candidate (value, index, row contents) and row j
-    if (tid == 0) {
-      __stcg(&xch->slot[par][blockIdx.x].val, bv);
-      __stcg(&xch->slot[par][blockIdx.x].idx, bi);
-    }
-    if (bv >= (R)0 && tid < jb) {
-      T v = S[tid * rpc + (bi - rs)];
-      T* dst = &xch->slot[par][blockIdx.x].row[tid];
-      if constexpr (Traits<T>::is_complex) { __stcg(&dst->x, v.x); __stcg(&dst->y, v.y); }
-      else __stcg(dst, v);
-    }
-    if (j >= rs && j < rs + nr && tid < jb) {
-      T v = S[tid * rpc + (j - rs)];
-      T* dst = &xch->rowj[par][tid];
-      if constexpr (Traits<T>::is_complex) { __stcg(&dst->x, v.x); __stcg(&dst->y, v.y); }
-      else __stcg(dst, v);
-    }
-    // ---- 3. one grid barrier per column
-    target += (unsigned)G;
-    grid_barrier(&xch->barrier, target);
-    // ---- 4. every CTA picks the global winner
-    R pv = (R)-1;
-    int pi = 0x7fffffff;
-    if (tid < G) {
-      pv = __ldcg(&xch->slot[par][tid].val);
-      pi = __ldcg(&xch->slot[par][tid].idx);
-      if (!(pv >= (R)0)) { pv = (R)-1; pi = 0x7fffffff; }
-    }
-    block_argmax<R>(pv, pi, sval, sidx);
-    if (tid < G) {
-      R v = __ldcg(&xch->slot[par][tid].val);
-      int i = __ldcg(&xch->slot[par][tid].idx);
-      if (v == pv && i == pi) s_pcta = tid;
-    }
-    __syncthreads();
-    if (tid < jb) {
-      const T* src = &xch->slot[par][s_pcta].row[tid];
-      const T* srj = &xch->rowj[par][tid];
-      T a, b;
-      if constexpr (Traits<T>::is_complex) {
-        a.x = __ldcg(&src->x); a.y = __ldcg(&src->y);
-        b.x = __ldcg(&srj->x); b.y = __ldcg(&srj->y);
-      } else { a = __ldcg(src); b = __ldcg(srj); }
-      prow[tid] = a;
-      rowj[tid] = b;
-    }
-    __syncthreads();
-    // ---- 5. row interchange j <-> pi
-    if (pi != j && tid < jb) {
-      if (pi >= rs && pi < rs + nr) S[tid * rpc + (pi - rs)] = rowj[tid];
-      if (j >= rs && j < rs + nr)   S[tid * rpc + (j - rs)] = prow[tid];
-    }
-    if (blockIdx.x == 0 && tid == 0) ipiv[j] = row0 + pi + 1;
-    __syncthreads();
-    // ---- 6. scale the column and rank-1 update the rest of the panel
-    const T pivot = prow[j];
-    if (is_zero(pivot)) {
-      if (blockIdx.x == 0 && tid == 0) atomicCAS(info, 0, info_off + j + 1);
-      // as in getf2: no scaling, the (zero-multiplier) update is skipped
-    } else {
-      const bool use_recip = abs1(pivot) >= sfmin<R>();
-      const T rinv = recip(pivot);
-      for (int r = tid; r < nr; r += LU_NT) {
-        int gr = rs + r;
-        if (gr > j) {
-          T a = S[j * rpc + r];
-          T l = use_recip ? mul(a, rinv) : div_(a, pivot);
-          S[j * rpc + r] = l;
-          for (int c = j + 1; c < jb; c++) S[c * rpc + r] = fnma_(l, prow[c], S[c * rpc + r]);
-        }
-      }
-    }
-    __syncthreads();
-  }
-  for (int c = 0; c < jb; c++)
-    for (int r = tid; r < nr; r += LU_NT) A[(int64_t)(rs + r) + (int64_t)c * lda] = S[c * rpc + r];
-}
 
 template <typename T>
 __global__ void laswp_kernel(int64_t n, T* __restrict__ A, int64_t lda, int64_t k1, int64_t k2,
@@ -344,48 +165,15 @@ __global__ void laswp_kernel(int64_t n, T* __restrict__ A, int64_t lda, int64_t 
   }
 }
 
-constexpr size_t LU_SMEM_BUDGET = 200 * 1024;
-
-template <typename T>
-struct LuPlan {
-  int nb0;                 // leaf panel width for this matrix height
-  LuExchange<T>* xch;
-};
-
-template <typename T>
-void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
-              int* d_info, LuExchange<T>* xch) {
-  // rows per CTA: as few CTAs as keep the panel resident and the per-column work short
-  int64_t G = ceil_div(m, 512);
-  if (G > ctx.sm_count) G = ctx.sm_count;
-  if (G < 1) G = 1;
-  int64_t rpc = ceil_div(m, G);
-  // grow G until the slice fits shared memory
-  while ((size_t)rpc * jb * sizeof(T) > LU_SMEM_BUDGET && G < ctx.sm_count) {
-    G++;
-    rpc = ceil_div(m, G);
-  }
-  rpc = round_up(rpc, 2);
-  G = ceil_div(m, rpc);
-  size_t smem = (size_t)rpc * jb * sizeof(T);
-  if (smem > LU_SMEM_BUDGET) {
-    fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
-    abort();
-  }
-  LA_CUDA_CHECK(cudaMemsetAsync(&xch->barrier, 0, sizeof(unsigned), ctx.stream));
-  int mi = (int)m, row0i = (int)row0, info_off = (int)row0, rpci = (int)rpc;
-  void* args[] = {&mi, &jb, &A, &lda, &ipiv, &row0i, &d_info, &info_off, &xch, &rpci};
-  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lu_panel_kernel<T>, dim3((unsigned)G),
-                                            dim3(LU_NT), args, smem, ctx.stream));
-}
+struct LuPlan { int nb0; };  // leaf panel width for this matrix height
 
 // Factor columns [j0, j0+jn) of the m-row matrix A below row j0 (all earlier updates
 // applied); pivots are global row indices.
 template <typename T>
 void getrf_rec(Context& ctx, int64_t m, T* A, int64_t lda, int* ipiv, int* d_info, int64_t j0,
-               int64_t jn, const LuPlan<T>& plan) {
+               int64_t jn, const LuPlan& plan) {
   if (jn <= plan.nb0) {
-    lu_panel<T>(ctx, m - j0, (int)jn, A + j0 + j0 * lda, lda, ipiv + j0, j0, d_info, plan.xch);
+    lu_panel<T>(ctx, m - j0, (int)jn, A + j0 + j0 * lda, lda, ipiv + j0, j0, d_info);
     return;
   }
   int64_t n1 = jn / 2;
@@ -398,15 +186,104 @@ void getrf_rec(Context& ctx, int64_t m, T* A, int64_t lda, int* ipiv, int* d_inf
   T* A22 = A + (j0 + n1) + (j0 + n1) * lda;
   const T* A11 = A + j0 + j0 * lda;
   const T* A21 = A + (j0 + n1) + j0 * lda;
-  laswp<T>(ctx, n2, A + (j0 + n1) * lda, lda, j0, j0 + n1, ipiv, false);
+  laswp_rows<T>(ctx, m, n2, A + (j0 + n1) * lda, lda, j0, j0 + n1, ipiv);
   trsm<T>(ctx, Left, Lower, OpN, Unit, n1, n2, one<T>(), A11, lda, A12, lda);
   gemm<T>(ctx, OpN, OpN, m - j0 - n1, n2, n1, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(),
           A22, lda);
   getrf_rec<T>(ctx, m, A, lda, ipiv, d_info, j0 + n1, n2, plan);
-  laswp<T>(ctx, n1, A + j0 * lda, lda, j0 + n1, j0 + jn, ipiv, false);
+  laswp_rows<T>(ctx, m, n1, A + j0 * lda, lda, j0 + n1, j0 + jn, ipiv);
 }
 
+
+// Net permutation of the interchange sequence ipiv[k1..k2): one CTA simulates the swaps on an
+// index map held in shared memory (O(1) per pivot) and emits, for every touched row, which
+// original row ends up there: entries e < npiv are the top block rows k1+e, entries
+// npiv..2*npiv-1 the pivot rows themselves (duplicates are harmless: same value, same place).
+__global__ void __launch_bounds__(256)
+laswp_prep_kernel(int k1, int npiv, int mapn, const int* __restrict__ ipiv, int* __restrict__ dst,
+                  int* __restrict__ src) {
+  extern __shared__ int content[];   // content[i] = original row now at row k1+i ; then pivots
+  int* piv = content + mapn;
+  for (int i = threadIdx.x; i < mapn; i += blockDim.x) content[i] = k1 + i;
+  for (int e = threadIdx.x; e < npiv; e += blockDim.x) piv[e] = ipiv[k1 + e] - 1 - k1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int e = 0; e < npiv; e++) {
+      const int p = piv[e];
+      const int a = content[e], b = content[p];
+      content[e] = b;
+      content[p] = a;
+    }
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < npiv; e += blockDim.x) {
+    dst[e] = k1 + e;
+    src[e] = content[e];
+    const int p = piv[e];
+    dst[npiv + e] = k1 + p;
+    src[npiv + e] = content[p];
+  }
+}
+
+// Apply a net row permutation (dst[e] <- src[e], e < nent) to n columns: each CTA stages one
+// column's touched rows in shared memory, then scatters them.
+template <typename T>
+__global__ void __launch_bounds__(256)
+laswp_apply_kernel(int64_t n, T* __restrict__ A, int64_t lda, int nent, const int* __restrict__ dst,
+                   const int* __restrict__ src) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* buf = reinterpret_cast<T*>(smem_raw);
+  for (int64_t c = blockIdx.x; c < n; c += gridDim.x) {
+    T* col = A + c * lda;
+    for (int e = threadIdx.x; e < nent; e += blockDim.x) buf[e] = col[src[e]];
+    __syncthreads();
+    for (int e = threadIdx.x; e < nent; e += blockDim.x) {
+      const int d = dst[e];
+      if (d != src[e]) col[d] = buf[e];
+    }
+    __syncthreads();
+  }
+}
+
+constexpr int LASWP_CHUNK = 1024;        // pivots per prep/apply pair
+constexpr int LASWP_MAX_MAP = 49152;     // rows the shared-memory index map can cover
+
 }  // namespace
+
+// `m` = number of rows of A (upper bound of the pivot indices); 0 = unknown (serial kernel).
+template <typename T>
+void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
+                const int* d_ipiv) {
+  if (n <= 0 || k2 <= k1) return;
+  static bool attr = false;
+  if (!attr) {
+    LA_CUDA_CHECK(cudaFuncSetAttribute(laswp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (LASWP_MAX_MAP + LASWP_CHUNK) * (int)sizeof(int)));
+    attr = true;
+  }
+  Arena::Mark mk = ctx.arena.mark();
+  int* lists = ctx.alloc<int>(4 * LASWP_CHUNK);
+  for (int64_t c1 = k1; c1 < k2; c1 += LASWP_CHUNK) {
+    const int64_t c2 = c1 + LASWP_CHUNK < k2 ? c1 + LASWP_CHUNK : k2;
+    const int npiv = (int)(c2 - c1);
+    const int64_t mapn = m - c1;
+    if (m <= 0 || mapn > LASWP_MAX_MAP) {
+      laswp_kernel<T><<<(unsigned)ceil_div(n, 128), 128, 0, ctx.stream>>>(n, A, lda, c1, c2, d_ipiv, 0);
+      LA_CUDA_CHECK(cudaGetLastError());
+      continue;
+    }
+    int* dst = lists;
+    int* src = lists + 2 * LASWP_CHUNK;
+    laswp_prep_kernel<<<1, 256, (size_t)(mapn + npiv) * sizeof(int), ctx.stream>>>(
+        (int)c1, npiv, (int)mapn, d_ipiv, dst, src);
+    const int nent = 2 * npiv;
+    int64_t grid = n < (int64_t)ctx.sm_count * 8 ? n : (int64_t)ctx.sm_count * 8;
+    laswp_apply_kernel<T><<<(unsigned)grid, 256, (size_t)nent * sizeof(T), ctx.stream>>>(
+        n, A, lda, nent, dst, src);
+    LA_CUDA_CHECK(cudaGetLastError());
+  }
+  ctx.arena.release(mk);
+}
 
 template <typename T>
 void laswp(Context& ctx, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, const int* d_ipiv,
@@ -422,32 +299,32 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   LA_CUDA_CHECK(cudaMemsetAsync(d_info, 0, sizeof(int), ctx.stream));
   const int64_t k = m < n ? m : n;
   if (k <= 0) return;
-  static bool attr_set = false;
-  if (!attr_set) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)LU_SMEM_BUDGET));
-    attr_set = true;
-  }
-  Arena::Mark mk = ctx.arena.mark();
-  LuPlan<T> plan;
-  plan.xch = (LuExchange<T>*)ctx.arena.alloc(sizeof(LuExchange<T>));
-  // widest leaf panel that stays resident when the tallest panel (m rows) is spread
-  // over all SMs
-  int64_t rpc = round_up(ceil_div(m, ctx.sm_count), 2);
-  int64_t nb0 = (int64_t)(LU_SMEM_BUDGET / (rpc * sizeof(T)));
-  if (nb0 > LU_MAX_JB) nb0 = LU_MAX_JB;
+  LuPlan plan;
+  const int64_t nb0 = lu_panel_max_width(ctx, m, sizeof(T));
   if (nb0 < 1) {
     fprintf(stderr, "la_b200: getrf: %lld rows exceed the panel kernel's capacity\n", (long long)m);
     abort();
   }
   plan.nb0 = (int)nb0;
-  getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, 0, k, plan);
-  if (n > k) {  // wide matrix: U12 = L11^-1 * P * A12
-    laswp<T>(ctx, n - k, A + k * lda, lda, 0, k, d_ipiv, false);
-    trsm<T>(ctx, Left, Lower, OpN, Unit, k, n - k, one<T>(), A, lda, A + k * lda, lda);
+  // Right-looking blocked LU: recursive factorisation of an m x NB panel, then row
+  // interchanges of the columns left and right of it, U12 = L11^-1 A12 and the rank-NB
+  // trailing update (where nearly all flops are).  Keeping the interchanges per panel bounds
+  // the serial part of laswp's net-permutation set-up to NB steps.
+  const int64_t NB = k >= 8192 ? 512 : (k >= 2048 ? 256 : 128);
+  for (int64_t j0 = 0; j0 < k; j0 += NB) {
+    const int64_t jb = NB < k - j0 ? NB : k - j0;
+    getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
+    if (j0 > 0) laswp_rows<T>(ctx, m, j0, A, lda, j0, j0 + jb, d_ipiv);
+    const int64_t nr = n - j0 - jb;  // columns to the right
+    if (nr > 0) {
+      T* A12 = A + j0 + (j0 + jb) * lda;
+      laswp_rows<T>(ctx, m, nr, A + (j0 + jb) * lda, lda, j0, j0 + jb, d_ipiv);
+      trsm<T>(ctx, Left, Lower, OpN, Unit, jb, nr, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
+      if (m - j0 - jb > 0)
+        gemm<T>(ctx, OpN, OpN, m - j0 - jb, nr, jb, from_real<T>(-1.0), A + (j0 + jb) + j0 * lda,
+                lda, A12, lda, one<T>(), A + (j0 + jb) + (j0 + jb) * lda, lda);
+    }
   }
-  ctx.arena.release(mk);
 }
 
 template <typename T>
@@ -456,7 +333,7 @@ void getrs(Context& ctx, Op trans, int64_t n, int64_t nrhs, const T* A, int64_t 
   if (n <= 0 || nrhs <= 0) return;
   if (!Traits<T>::is_complex && trans == OpC) trans = OpT;
   if (trans == OpN) {
-    laswp<T>(ctx, nrhs, B, ldb, 0, n, d_ipiv, false);
+    laswp_rows<T>(ctx, n, nrhs, B, ldb, 0, n, d_ipiv);
     trsm<T>(ctx, Left, Lower, OpN, Unit, n, nrhs, one<T>(), A, lda, B, ldb);
     trsm<T>(ctx, Left, Upper, OpN, NonUnit, n, nrhs, one<T>(), A, lda, B, ldb);
   } else {

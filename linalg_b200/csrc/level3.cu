@@ -5,6 +5,7 @@
 // src/linalg/mult.cr:26-91 (libCBLAS.cr:174-201); TRSM/HERK are the trailing-update
 // kernels inside ?getrf/?potrf/?getrs/?potrs/?trtrs.
 #include "la_internal.h"
+#include "tri_small.cuh"
 
 namespace la {
 
@@ -183,84 +184,70 @@ void symmetrize(Context& ctx, bool herm, Uplo uplo, int64_t n, const T* A, int64
 // ------------------------------------------------------------------ TRSM
 namespace {
 
-constexpr int TRSM_NB = 32;   // order of the triangular base case
-// vectors (columns of B for Left, rows for Right) per CTA; sized so that the static
-// shared memory (Ms + Xs) stays under 48 KB for every element type
-template <typename T> struct TrsmCfg { static constexpr int NT = 128; };
-template <> struct TrsmCfg<zcomplex> { static constexpr int NT = 32; };
+// Base case of the recursive TRSM: one thread per right-hand-side vector (a column of B for
+// side = Left, a row for side = Right) solves against a triangular block of order <= NB held
+// in shared memory, with the vector in registers (tri_small.cuh).
+template <typename T> struct TrsmCfg { static constexpr int NB = 64, NT = 64; };
+template <> struct TrsmCfg<zcomplex> { static constexpr int NB = 32, NT = 64; };
 
-// Solve M x = alpha*b for one vector per thread, M = effective na x na triangular matrix in
-// shared memory (dense, other triangle zero).  Xs[i][tid] holds b on entry, x on exit.
 template <typename T>
-__device__ __forceinline__ void tri_solve_vec(const T (*Ms)[TRSM_NB + 1],
-                                              T (*Xs)[TrsmCfg<T>::NT + 1],
-                                              int na, bool lower, bool unit, T alpha, int t) {
-  if (lower) {
-    for (int i = 0; i < na; i++) {
-      T s = mul(alpha, Xs[i][t]);
-      for (int j = 0; j < i; j++) s = fnma_(Ms[i][j], Xs[j][t], s);
-      Xs[i][t] = unit ? s : div_(s, Ms[i][i]);
-    }
-  } else {
-    for (int i = na - 1; i >= 0; i--) {
-      T s = mul(alpha, Xs[i][t]);
-      for (int j = i + 1; j < na; j++) s = fnma_(Ms[i][j], Xs[j][t], s);
-      Xs[i][t] = unit ? s : div_(s, Ms[i][i]);
-    }
-  }
-}
-
-// Load the effective matrix M(i,j): Left:  M = op(A);  Right: M = op(A)^T (so that
-// x*op(A) = b  <=>  M x^T = b^T).  Only the stored triangle of A is read.
-template <typename T>
-__device__ __forceinline__ void load_tri(T (*Ms)[TRSM_NB + 1], const T* A, int64_t lda, int na,
-                                         bool a_lower, int op, bool right) {
-  for (int idx = threadIdx.x; idx < na * na; idx += blockDim.x) {
-    int i = idx % na, j = idx / na;  // stored element A(i,j)
-    bool stored = a_lower ? (i >= j) : (i <= j);
-    T v = stored ? A[i + (int64_t)j * lda] : zero<T>();
-    // op(A)(r,c): N -> A(r,c); T -> A(c,r); C -> conj(A(c,r))
-    int r = i, c = j;
-    if (op != OpN) { r = j; c = i; }
-    if (op == OpC) v = conj_(v);
-    if (right) { int t = r; r = c; c = t; }
-    Ms[r][c] = v;
-  }
+constexpr size_t trsm_smem_bytes() {
+  return sizeof(T) * (size_t)TrsmCfg<T>::NB * (TrsmCfg<T>::NB + 1) +
+         sizeof(T) * (size_t)TrsmCfg<T>::NB * (TrsmCfg<T>::NT + 1);
 }
 
 template <typename T>
 __global__ void __launch_bounds__(TrsmCfg<T>::NT)
 trsm_base_kernel(int right, int a_lower, int op, int unit, int na, int64_t nvec, T alpha,
                  const T* __restrict__ A, int64_t lda, T* __restrict__ B, int64_t ldb) {
-  constexpr int TRSM_NT = TrsmCfg<T>::NT;
-  __shared__ T Ms[TRSM_NB][TRSM_NB + 1];
-  __shared__ T Xs[TRSM_NB][TRSM_NT + 1];
-  load_tri<T>(Ms, A, lda, na, a_lower != 0, op, right != 0);
+  constexpr int NB = TrsmCfg<T>::NB, NT = TrsmCfg<T>::NT, LDM = NB + 1, LDX = NT + 1;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* Ms = reinterpret_cast<T*>(smem_raw);   // effective matrix M (see below), row pitch LDM
+  T* Xs = Ms + NB * LDM;                    // Left side staging: Xs[i * LDX + v]
+  // M = op(A) for Left;  M = op(A)^T for Right (x*op(A) = b  <=>  M x^T = b^T).
+  for (int idx = threadIdx.x; idx < na * na; idx += NT) {
+    int i = idx % na, j = idx / na;  // stored element A(i,j); only the stored triangle is read
+    bool stored = a_lower ? (i >= j) : (i <= j);
+    T v = stored ? A[i + (int64_t)j * lda] : zero<T>();
+    int r = i, c = j;
+    if (op != OpN) { r = j; c = i; }
+    if (op == OpC) v = conj_(v);
+    if (right) { int t = r; r = c; c = t; }
+    Ms[r * LDM + c] = v;
+  }
   bool eff_lower = (a_lower != 0) != (op != OpN);
   if (right) eff_lower = !eff_lower;
-  const int64_t v0 = (int64_t)blockIdx.x * TRSM_NT;
-  const int nv = (int)((nvec - v0) < TRSM_NT ? (nvec - v0) : TRSM_NT);
+  const int64_t v0 = (int64_t)blockIdx.x * NT;
+  const int nv = (int)((nvec - v0) < NT ? (nvec - v0) : NT);
+  const int t = threadIdx.x;
+  T x[NB];
   if (right) {
-    // vectors are rows of B: element i of vector v is B(v0+v, i): coalesced over v
-    for (int i = 0; i < na; i++)
-      if ((int)threadIdx.x < nv) Xs[i][threadIdx.x] = B[v0 + threadIdx.x + (int64_t)i * ldb];
+#pragma unroll
+    for (int i = 0; i < NB; i++)
+      x[i] = (i < na && t < nv) ? B[v0 + t + (int64_t)i * ldb] : zero<T>();
+    __syncthreads();
   } else {
-    // vectors are columns of B: element i of vector v is B(i, v0+v): coalesced over i
-    for (int idx = threadIdx.x; idx < na * nv; idx += blockDim.x) {
+    for (int idx = t; idx < na * nv; idx += NT) {
       int i = idx % na, v = idx / na;
-      Xs[i][v] = B[i + (v0 + v) * ldb];
+      Xs[i * LDX + v] = B[i + (v0 + v) * ldb];
     }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NB; i++) x[i] = (i < na && t < nv) ? Xs[i * LDX + t] : zero<T>();
   }
-  __syncthreads();
-  if ((int)threadIdx.x < nv) tri_solve_vec<T>(Ms, Xs, na, eff_lower, unit != 0, alpha, threadIdx.x);
-  __syncthreads();
+  if (t < nv) solve_vec_regs<T, NB, LDM>(Ms, na, eff_lower, unit != 0, alpha, x);
   if (right) {
-    for (int i = 0; i < na; i++)
-      if ((int)threadIdx.x < nv) B[v0 + threadIdx.x + (int64_t)i * ldb] = Xs[i][threadIdx.x];
+#pragma unroll
+    for (int i = 0; i < NB; i++)
+      if (i < na && t < nv) B[v0 + t + (int64_t)i * ldb] = x[i];
   } else {
-    for (int idx = threadIdx.x; idx < na * nv; idx += blockDim.x) {
+#pragma unroll
+    for (int i = 0; i < NB; i++)
+      if (i < na && t < nv) Xs[i * LDX + t] = x[i];
+    __syncthreads();
+    for (int idx = t; idx < na * nv; idx += NT) {
       int i = idx % na, v = idx / na;
-      B[i + (v0 + v) * ldb] = Xs[i][v];
+      B[i + (v0 + v) * ldb] = Xs[i * LDX + v];
     }
   }
 }
@@ -270,10 +257,18 @@ void trsm_rec(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, i
               const T* A, int64_t lda, T* B, int64_t ldb) {
   const int64_t na = side == Left ? m : n;
   const int64_t nvec = side == Left ? n : m;
+  constexpr int TRSM_NB = TrsmCfg<T>::NB;
   if (na <= TRSM_NB) {
     constexpr int TRSM_NT = TrsmCfg<T>::NT;
+    static bool attr = false;
+    if (!attr) {
+      LA_CUDA_CHECK(cudaFuncSetAttribute(trsm_base_kernel<T>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)trsm_smem_bytes<T>()));
+      attr = true;
+    }
     unsigned g = (unsigned)ceil_div(nvec, TRSM_NT);
-    trsm_base_kernel<T><<<g, TRSM_NT, 0, ctx.stream>>>(side == Right, uplo == Lower, (int)op,
+    trsm_base_kernel<T><<<g, TRSM_NT, trsm_smem_bytes<T>(), ctx.stream>>>(side == Right, uplo == Lower, (int)op,
                                                        diag == Unit, (int)na, nvec, alpha, A, lda,
                                                        B, ldb);
     LA_CUDA_CHECK(cudaGetLastError());
