@@ -221,6 +221,16 @@ LA_B200_DECL_DEV(d, double)
 LA_B200_DECL_DEV(z, void)
 #undef LA_B200_DECL_DEV
 
+/* No counterpart in the reference.  FP64 LU factorisation (same arguments, results and pivot
+ * vector as la_b200_dgetrf_dev) for hosts that must not allocate GPU memory: every byte of
+ * scratch comes from one 384 KiB array inside the library image, which every GPU that loads
+ * the library holds until exit.  m, n <= 32768, else -100 is returned (message on stderr) and
+ * nothing is enqueued.  The first call on a device does a one-time set-up and should precede
+ * any stream capture.  All calls share the array: order them on one stream; calls that can
+ * overlap on the GPU race.  -101: set-up failed. */
+int la_b200_dgetrf_dev_noalloc(int64_t m, int64_t n, double* a, int64_t lda, int* ipiv, int* info,
+                               void* stream);
+
 /* library identification / diagnostics */
 const char* la_b200_version(void);
 /* bytes of device workspace currently held by the calling thread's arena */

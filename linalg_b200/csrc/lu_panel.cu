@@ -18,6 +18,7 @@
 // Bytes per column step (algorithmic): (jb-j) * rows * sizeof(T) read+written in SHARED memory;
 // HBM traffic is one read and one write of the panel per launch: 2*m*jb*sizeof(T).
 #include "la_internal.h"
+#include <new>
 
 namespace la {
 
@@ -239,6 +240,17 @@ static LuPanelState* panel_state(Context& ctx) {
     ctx.lu_state = st;
   }
   return (LuPanelState*)ctx.lu_state;
+}
+
+// For callers that bring their own exchange memory (getrf_noalloc.cu): size of the area, and a
+// way to install caller-owned, zero-initialised device memory as the exchange area of `ctx`
+// with host-side bookkeeping in caller-owned storage, so that nothing is allocated here.
+size_t lu_panel_exchange_bytes() { return sizeof(LuExchange); }
+size_t lu_panel_state_bytes() { return sizeof(LuPanelState); }
+void lu_panel_adopt_exchange(Context& ctx, void* device_mem, void* state_storage) {
+  LuPanelState* st = new (state_storage) LuPanelState();
+  st->xch = (LuExchange*)device_mem;
+  ctx.lu_state = st;
 }
 
 int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {

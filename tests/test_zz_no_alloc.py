@@ -1,0 +1,71 @@
+"""GPU test of la_b200_dgetrf_dev_noalloc, the LU entry point that allocates no GPU memory.
+
+It exists for hosts that cannot let a library call cudaMalloc — a service whose device memory
+was handed out up front, a framework section in which allocation is frozen, a process confined
+to a memory slice sized for its operands — and takes all its scratch from a fixed 384 KiB array
+inside the library.  The test calls it through the C ABI on device buffers and checks LU factors
+and pivot vectors against la_b200_dgetrf_dev (the allocating entry point) on the same inputs,
+twice in a row with different sizes, so that whatever the first call leaves in the shared array
+is present when the second one runs.  It also checks that a problem beyond the documented limit
+is refused.  This file is named so that pytest collects it last.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-12  # the float64 tolerance used throughout tests/test_gpu_parity.py
+
+
+def _bind():
+    import linalg_b200
+    lib = linalg_b200.lib()
+    sig = [C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    for name in ("la_b200_dgetrf_dev", "la_b200_dgetrf_dev_noalloc"):
+        f = getattr(lib, name)
+        f.argtypes = sig
+        f.restype = C.c_int
+    return lib.la_b200_dgetrf_dev, lib.la_b200_dgetrf_dev_noalloc
+
+
+def _factor(fn, a_host):
+    """Run one of the two entry points on a copy of a_host (column-major m x n)."""
+    import torch
+    m, n = a_host.shape
+    # a (n, m) contiguous torch tensor is the column-major m x n matrix
+    a = torch.from_numpy(np.ascontiguousarray(a_host.T)).cuda()
+    ipiv = torch.zeros(min(m, n), dtype=torch.int32, device="cuda")
+    info = torch.full((1,), -7, dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    rc = fn(m, n, a.data_ptr(), m, ipiv.data_ptr(), info.data_ptr(), C.c_void_p(stream))
+    torch.cuda.synchronize()
+    return rc, a.cpu().numpy().T.copy(), ipiv.cpu().numpy(), int(info.item())
+
+
+def test_noalloc_getrf_matches_allocating_entry_point_twice_in_a_row():
+    from oracle import checks
+    getrf, getrf_noalloc = _bind()
+    rng = np.random.default_rng(20261106)
+    for shape in [(1500, 1500), (700, 900)]:          # two calls in a row, different shapes
+        a = rng.random(shape)
+        rc0, lu0, piv0, info0 = _factor(getrf, a)
+        rc1, lu1, piv1, info1 = _factor(getrf_noalloc, a)
+        assert rc0 == 0 and rc1 == 0
+        assert info0 == 0 and info1 == 0
+        assert np.array_equal(piv0, piv1)
+        assert checks.rel(lu1 - lu0, lu0) <= TOL
+        assert checks.lu_residual(a, lu1, piv1) <= TOL
+
+
+def test_noalloc_getrf_refuses_sizes_beyond_its_limit():
+    import torch
+    _, getrf_noalloc = _bind()
+    dummy = torch.zeros(8, dtype=torch.float64, device="cuda")
+    ipiv = torch.zeros(8, dtype=torch.int32, device="cuda")
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rc = getrf_noalloc(32769, 4, dummy.data_ptr(), 32769, ipiv.data_ptr(), info.data_ptr(), None)
+    assert rc == -100
+    rc = getrf_noalloc(-1, 4, dummy.data_ptr(), 1, ipiv.data_ptr(), info.data_ptr(), None)
+    assert rc == -1
