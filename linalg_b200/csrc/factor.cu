@@ -1,138 +1,14 @@
-// la_b200 — Cholesky and LU factorisations and the solves built on them.
+// la_b200 — LU factorisation and the solves built on it (Cholesky lives in cholesky.cu).
 //
-// Reference call sites replaced: ?potrf_/?potrs_/?posv_ (src/linalg/cholesky.cr:47-90,
-// src/linalg/linalg.cr:433-434), ?getrf_/?getrs_/?gesv_ (src/linalg/lu.cr:74-80,151-162,
+// Reference call sites replaced: ?getrf_/?getrs_/?gesv_ (src/linalg/lu.cr:74-80,151-162,
 // src/linalg/linalg.cr:443-445), ?trtrs_ (src/linalg/linalg.cr:431-432).
 //
-// Both factorisations are recursive (the shape LAPACK 3.12's ?getrf2/?potrf2 use), so that
-// almost all flops land in large GEMM / TRSM calls, with hand-written panel kernels at the
-// leaves:
-//   * potf2_kernel   one CTA, block <= 64x64 resident in shared memory.
-//   * lu_panel_kernel one cooperative launch per leaf panel (<= 32 columns, any height):
-//       the panel is distributed by rows over the CTAs' shared memory and each column
-//       costs ONE grid barrier (local arg-max + candidate row published together).
-//   * laswp_kernel    row interchanges.
+// Blocked right-looking driver around a recursive panel factorisation; the leaf panel kernel
+// is in lu_panel.cu, the row interchanges (net-permutation laswp) are here.
 #include "la_internal.h"
 #include <cooperative_groups.h>
 
 namespace la {
-
-// =========================================================================== Cholesky
-namespace {
-
-constexpr int POTF2_NB = 64;
-
-// Factor one n x n (n <= 64) diagonal block in shared memory.  The block is always
-// factored as lower (for uplo = U the conjugate transpose is loaded / stored), only the
-// named triangle of A is read or written.
-template <typename T>
-__global__ void __launch_bounds__(256)
-potf2_kernel(int lower, int n, T* __restrict__ A, int64_t lda, int* info, int info_off) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  T(*S)[POTF2_NB + 1] = reinterpret_cast<T(*)[POTF2_NB + 1]>(smem_raw);
-  __shared__ int fail;
-  if (*info != 0) return;  // an earlier block already failed: LAPACK would have stopped
-  const int tid = threadIdx.x;
-  if (tid == 0) fail = 0;
-  for (int idx = tid; idx < n * n; idx += blockDim.x) {
-    int i = idx % n, j = idx / n;
-    if (lower) { if (i >= j) S[i][j] = A[i + (int64_t)j * lda]; }
-    else       { if (i <= j) S[j][i] = conj_(A[i + (int64_t)j * lda]); }
-  }
-  __syncthreads();
-  for (int j = 0; j < n; j++) {
-    if (tid == 0) {
-      double d = (double)real_(S[j][j]);
-      if (!(d > 0.0)) {  // also catches NaN, as LAPACK's disnan test does
-        fail = j + 1;
-      } else {
-        S[j][j] = from_real<T>(sqrt(d));
-      }
-    }
-    __syncthreads();
-    if (fail) break;
-    const double rinv = 1.0 / (double)real_(S[j][j]);
-    for (int i = j + 1 + tid; i < n; i += blockDim.x) S[i][j] = scale_real(S[i][j], (typename Traits<T>::real)rinv);
-    __syncthreads();
-    // trailing update of the lower triangle: S(i,k) -= S(i,j)*conj(S(k,j)), k>j, i>=k
-    const int rem = n - j - 1;
-    for (int idx = tid; idx < rem * rem; idx += blockDim.x) {
-      int i = j + 1 + idx % rem, k = j + 1 + idx / rem;
-      if (i >= k) {
-        T v = fnma_(S[i][j], conj_(S[k][j]), S[i][k]);
-        if (i == k) v = from_real<T>((double)real_(v));
-        S[i][k] = v;
-      }
-    }
-    __syncthreads();
-  }
-  if (fail) {
-    if (tid == 0) atomicCAS(info, 0, info_off + fail);
-    // LAPACK leaves the leading (fail-1) columns factored; write those back
-  }
-  const int ncols_done = fail ? fail - 1 : n;
-  for (int idx = tid; idx < n * n; idx += blockDim.x) {
-    int i = idx % n, j = idx / n;
-    if (lower) { if (i >= j && j < ncols_done) A[i + (int64_t)j * lda] = S[i][j]; }
-    else       { if (i <= j && i < ncols_done) A[i + (int64_t)j * lda] = conj_(S[j][i]); }
-  }
-}
-
-template <typename T>
-void potrf_rec(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info,
-               int64_t off) {
-  if (n <= POTF2_NB) {
-    size_t smem = sizeof(T) * POTF2_NB * (POTF2_NB + 1);
-    potf2_kernel<T><<<1, 256, smem, ctx.stream>>>(uplo == Lower, (int)n, A, lda, d_info, (int)off);
-    LA_CUDA_CHECK(cudaGetLastError());
-    return;
-  }
-  int64_t n1 = round_up(n / 2, POTF2_NB);
-  if (n1 >= n) n1 = n / 2;
-  int64_t n2 = n - n1;
-  T* A11 = A;
-  T* A22 = A + n1 + n1 * lda;
-  potrf_rec<T>(ctx, uplo, n1, A11, lda, d_info, off);
-  if (uplo == Lower) {
-    T* A21 = A + n1;
-    // A21 <- A21 * L11^-H ;  A22 <- A22 - A21*A21^H
-    trsm<T>(ctx, Right, Lower, OpC, NonUnit, n2, n1, one<T>(), A11, lda, A21, lda);
-    herk<T>(ctx, Lower, OpN, n2, n1, -1.0, A21, lda, 1.0, A22, lda);
-  } else {
-    T* A12 = A + n1 * lda;
-    // A12 <- U11^-H * A12 ;  A22 <- A22 - A12^H*A12
-    trsm<T>(ctx, Left, Upper, OpC, NonUnit, n1, n2, one<T>(), A11, lda, A12, lda);
-    herk<T>(ctx, Upper, OpC, n2, n1, -1.0, A12, lda, 1.0, A22, lda);
-  }
-  potrf_rec<T>(ctx, uplo, n2, A22, lda, d_info, off + n1);
-}
-
-}  // namespace
-
-template <typename T>
-void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
-  LA_CUDA_CHECK(cudaMemsetAsync(d_info, 0, sizeof(int), ctx.stream));
-  if (n <= 0) return;
-  static bool attr_set = false;
-  if (!attr_set) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(potf2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)(sizeof(T) * POTF2_NB * (POTF2_NB + 1))));
-  }
-  potrf_rec<T>(ctx, uplo, n, A, lda, d_info, 0);
-}
-
-template <typename T>
-void potrs(Context& ctx, Uplo uplo, int64_t n, int64_t nrhs, const T* A, int64_t lda, T* B,
-           int64_t ldb) {
-  if (n <= 0 || nrhs <= 0) return;
-  if (uplo == Lower) {
-    trsm<T>(ctx, Left, Lower, OpN, NonUnit, n, nrhs, one<T>(), A, lda, B, ldb);
-    trsm<T>(ctx, Left, Lower, OpC, NonUnit, n, nrhs, one<T>(), A, lda, B, ldb);
-  } else {
-    trsm<T>(ctx, Left, Upper, OpC, NonUnit, n, nrhs, one<T>(), A, lda, B, ldb);
-    trsm<T>(ctx, Left, Upper, OpN, NonUnit, n, nrhs, one<T>(), A, lda, B, ldb);
-  }
-}
 
 // =========================================================================== LU
 template <typename T>
@@ -374,8 +250,6 @@ void trtrs(Context& ctx, Uplo uplo, Op trans, Diag diag, int64_t n, int64_t nrhs
 }
 
 #define LA_INST_FACTOR(T)                                                                         \
-  template void potrf<T>(Context&, Uplo, int64_t, T*, int64_t, int*);                             \
-  template void potrs<T>(Context&, Uplo, int64_t, int64_t, const T*, int64_t, T*, int64_t);       \
   template void laswp<T>(Context&, int64_t, T*, int64_t, int64_t, int64_t, const int*, bool);     \
   template void getrf<T>(Context&, int64_t, int64_t, T*, int64_t, int*, int*);                    \
   template void getrs<T>(Context&, Op, int64_t, int64_t, const T*, int64_t, const int*, T*,       \

@@ -120,8 +120,12 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   const int rs = blockIdx.x * rpc;
   const int nr = max(0, min(m - rs, rpc));
 
-  for (int c = 0; c < jb; c++)
-    for (int r = tid; r < nr; r += LU_NT) S[c * rpc + r] = A[(int64_t)(rs + r) + (int64_t)c * lda];
+  // each thread stages its rows with several independent loads in flight (coalesced over r)
+  for (int r = tid; r < nr; r += LU_NT) {
+    const T* src = A + (int64_t)(rs + r);
+#pragma unroll 8
+    for (int c = 0; c < jb; c++) S[c * rpc + r] = src[(int64_t)c * lda];
+  }
   __syncthreads();
 
   // arg-max of column 0 over owned rows
@@ -219,8 +223,11 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
     // prow / sval are rewritten only after the next __syncthreads pair, S rows are private
   }
   __syncthreads();
-  for (int c = 0; c < jb; c++)
-    for (int r = tid; r < nr; r += LU_NT) A[(int64_t)(rs + r) + (int64_t)c * lda] = S[c * rpc + r];
+  for (int r = tid; r < nr; r += LU_NT) {
+    T* dst = A + (int64_t)(rs + r);
+#pragma unroll 8
+    for (int c = 0; c < jb; c++) dst[(int64_t)c * lda] = S[c * rpc + r];
+  }
 }
 
 }  // namespace
