@@ -21,10 +21,17 @@ template <> struct PotfCfg<zcomplex> { static constexpr int NB = 64; };
 constexpr int POTF_IB = 32;
 constexpr int POTF_NT = 256;
 
+template <typename T> __device__ __forceinline__ T shfl_T(T v, int src) {
+  return __shfl_sync(0xffffffffu, v, src);
+}
+template <> __device__ __forceinline__ zcomplex shfl_T<zcomplex>(zcomplex v, int src) {
+  return zcomplex{__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src)};
+}
+
 template <typename T>
 constexpr size_t potf2_smem_bytes() {
   return sizeof(T) * ((size_t)PotfCfg<T>::NB * (PotfCfg<T>::NB + 1) + POTF_IB * (POTF_IB + 1) +
-                      (size_t)POTF_IB * PotfCfg<T>::NB);
+                      (size_t)POTF_IB * PotfCfg<T>::NB + POTF_IB);
 }
 
 // Leaf: one CTA factors an n x n diagonal block (n <= NB) held in shared memory, 32 columns at a
@@ -45,6 +52,7 @@ potf2_kernel(int lower, int n, T* __restrict__ A, int64_t lda, int* info, int in
   T* S = reinterpret_cast<T*>(smem_raw);  // S[i * LDS + j], lower triangle
   T* Ms = S + NB * LDS;                   // conj(D) of the current diagonal block
   T* Pt = Ms + POTF_IB * LDM;             // Pt[c * NB + i]: solved panel, transposed
+  T* rdiag = Pt + POTF_IB * NB;           // 1 / diag(D)
   __shared__ int fail;
   if (*info != 0) return;  // an earlier block already failed: LAPACK would have stopped there
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -58,34 +66,46 @@ potf2_kernel(int lower, int n, T* __restrict__ A, int64_t lda, int* info, int in
   int done_cols = n;
   for (int j0 = 0; j0 < n; j0 += POTF_IB) {
     const int jb = min(POTF_IB, n - j0);
-    if (warp == 0) {  // ---- (1) diagonal block
+    if (warp == 0) {  // ---- (1) diagonal block: lane i keeps row i in registers
       T* D = S + j0 * LDS + j0;
+      T a[POTF_IB];
+#pragma unroll
+      for (int c = 0; c < POTF_IB; c++)
+        a[c] = (lane < jb && c <= lane) ? D[lane * LDS + c] : zero<T>();
       int f = 0;
-      for (int j = 0; j < jb; j++) {
-        const double d = (double)real_(D[j * LDS + j]);
-        if (!(d > 0.0)) { f = j0 + j + 1; break; }  // also catches NaN; uniform over the warp
-        const double sq = sqrt(d);
-        const R rinv = (R)(1.0 / sq);
-        __syncwarp();
-        if (lane == j) D[j * LDS + j] = from_real<T>(sq);
-        if (lane > j && lane < jb) D[lane * LDS + j] = scale_real(D[lane * LDS + j], rinv);
-        __syncwarp();
-        if (lane > j && lane < jb) {
-          const T lij = D[lane * LDS + j];
-          for (int k = j + 1; k <= lane; k++) {
-            T v = fnma_(lij, conj_(D[k * LDS + j]), D[lane * LDS + k]);
-            if (k == lane) v = from_real<T>((double)real_(v));
-            D[lane * LDS + k] = v;
+#pragma unroll
+      for (int j = 0; j < POTF_IB; j++) {
+        if (j < jb && !f) {
+          const double d = __shfl_sync(0xffffffffu, (double)real_(a[j]), j);
+          if (!(d > 0.0)) {
+            f = j0 + j + 1;  // also catches NaN; uniform over the warp
+          } else {
+            const double sq = sqrt(d);
+            const R rinv = (R)(1.0 / sq);
+            if (lane == j) { a[j] = from_real<T>(sq); rdiag[j] = from_real<T>(1.0 / sq); }
+            if (lane > j) a[j] = scale_real(a[j], rinv);
+            // a(i,k) -= a(i,j) * conj(a(k,j)) for j < k <= i; a(k,j) lives in lane k
+#pragma unroll
+            for (int k = j + 1; k < POTF_IB; k++) {
+              const T akj = shfl_T(a[j], k);
+              if (lane >= k) {
+                T v = fnma_(a[j], conj_(akj), a[k]);
+                if (lane == k) v = from_real<T>((double)real_(v));
+                a[k] = v;
+              }
+            }
           }
         }
-        __syncwarp();
       }
       if (f && lane == 0) fail = f;
-      if (!f)
-        for (int idx = lane; idx < jb * jb; idx += 32) {
-          int r = idx / jb, c = idx % jb;
-          Ms[r * LDM + c] = c <= r ? conj_(D[r * LDS + c]) : zero<T>();
-        }
+      if (!f && lane < jb) {
+#pragma unroll
+        for (int c = 0; c < POTF_IB; c++)
+          if (c < jb) {
+            if (c <= lane) D[lane * LDS + c] = a[c];
+            Ms[lane * LDM + c] = c <= lane ? conj_(a[c]) : zero<T>();
+          }
+      }
     }
     __syncthreads();
     if (fail) { done_cols = j0; break; }
@@ -96,7 +116,7 @@ potf2_kernel(int lower, int n, T* __restrict__ A, int64_t lda, int* info, int in
       T x[POTF_IB];
 #pragma unroll
       for (int c = 0; c < POTF_IB; c++) x[c] = c < jb ? S[i * LDS + j0 + c] : zero<T>();
-      solve_vec_regs<T, POTF_IB, LDM>(Ms, jb, true, false, one<T>(), x);
+      solve_vec_regs<T, POTF_IB, LDM>(Ms, rdiag, jb, true, false, one<T>(), x);
 #pragma unroll
       for (int c = 0; c < POTF_IB; c++)
         if (c < jb) { S[i * LDS + j0 + c] = x[c]; Pt[c * NB + tid] = x[c]; }

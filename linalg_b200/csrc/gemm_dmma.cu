@@ -84,7 +84,7 @@ struct GemmParams {
   double* C;
   int64_t ldc;
   int tri;
-  int tiles_m, tiles_n;
+  int tiles_m, tiles_n, num_tiles;
 };
 
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
@@ -103,7 +103,52 @@ __device__ __forceinline__ uint32_t frag_off(int mn, int k) {
     return (uint32_t)(mn * 128 + ((((k >> 1) ^ (mn & 7))) << 4) + ((k & 1) << 3));
 }
 
-__device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
+// Tile t -> (tm, tn).  Full products walk groups of GROUP_M tile rows (L2 reuse of the A rows of
+// a group and of the B columns it sweeps).  Masked (SYRK-style) products enumerate only the
+// tiles that intersect the stored triangle, in the same banded order, so that the persistent
+// CTAs stay balanced.  Lower: valid tiles have tm >= tn (BM == BN).
+__host__ __device__ inline int tri_band_count(int g0, int gsz, int TN, int& cnt_full) {
+  const int cols_full = (g0 + 1 < TN) ? g0 + 1 : TN;
+  cnt_full = cols_full * gsz;
+  int cnt_part = 0;
+  const int tend = (g0 + gsz < TN) ? g0 + gsz : TN;
+  for (int tn = g0 + 1; tn < tend; tn++) cnt_part += g0 + gsz - tn;
+  return cnt_full + cnt_part;
+}
+__host__ __device__ inline int tri_tile_count(int TM, int TN) {
+  int total = 0;
+  for (int g0 = 0; g0 < TM; g0 += GROUP_M) {
+    int cf;
+    total += tri_band_count(g0, (TM - g0 < GROUP_M) ? TM - g0 : GROUP_M, TN, cf);
+  }
+  return total;
+}
+__device__ __forceinline__ void tri_tile_coords(int t, int TM, int TN, int& tm, int& tn) {
+  int g0 = 0, gsz, cnt_full;
+  while (true) {
+    gsz = min(GROUP_M, TM - g0);
+    const int cnt = tri_band_count(g0, gsz, TN, cnt_full);
+    if (t < cnt) break;
+    t -= cnt;
+    g0 += gsz;
+  }
+  if (t < cnt_full) {
+    tn = t / gsz;
+    tm = g0 + t % gsz;
+  } else {
+    t -= cnt_full;
+    for (tn = g0 + 1;; tn++) {
+      const int c = g0 + gsz - tn;
+      if (t < c) { tm = tn + t; break; }
+      t -= c;
+    }
+  }
+}
+
+__device__ __forceinline__ void tile_coords(int tri, int t, int tiles_m, int tiles_n, int& tm,
+                                            int& tn) {
+  if (tri == TriLower) { tri_tile_coords(t, tiles_m, tiles_n, tm, tn); return; }
+  if (tri == TriUpper) { tri_tile_coords(t, tiles_n, tiles_m, tn, tm); return; }
   const int per_group = GROUP_M * tiles_n;
   const int g = t / per_group;
   const int first_m = g * GROUP_M;
@@ -111,12 +156,6 @@ __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int
   const int r = t - g * per_group;
   tm = first_m + r % gsz;
   tn = r / gsz;
-}
-
-__device__ __forceinline__ bool tile_skipped(int tri, int tm, int tn) {
-  if (tri == TriLower) return tm * BM + BM - 1 < tn * BN;
-  if (tri == TriUpper) return tm * BM > tn * BN + BN - 1;
-  return false;
 }
 
 template <bool A_MN, bool B_MN>
@@ -138,7 +177,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   __syncthreads();
 
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int num_tiles = p.num_tiles;
   const int kblocks = (int)((p.k + BK - 1) / BK);
 
   if (warp >= CONSUMER_WARPS) {
@@ -151,8 +190,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         int tm, tn;
-        tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-        if (tile_skipped(p.tri, tm, tn)) continue;
+        tile_coords(p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
         const int m0 = tm * BM, n0 = tn * BN;
         for (int kb = 0; kb < kblocks; kb++) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -192,8 +230,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
     int tm, tn;
-    tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-    if (tile_skipped(p.tri, tm, tn)) continue;
+    tile_coords(p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
 
     double acc[8][4][2];
 #pragma unroll
@@ -258,7 +295,7 @@ void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     LA_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr = true;
   }
-  int tiles = p.tiles_m * p.tiles_n;
+  int tiles = p.num_tiles;
   int grid = tiles < ctx.sm_count ? tiles : ctx.sm_count;
   kern<<<grid, NTHREADS, SMEM_BYTES, ctx.stream>>>(tmA, tmB, p);
   LA_CUDA_CHECK(cudaGetLastError());
@@ -301,6 +338,10 @@ bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, 
   p.tiles_m = (int)ceil_div(m, BM);
   p.tiles_n = (int)ceil_div(n, BN);
   if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
+  if (tri == TriLower) p.num_tiles = tri_tile_count(p.tiles_m, p.tiles_n);
+  else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
+  else p.num_tiles = p.tiles_m * p.tiles_n;
+  if (p.num_tiles <= 0) return true;
   if (a_mn && b_mn) launch<true, true>(ctx, tmA, tmB, p);
   else if (a_mn && !b_mn) launch<true, false>(ctx, tmA, tmB, p);
   else if (!a_mn && b_mn) launch<false, true>(ctx, tmA, tmB, p);

@@ -193,7 +193,7 @@ template <> struct TrsmCfg<zcomplex> { static constexpr int NB = 32, NT = 64; };
 template <typename T>
 constexpr size_t trsm_smem_bytes() {
   return sizeof(T) * (size_t)TrsmCfg<T>::NB * (TrsmCfg<T>::NB + 1) +
-         sizeof(T) * (size_t)TrsmCfg<T>::NB * (TrsmCfg<T>::NT + 1);
+         sizeof(T) * (size_t)TrsmCfg<T>::NB * (TrsmCfg<T>::NT + 1) + sizeof(T) * TrsmCfg<T>::NB;
 }
 
 template <typename T>
@@ -204,6 +204,7 @@ trsm_base_kernel(int right, int a_lower, int op, int unit, int na, int64_t nvec,
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* Ms = reinterpret_cast<T*>(smem_raw);   // effective matrix M (see below), row pitch LDM
   T* Xs = Ms + NB * LDM;                    // Left side staging: Xs[i * LDX + v]
+  T* rdiag = Xs + NB * LDX;                 // reciprocals of M's diagonal
   // M = op(A) for Left;  M = op(A)^T for Right (x*op(A) = b  <=>  M x^T = b^T).
   for (int idx = threadIdx.x; idx < na * na; idx += NT) {
     int i = idx % na, j = idx / na;  // stored element A(i,j); only the stored triangle is read
@@ -226,16 +227,20 @@ trsm_base_kernel(int right, int a_lower, int op, int unit, int na, int64_t nvec,
     for (int i = 0; i < NB; i++)
       x[i] = (i < na && t < nv) ? B[v0 + t + (int64_t)i * ldb] : zero<T>();
     __syncthreads();
+    if (t < na && !unit) rdiag[t] = recip(Ms[t * LDM + t]);
+    __syncthreads();
   } else {
     for (int idx = t; idx < na * nv; idx += NT) {
       int i = idx % na, v = idx / na;
       Xs[i * LDX + v] = B[i + (v0 + v) * ldb];
     }
     __syncthreads();
+    if (t < na && !unit) rdiag[t] = recip(Ms[t * LDM + t]);
 #pragma unroll
     for (int i = 0; i < NB; i++) x[i] = (i < na && t < nv) ? Xs[i * LDX + t] : zero<T>();
+    __syncthreads();
   }
-  if (t < nv) solve_vec_regs<T, NB, LDM>(Ms, na, eff_lower, unit != 0, alpha, x);
+  if (t < nv) solve_vec_regs<T, NB, LDM>(Ms, rdiag, na, eff_lower, unit != 0, alpha, x);
   if (right) {
 #pragma unroll
     for (int i = 0; i < NB; i++)

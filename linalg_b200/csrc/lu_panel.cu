@@ -24,10 +24,11 @@ namespace la {
 
 namespace {
 
-constexpr int LU_NT = 256;
+constexpr int LU_NT = 512;
 constexpr int LU_MAX_JB = 32;
 constexpr int LU_MAX_CTAS = 160;
-constexpr size_t LU_SMEM_BUDGET = 200 * 1024;
+constexpr size_t LU_SMEM_BUDGET = 136 * 1024;   // row slice; the landing areas come on top
+constexpr size_t LU_SMEM_TOTAL = 224 * 1024;
 
 struct __align__(16) LLPacket {
   unsigned long long data;
@@ -36,6 +37,9 @@ struct __align__(16) LLPacket {
 
 template <typename T> struct Words { static constexpr int N = 1; };
 template <> struct Words<zcomplex> { static constexpr int N = 2; };
+// widest leaf per element type (the row is staged in registers during the update)
+template <typename T> struct MaxJb { static constexpr int N = LU_MAX_JB; };
+template <> struct MaxJb<zcomplex> { static constexpr int N = 16; };
 
 struct LuExchange {
   LLPacket hdr[2][LU_MAX_CTAS];                       // data = |a| (double bits); tag = seq<<32 | row
@@ -108,15 +112,18 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
                 int* info, LuExchange* xch, int rpc, unsigned seq_base) {
   using R = typename Traits<T>::real;
   constexpr int W = Words<T>::N;
+  constexpr int NW = LU_NT / 32;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  T* S = reinterpret_cast<T*>(smem_raw);  // S[c * rpc + r]
-  __shared__ T prow[LU_MAX_JB];
-  __shared__ double sval[LU_NT / 32];
-  __shared__ int sidx[LU_NT / 32];
-  __shared__ int s_pi;
+  const int G = gridDim.x;
+  T* S = reinterpret_cast<T*>(smem_raw);         // S[c * rpc + r]: this CTA's row slice
+  T* rows_all = S + (size_t)jb * rpc;            // rows_all[g * jb + c]: every CTA's candidate row
+  T* rj = rows_all + (size_t)G * jb;             // rj[c]: row j of the panel
+  double* hv = reinterpret_cast<double*>(((uintptr_t)(rj + LU_MAX_JB) + 7) & ~(uintptr_t)7);  // headers
+  int* hi = reinterpret_cast<int*>(hv + G);
+  __shared__ double sval[NW];
+  __shared__ int sidx[NW];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int G = gridDim.x;
   const int rs = blockIdx.x * rpc;
   const int nr = max(0, min(m - rs, rpc));
 
@@ -126,78 +133,83 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
 #pragma unroll 8
     for (int c = 0; c < jb; c++) S[c * rpc + r] = src[(int64_t)c * lda];
   }
-  __syncthreads();
-
-  // arg-max of column 0 over owned rows
+  // arg-max of column 0 over owned rows (each thread only ever touches its own rows of S)
   double bv = -1.0;
   int bi = 0x7fffffff;
   for (int r = tid; r < nr; r += LU_NT) {
     double v = (double)abs1(S[r]);
-    if (v > bv || bi == 0x7fffffff) { bv = v; bi = rs + r; }   // NaN-safe: first row always taken
+    if (v > bv || bi == 0x7fffffff) { bv = v; bi = rs + r; }  // NaN-safe: first row always taken
   }
 
   for (int j = 0; j < jb; j++) {
     const int par = j & 1;
     const unsigned seq = seq_base + (unsigned)j + 1u;
-    // ---- CTA-level arg-max: warps reduce, warp 0 finishes
+    // ---- CTA-level arg-max: warps reduce, warp 0 finishes and publishes
     warp_argmax(bv, bi);
     if (lane == 0) { sval[warp] = bv; sidx[warp] = bi; }
     __syncthreads();
     if (warp == 0) {
-      double cv = lane < LU_NT / 32 ? sval[lane] : -2.0;
-      int ci = lane < LU_NT / 32 ? sidx[lane] : 0x7fffffff;
+      double cv = lane < NW ? sval[lane] : -2.0;
+      int ci = lane < NW ? sidx[lane] : 0x7fffffff;
       warp_argmax(cv, ci);
-      // ---- publish candidate, its row, and row j
       const bool have = ci != 0x7fffffff;
-      if (lane == 0)
-        ll_store(&xch->hdr[par][blockIdx.x], (unsigned long long)__double_as_longlong(cv),
-                 ((unsigned long long)seq << 32) | (unsigned)(have ? ci : 0xffffffffu));
-      if (have && lane < jb)
-        ll_put<T>(&xch->row[par][blockIdx.x][lane * W], S[lane * rpc + (ci - rs)], seq);
-      if (j >= rs && j < rs + nr && lane < jb)
-        ll_put<T>(&xch->rowj[par][lane * W], S[lane * rpc + (j - rs)], seq);
-      // ---- gather all headers, pick the winner
-      double pv = -1.0;
-      int pi = 0x7fffffff, pg = 0;
-      for (int g = lane; g < G; g += 32) {
-        unsigned long long d, t;
-        ll_wait(&xch->hdr[par][g], seq, d, t);
-        double v = __longlong_as_double((long long)d);
-        unsigned uidx = (unsigned)(t & 0xffffffffull);
-        int idx = uidx == 0xffffffffu ? 0x7fffffff : (int)uidx;
-        if (idx != 0x7fffffff && (pi == 0x7fffffff || v > pv || (v == pv && idx < pi))) {
-          pv = v; pi = idx; pg = g;
-        }
-      }
-      {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          double ov = __shfl_xor_sync(0xffffffffu, pv, o);
-          int oi = __shfl_xor_sync(0xffffffffu, pi, o);
-          int og = __shfl_xor_sync(0xffffffffu, pg, o);
-          if (oi != 0x7fffffff && (pi == 0x7fffffff || ov > pv || (ov == pv && oi < pi))) {
-            pv = ov; pi = oi; pg = og;
-          }
-        }
-      }
-      // ---- fetch the pivot row and row j, swap in place
-      T pr = zero<T>(), rj = zero<T>();
-      if (lane < jb) {
-        pr = ll_get<T>(&xch->row[par][pg][lane * W], seq);
-        if (pi != j) rj = ll_get<T>(&xch->rowj[par][lane * W], seq);
-        prow[lane] = pr;
-        if (pi != j) {
-          if (pi >= rs && pi < rs + nr) S[lane * rpc + (pi - rs)] = rj;
-          if (j >= rs && j < rs + nr) S[lane * rpc + (j - rs)] = pr;
-        }
-      }
-      if (lane == 0) {
-        s_pi = pi;
-        if (blockIdx.x == 0) ipiv[j] = row0 + pi + 1;
+      const T crow = (have && lane < jb) ? S[lane * rpc + (ci - rs)] : zero<T>();
+      const bool own_j = j >= rs && j < rs + nr;
+      if (G == 1) {  // single CTA: no global exchange
+        if (lane == 0) { hv[0] = cv; hi[0] = ci; }
+        if (lane < jb) { rows_all[lane] = crow; rj[lane] = S[lane * rpc + (j - rs)]; }
+      } else {
+        if (lane == 0)
+          ll_store(&xch->hdr[par][blockIdx.x], (unsigned long long)__double_as_longlong(cv),
+                   ((unsigned long long)seq << 32) | (unsigned)(have ? ci : 0xffffffffu));
+        if (lane < jb) ll_put<T>(&xch->row[par][blockIdx.x][lane * W], crow, seq);
+        if (own_j && lane < jb) ll_put<T>(&xch->rowj[par][lane * W], S[lane * rpc + (j - rs)], seq);
       }
     }
+    // ---- all warps gather: warp w lands the packets of CTAs w, w+NW, ... in shared memory
+    if (G > 1) {
+      for (int g = warp; g < G; g += NW) {
+        if (lane < jb) rows_all[g * jb + lane] = ll_get<T>(&xch->row[par][g][lane * W], seq);
+        if (lane == 31) {
+          unsigned long long d, t;
+          ll_wait(&xch->hdr[par][g], seq, d, t);
+          hv[g] = __longlong_as_double((long long)d);
+          const unsigned uidx = (unsigned)(t & 0xffffffffull);
+          hi[g] = uidx == 0xffffffffu ? 0x7fffffff : (int)uidx;
+        }
+      }
+      if (warp == NW - 1 && lane < jb) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
+    }
     __syncthreads();
-    // ---- scale column j, rank-1 update, and arg-max of column j+1 in the same pass
+    // ---- every warp derives the same winner from the landed headers
+    double pv = -1.0;
+    int pi = 0x7fffffff, pg = 0;
+    for (int g = lane; g < G; g += 32) {
+      const double v = hv[g];
+      const int idx = hi[g];
+      if (idx != 0x7fffffff && (pi == 0x7fffffff || v > pv || (v == pv && idx < pi))) {
+        pv = v; pi = idx; pg = g;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ov = __shfl_xor_sync(0xffffffffu, pv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, pi, o);
+      const int og = __shfl_xor_sync(0xffffffffu, pg, o);
+      if (oi != 0x7fffffff && (pi == 0x7fffffff || ov > pv || (ov == pv && oi < pi))) {
+        pv = ov; pi = oi; pg = og;
+      }
+    }
+    const T* prow = rows_all + pg * jb;
+    if (blockIdx.x == 0 && tid == 0) ipiv[j] = row0 + pi + 1;
+    // ---- row interchange j <-> pi inside the slices that own them (warp 0, one lane per column)
+    if (pi != j && warp == 0 && lane < jb) {
+      if (pi >= rs && pi < rs + nr) S[lane * rpc + (pi - rs)] = rj[lane];
+      if (j >= rs && j < rs + nr) S[lane * rpc + (j - rs)] = prow[lane];
+    }
+    __syncthreads();
+    // ---- scale column j, rank-1 update of the columns to its right, and the arg-max of
+    //      column j+1 in the same pass; each thread works on its own rows only
     const T pivot = prow[j];
     const bool zero_pivot = is_zero(pivot);
     if (zero_pivot && blockIdx.x == 0 && tid == 0) atomicCAS(info, 0, row0 + j + 1);
@@ -207,20 +219,38 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
     bi = 0x7fffffff;
     for (int r = tid; r < nr; r += LU_NT) {
       const int gr = rs + r;
-      if (gr > j) {
-        if (!zero_pivot) {
-          const T a = S[j * rpc + r];
-          const T l = use_recip ? mul(a, rinv) : div_(a, pivot);
-          S[j * rpc + r] = l;
-          for (int c = j + 1; c < jb; c++) S[c * rpc + r] = fnma_(l, prow[c], S[c * rpc + r]);
-        }
+      if (gr <= j) continue;
+      T* row = S + r;
+      if (zero_pivot) {  // as ?getf2: nothing to scale, the update is a no-op
         if (j + 1 < jb) {
-          double v = (double)abs1(S[(j + 1) * rpc + r]);
-          if (v > bv || bi == 0x7fffffff) { bv = v; bi = gr; }
+          const double av = (double)abs1(row[(j + 1) * rpc]);
+          if (av > bv || bi == 0x7fffffff) { bv = av; bi = gr; }
         }
+        continue;
       }
+      const T a = row[j * rpc];
+      const T l = use_recip ? mul(a, rinv) : div_(a, pivot);
+      row[j * rpc] = l;
+      int c = j + 1;
+      if (c < jb) {
+        const T x = fnma_(l, prow[c], row[c * rpc]);
+        row[c * rpc] = x;
+        const double av = (double)abs1(x);
+        if (av > bv || bi == 0x7fffffff) { bv = av; bi = gr; }
+        c++;
+      }
+      for (; c + 3 < jb; c += 4) {  // loads first, so that four updates are in flight
+        const T x0 = row[c * rpc], x1 = row[(c + 1) * rpc], x2 = row[(c + 2) * rpc],
+                x3 = row[(c + 3) * rpc];
+        const T p0 = prow[c], p1 = prow[c + 1], p2 = prow[c + 2], p3 = prow[c + 3];
+        row[c * rpc] = fnma_(l, p0, x0);
+        row[(c + 1) * rpc] = fnma_(l, p1, x1);
+        row[(c + 2) * rpc] = fnma_(l, p2, x2);
+        row[(c + 3) * rpc] = fnma_(l, p3, x3);
+      }
+      for (; c < jb; c++) row[c * rpc] = fnma_(l, prow[c], row[c * rpc]);
     }
-    // prow / sval are rewritten only after the next __syncthreads pair, S rows are private
+    // landing areas and sval are rewritten only after the next column's first __syncthreads
   }
   __syncthreads();
   for (int r = tid; r < nr; r += LU_NT) {
@@ -263,7 +293,8 @@ void lu_panel_adopt_exchange(Context& ctx, void* device_mem, void* state_storage
 int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
   int64_t rpc = round_up(ceil_div(m, ctx.sm_count), 2);
   int64_t nb0 = (int64_t)(LU_SMEM_BUDGET / (rpc * elem_bytes));
-  if (nb0 > LU_MAX_JB) nb0 = LU_MAX_JB;
+  const int64_t cap = elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
+  if (nb0 > cap) nb0 = cap;
   return (int)nb0;
 }
 
@@ -274,7 +305,7 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
   if (!attr) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)LU_SMEM_BUDGET));
+                                       (int)LU_SMEM_TOTAL));
     attr = true;
   }
   LuPanelState* st = panel_state(ctx);
@@ -294,6 +325,8 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
     fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
     abort();
   }
+  // landing areas: every CTA's candidate row, row j, headers
+  smem += ((size_t)G * jb + LU_MAX_JB) * sizeof(T) + (size_t)G * (sizeof(double) + sizeof(int)) + 16;
   int mi = (int)m, row0i = (int)row0, rpci = (int)rpc;
   unsigned seq_base = st->seq;
   st->seq += 64;
