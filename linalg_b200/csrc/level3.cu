@@ -6,8 +6,13 @@
 // kernels inside ?getrf/?potrf/?getrs/?potrs/?trtrs.
 #include "la_internal.h"
 #include "tri_small.cuh"
+#include <type_traits>
 
 namespace la {
+
+// trsm_dmma.cu
+bool trsm_base_dmma_f64(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, int64_t n,
+                        double alpha, const double* A, int64_t lda, double* B, int64_t ldb);
 
 // ------------------------------------------------------------------ GEMM dispatch
 int& last_gemm_path() {
@@ -264,6 +269,9 @@ void trsm_rec(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, i
   const int64_t nvec = side == Left ? n : m;
   constexpr int TRSM_NB = TrsmCfg<T>::NB;
   if (na <= TRSM_NB) {
+    if constexpr (std::is_same<T, double>::value) {
+      if (trsm_base_dmma_f64(ctx, side, uplo, op, diag, m, n, alpha, A, lda, B, ldb)) return;
+    }
     constexpr int TRSM_NT = TrsmCfg<T>::NT;
     static bool attr = false;
     if (!attr) {
