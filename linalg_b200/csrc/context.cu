@@ -129,6 +129,24 @@ Context* thread_context(cudaStream_t stream) {
   return per_device[dev];
 }
 
+Context* side_context(Context& c) {
+  if (!c.side) {
+    Context* s = new Context();
+    s->device = c.device;
+    s->sm_count = c.sm_count;
+    s->allow_side_stream = false;
+    int lo = 0, hi = 0;
+    LA_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    LA_CUDA_CHECK(cudaStreamCreateWithPriority(&s->stream, cudaStreamNonBlocking, hi));
+    s->owns_stream = true;
+    for (auto& e : s->ev) LA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c.side = s;
+  }
+  if (!c.ev[0])
+    for (auto& e : c.ev) LA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  return c.side;
+}
+
 void* pinned_scratch(Context& c, size_t bytes) {
   if (bytes > c.pinned_size) {
     if (c.pinned) cudaFreeHost(c.pinned);

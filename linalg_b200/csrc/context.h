@@ -36,6 +36,9 @@ struct Context {
   void* pinned = nullptr;          // small pinned bounce buffer (info, ipiv)
   size_t pinned_size = 0;
   void* lu_state = nullptr;        // LU panel exchange area + launch sequence (lu_panel.cu)
+  int sm_limit = 0;                // > 0: persistent kernels use at most this many CTAs
+  bool allow_side_stream = true;   // look-ahead may create `side` (a stream, events, an arena)
+  Context* side = nullptr;         // second context for work overlapped with the main stream
   template <typename T> T* alloc(size_t n) { return (T*)arena.alloc(n * sizeof(T)); }
 };
 
@@ -54,5 +57,8 @@ struct ContextLease {
 Context* thread_context(cudaStream_t stream);
 
 void* pinned_scratch(Context& c, size_t bytes);
+
+// Lazily created companion context (own high-priority stream and arena) for look-ahead.
+Context* side_context(Context& c);
 
 }  // namespace la

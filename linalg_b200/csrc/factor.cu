@@ -187,18 +187,45 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   // trailing update (where nearly all flops are).  Keeping the interchanges per panel bounds
   // the serial part of laswp's net-permutation set-up to NB steps.
   const int64_t NB = k >= 8192 ? 512 : (k >= 2048 ? 256 : 128);
+  // Look-ahead: once the columns of the NEXT panel have received their update, that panel is
+  // factored on a side stream (a chain of latency-bound leaf launches that needs only a few
+  // SMs) while the main stream finishes the trailing update on the remaining SMs.
+  const int64_t leaf_ctas = ceil_div(m, 512);
+  const bool lookahead = ctx.allow_side_stream && k >= 4096 && leaf_ctas <= 40 && k > NB;
+  Context* side = lookahead ? side_context(ctx) : nullptr;
+  const int side_sms = (int)(leaf_ctas < 16 ? 16 : leaf_ctas);
+  bool panel_done = false;  // panel of the current j0 already factored (on the side stream)?
   for (int64_t j0 = 0; j0 < k; j0 += NB) {
     const int64_t jb = NB < k - j0 ? NB : k - j0;
-    getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
+    if (!panel_done) getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
+    panel_done = false;
     if (j0 > 0) laswp_rows<T>(ctx, m, j0, A, lda, j0, j0 + jb, d_ipiv);
     const int64_t nr = n - j0 - jb;  // columns to the right
-    if (nr > 0) {
-      T* A12 = A + j0 + (j0 + jb) * lda;
-      laswp_rows<T>(ctx, m, nr, A + (j0 + jb) * lda, lda, j0, j0 + jb, d_ipiv);
-      trsm<T>(ctx, Left, Lower, OpN, Unit, jb, nr, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
-      if (m - j0 - jb > 0)
-        gemm<T>(ctx, OpN, OpN, m - j0 - jb, nr, jb, from_real<T>(-1.0), A + (j0 + jb) + j0 * lda,
-                lda, A12, lda, one<T>(), A + (j0 + jb) + (j0 + jb) * lda, lda);
+    if (nr <= 0) continue;
+    T* A12 = A + j0 + (j0 + jb) * lda;
+    laswp_rows<T>(ctx, m, nr, A + (j0 + jb) * lda, lda, j0, j0 + jb, d_ipiv);
+    trsm<T>(ctx, Left, Lower, OpN, Unit, jb, nr, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
+    const int64_t mr = m - j0 - jb;
+    if (mr <= 0) continue;
+    const T* A21 = A + (j0 + jb) + j0 * lda;
+    T* A22 = A + (j0 + jb) + (j0 + jb) * lda;
+    const int64_t j1 = j0 + jb;
+    const int64_t jb1 = j1 < k ? (NB < k - j1 ? NB : k - j1) : 0;
+    if (lookahead && jb1 > 0 && nr > jb1) {
+      gemm<T>(ctx, OpN, OpN, mr, jb1, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
+      LA_CUDA_CHECK(cudaEventRecord(ctx.ev[0], ctx.stream));
+      LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));
+      side->sm_limit = side_sms;
+      getrf_rec<T>(*side, m, A, lda, d_ipiv, d_info, j1, jb1, plan);
+      LA_CUDA_CHECK(cudaEventRecord(side->ev[0], side->stream));
+      ctx.sm_limit = ctx.sm_count - side_sms;
+      gemm<T>(ctx, OpN, OpN, mr, nr - jb1, jb, from_real<T>(-1.0), A21, lda, A12 + jb1 * lda, lda,
+              one<T>(), A22 + jb1 * lda, lda);
+      ctx.sm_limit = 0;
+      LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, side->ev[0], 0));
+      panel_done = true;
+    } else {
+      gemm<T>(ctx, OpN, OpN, mr, nr, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
     }
   }
 }

@@ -296,7 +296,8 @@ void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     attr = true;
   }
   int tiles = p.num_tiles;
-  int grid = tiles < ctx.sm_count ? tiles : ctx.sm_count;
+  const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+  int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NTHREADS, SMEM_BYTES, ctx.stream>>>(tmA, tmB, p);
   LA_CUDA_CHECK(cudaGetLastError());
 }

@@ -83,6 +83,7 @@ NoAllocDevice* setup_current_device() {
     return nullptr;
   }
   d.ctx.device = dev;
+  d.ctx.allow_side_stream = false;   // look-ahead would create a stream and an arena
   d.ctx.sm_count = sms;
   la::lu_panel_adopt_exchange(d.ctx, base, d.panel_state);
   // the rest of the array becomes the (only) block of this context's bump arena

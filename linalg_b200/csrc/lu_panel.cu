@@ -122,6 +122,7 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   int* hi = reinterpret_cast<int*>(hv + G);
   __shared__ double sval[NW];
   __shared__ int sidx[NW];
+  __shared__ int s_pg;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rs = blockIdx.x * rpc;
@@ -181,33 +182,39 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
       if (warp == NW - 1 && lane < jb) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
     }
     __syncthreads();
-    // ---- every warp derives the same winner from the landed headers
-    double pv = -1.0;
-    int pi = 0x7fffffff, pg = 0;
-    for (int g = lane; g < G; g += 32) {
-      const double v = hv[g];
-      const int idx = hi[g];
-      if (idx != 0x7fffffff && (pi == 0x7fffffff || v > pv || (v == pv && idx < pi))) {
-        pv = v; pi = idx; pg = g;
+    // ---- warp 0 derives the winner from the landed headers, interchanges rows j <-> pi inside
+    //      the slices that own them (one lane per column) and posts (pi, pg) for the others
+    if (warp == 0) {
+      double pv = -1.0;
+      int pi = 0x7fffffff, pg = 0;
+      for (int g = lane; g < G; g += 32) {
+        const double v = hv[g];
+        const int idx = hi[g];
+        if (idx != 0x7fffffff && (pi == 0x7fffffff || v > pv || (v == pv && idx < pi))) {
+          pv = v; pi = idx; pg = g;
+        }
       }
-    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double ov = __shfl_xor_sync(0xffffffffu, pv, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, pi, o);
-      const int og = __shfl_xor_sync(0xffffffffu, pg, o);
-      if (oi != 0x7fffffff && (pi == 0x7fffffff || ov > pv || (ov == pv && oi < pi))) {
-        pv = ov; pi = oi; pg = og;
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, pv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, pi, o);
+        const int og = __shfl_xor_sync(0xffffffffu, pg, o);
+        if (oi != 0x7fffffff && (pi == 0x7fffffff || ov > pv || (ov == pv && oi < pi))) {
+          pv = ov; pi = oi; pg = og;
+        }
       }
-    }
-    const T* prow = rows_all + pg * jb;
-    if (blockIdx.x == 0 && tid == 0) ipiv[j] = row0 + pi + 1;
-    // ---- row interchange j <-> pi inside the slices that own them (warp 0, one lane per column)
-    if (pi != j && warp == 0 && lane < jb) {
-      if (pi >= rs && pi < rs + nr) S[lane * rpc + (pi - rs)] = rj[lane];
-      if (j >= rs && j < rs + nr) S[lane * rpc + (j - rs)] = prow[lane];
+      const T* pr = rows_all + pg * jb;
+      if (pi != j && lane < jb) {
+        if (pi >= rs && pi < rs + nr) S[lane * rpc + (pi - rs)] = rj[lane];
+        if (j >= rs && j < rs + nr) S[lane * rpc + (j - rs)] = pr[lane];
+      }
+      if (lane == 0) {
+        s_pg = pg;
+        if (blockIdx.x == 0) ipiv[j] = row0 + pi + 1;
+      }
     }
     __syncthreads();
+    const T* prow = rows_all + s_pg * jb;
     // ---- scale column j, rank-1 update of the columns to its right, and the arg-max of
     //      column j+1 in the same pass; each thread works on its own rows only
     const T pivot = prow[j];
