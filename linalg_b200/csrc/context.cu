@@ -85,6 +85,7 @@ static void init_context(Context* c, bool make_stream) {
     c->owns_stream = true;
   }
   LA_CUDA_CHECK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  LA_CUDA_CHECK(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
   for (auto& e : c->ev) LA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   LA_CUDA_CHECK(cudaMalloc(&c->d_info, 256));
   LA_CUDA_CHECK(cudaMemset(c->d_info, 0, 256));

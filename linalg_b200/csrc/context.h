@@ -28,7 +28,8 @@ struct Context {
   int device = 0;
   cudaStream_t stream = nullptr;   // compute stream of this context
   bool owns_stream = false;
-  cudaStream_t copy_stream = nullptr;  // H2D/D2H overlap in the host-pointer shims
+  cudaStream_t copy_stream = nullptr;  // H2D overlap in the host-pointer shims
+  cudaStream_t d2h_stream = nullptr;   // D2H overlap (the other PCIe direction)
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   Arena arena;
   int sm_count = 0;

@@ -10,8 +10,8 @@
 //   * persistent CTAs (one per SM), grouped tile order for L2 reuse;
 //   * CTA tile 128x128x16, 4-stage ring of TMA loads (cp.async.bulk.tensor.2d, 128-byte
 //     swizzle, zero fill at ragged edges) signalled through mbarriers;
-//   * 1 producer warpgroup (one elected lane issues TMA; setmaxnreg hands its registers to
-//     the consumers) + 8 consumer warps (2x4), warp tile 64x32 = 8x4 DMMA tiles, 64 FP64
+//   * 1 producer warpgroup (one elected lane issues TMA; a whole warpgroup because register
+//     allocation is per 4 warps: 384 threads x 168 registers fill the SM) + 8 consumer warps (2x4), warp tile 64x32 = 8x4 DMMA tiles, 64 FP64
 //     accumulators per thread;
 //   * both operand layouts per side (contiguous along M/N or along K), so NN/NT/TN/TT need
 //     no transposition pass;
@@ -70,7 +70,7 @@ namespace {
 
 constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4;
 constexpr int CONSUMER_WARPS = 8;
-constexpr int PRODUCER_WARPS = 4;  // a full warpgroup, so that setmaxnreg can hand its registers over
+constexpr int PRODUCER_WARPS = 4;  // warps are allocated in groups of four
 constexpr int NTHREADS = (CONSUMER_WARPS + PRODUCER_WARPS) * 32;
 constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KB
 constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KB
@@ -182,7 +182,10 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (warp >= CONSUMER_WARPS) {
     // ===================== TMA producer (one elected lane of the producer warpgroup) =======
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    // The producer warpgroup hands registers to the consumers.  Its own code must then fit in
+    // what it keeps (a larger footprint silently corrupts other warps' registers), hence the
+    // generous 56 and the rolled issue loops below.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (warp == CONSUMER_WARPS && lane == 0) {
       tma_prefetch_desc(&tmA);
       tma_prefetch_desc(&tmB);
@@ -199,14 +202,14 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           unsigned char* sB = sA + A_STAGE_BYTES;
           const int k0 = kb * BK;
           if (A_MN) {
-#pragma unroll
+#pragma unroll 1
             for (int j = 0; j < BM / 16; j++)
               tma_load_2d(sA + j * (BK * 128), &tmA, &full_bar[stage], m0 + 16 * j, k0);
           } else {
             tma_load_2d(sA, &tmA, &full_bar[stage], k0, m0);
           }
           if (B_MN) {
-#pragma unroll
+#pragma unroll 1
             for (int j = 0; j < BN / 16; j++)
               tma_load_2d(sB + j * (BK * 128), &tmB, &full_bar[stage], n0 + 16 * j, k0);
           } else {
@@ -220,7 +223,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
 
   // ===================== DMMA consumers =====================
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
   const int gid = lane >> 2, tig = lane & 3;
   const int wm = warp & 1, wn = warp >> 1;     // 2 x 4 warps -> 64 x 32 warp tiles
   const int kslot = (tig & 1) + 8 * (tig >> 1);  // + 2*step

@@ -37,16 +37,53 @@ static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, in
   Arena::Mark mk = ctx->arena.mark();
   const bool need_ab = !is_zero(alpha) && k > 0;
   DevMat<T> dA, dB;
-  if (need_ab) {
-    dA = dev_from_host<T>(*ctx, ar, ac, A, lda);
-    dB = dev_from_host<T>(*ctx, br, bc, B, ldb);
-  }
   DevMat<T> dC = dev_alloc<T>(*ctx, m, n);
-  if (!is_zero(beta)) upload<T>(*ctx, dC, C, ldc);
-  gemm<T>(*ctx, (Op)ta, (Op)tb, m, n, need_ab ? k : 0, alpha, dA.p, dA.ld, dB.p, dB.ld, beta, dC.p,
-          dC.ld);
-  download<T>(*ctx, dC, C, ldc);
-  sync(*ctx);
+  // Large products are pipelined over column blocks of C: while block j is being multiplied,
+  // block j+1 of B (and of C when beta != 0) travels host->device and block j-1 of C travels
+  // back, so that only the upload of A and of the first block is exposed.
+  const double work = (double)m * (double)n * (double)k;
+  const int64_t nchunks = (need_ab && work >= 8e9 && n >= 2048) ? 8 : 1;
+  if (nchunks == 1) {
+    if (need_ab) {
+      dA = dev_from_host<T>(*ctx, ar, ac, A, lda);
+      dB = dev_from_host<T>(*ctx, br, bc, B, ldb);
+    }
+    if (!is_zero(beta)) upload<T>(*ctx, dC, C, ldc);
+    gemm<T>(*ctx, (Op)ta, (Op)tb, m, n, need_ab ? k : 0, alpha, dA.p, dA.ld, dB.p, dB.ld, beta,
+            dC.p, dC.ld);
+    download<T>(*ctx, dC, C, ldc);
+    sync(*ctx);
+  } else {
+    dA = dev_alloc<T>(*ctx, ar, ac);
+    dB = dev_alloc<T>(*ctx, br, bc);
+    const int64_t nb = round_up(ceil_div(n, nchunks), 128);
+    cudaStream_t up = ctx->copy_stream, down = ctx->d2h_stream;
+    cudaEvent_t ev_up[16], ev_done[16];
+    upload<T>(*ctx, dA, A, lda, up);
+    int nc = 0;
+    for (int64_t c0 = 0; c0 < n; c0 += nb, nc++) {
+      const int64_t cn = nb < n - c0 ? nb : n - c0;
+      LA_CUDA_CHECK(cudaEventCreateWithFlags(&ev_up[nc], cudaEventDisableTiming));
+      LA_CUDA_CHECK(cudaEventCreateWithFlags(&ev_done[nc], cudaEventDisableTiming));
+      // columns [c0, c0+cn) of op(B): a column block of B (tb == N) or a row block (otherwise)
+      DevMat<T> vB = dB, vC = dC;
+      const T* hB;
+      if (tb == OpN) { vB.p = dB.p + c0 * dB.ld; vB.rows = k; vB.cols = cn; hB = B + c0 * (int64_t)ldb; }
+      else           { vB.p = dB.p + c0;         vB.rows = cn; vB.cols = k; hB = B + c0; }
+      upload<T>(*ctx, vB, hB, ldb, up);
+      vC.p = dC.p + c0 * dC.ld; vC.cols = cn;
+      if (!is_zero(beta)) upload<T>(*ctx, vC, C + c0 * (int64_t)ldc, ldc, up);
+      LA_CUDA_CHECK(cudaEventRecord(ev_up[nc], up));
+      LA_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ev_up[nc], 0));
+      gemm<T>(*ctx, (Op)ta, (Op)tb, m, cn, k, alpha, dA.p, dA.ld, vB.p, dB.ld, beta, vC.p, dC.ld);
+      LA_CUDA_CHECK(cudaEventRecord(ev_done[nc], ctx->stream));
+      LA_CUDA_CHECK(cudaStreamWaitEvent(down, ev_done[nc], 0));
+      download<T>(*ctx, vC, C + c0 * (int64_t)ldc, ldc, down);
+    }
+    LA_CUDA_CHECK(cudaStreamSynchronize(down));
+    sync(*ctx);
+    for (int i = 0; i < nc; i++) { cudaEventDestroy(ev_up[i]); cudaEventDestroy(ev_done[i]); }
+  }
   ctx->arena.release(mk);
 }
 

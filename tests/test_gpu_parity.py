@@ -111,6 +111,19 @@ def test_gemm_reference_call_pattern_and_edges(rng, dt, product_abi, oracle_abi)
     assert checks.rel(Cr - Ar @ Br, Ar @ Br) < 16 * _eps(dt)
 
 
+@pytest.mark.parametrize("tb", [ffi.NO_TRANS, ffi.TRANS])
+def test_large_gemm_takes_the_pipelined_host_path(rng, tb, product_abi, oracle_abi):
+    # >= 8e9 multiply-adds and n >= 2048: cblas_dgemm overlaps the column blocks' H2D / D2H
+    # copies with the products (shim_cblas.cu); ragged n so that the last block is partial
+    m, n, k = 2200, 2500, 1600
+    A = _rand(rng, (m, k), np.float64, -0.5)
+    B = _rand(rng, (k, n) if tb == ffi.NO_TRANS else (n, k), np.float64, -0.5)
+    C0 = _rand(rng, (m, n), np.float64, -0.5)
+    got = _gemm_call(product_abi, np.float64, ffi.NO_TRANS, tb, m, n, k, 1.0, A, B, 1.0, C0)
+    ref = _gemm_call(oracle_abi, np.float64, ffi.NO_TRANS, tb, m, n, k, 1.0, A, B, 1.0, C0)
+    assert checks.rel(got - ref, ref) < 8 * _eps(np.float64) * np.sqrt(k)
+
+
 def test_f32_gemm_keeps_fp32_accuracy_on_ill_scaled_input(rng, product_abi):
     # north_star: the Float32 path must hold FP32 accuracy (3xTF32 split), also when the
     # operands span many binades and cancel
