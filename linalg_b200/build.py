@@ -48,6 +48,7 @@ def _defines():
         have.append("-DLA_HAVE_DMMA_Z")
     if (CSRC / "gemm_tf32x3.cu").exists():
         have.append("-DLA_HAVE_TF32X3")
+    have += os.environ.get("LA_EXTRA_DEFINES", "").split()
     return have
 
 

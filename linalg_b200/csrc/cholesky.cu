@@ -80,9 +80,11 @@ potf2_kernel(int lower, int n, T* __restrict__ A, int64_t lda, int* info, int in
           if (!(d > 0.0)) {
             f = j0 + j + 1;  // also catches NaN; uniform over the warp
           } else {
+            // sqrt and reciprocal sqrt are independent, so neither waits for the other
             const double sq = sqrt(d);
-            const R rinv = (R)(1.0 / sq);
-            if (lane == j) { a[j] = from_real<T>(sq); rdiag[j] = from_real<T>(1.0 / sq); }
+            const double rs = rsqrt(d);
+            const R rinv = (R)rs;
+            if (lane == j) { a[j] = from_real<T>(sq); rdiag[j] = from_real<T>(rs); }
             if (lane > j) a[j] = scale_real(a[j], rinv);
             // a(i,k) -= a(i,j) * conj(a(k,j)) for j < k <= i; a(k,j) lives in lane k
 #pragma unroll

@@ -93,19 +93,88 @@ template <> __device__ __forceinline__ zcomplex ll_get<zcomplex>(const LLPacket*
   return v;
 }
 
-// candidates are valid iff their index is; NaNs never win a comparison but never dead-lock
-__device__ __forceinline__ void argmax_combine(double& v, int& i, double ov, int oi) {
+// Pivot candidates are compared through integer keys: for non-negative doubles the IEEE bit
+// pattern orders like the value, and integer compares are several times shorter than FP64 ones
+// on the serial path of every column.  NaN magnitudes get key 0 (they never win, as in i?amax,
+// where every comparison with a NaN is false).  A candidate is valid iff its index is.
+typedef unsigned long long ukey;
+__device__ __forceinline__ ukey key_of(double absval) {
+  const ukey k = (ukey)__double_as_longlong(absval);
+  return k > 0x7ff0000000000000ull ? 0ull : k;
+}
+__device__ __forceinline__ void argmax_combine(ukey& v, int& i, ukey ov, int oi) {
   if (oi != 0x7fffffff && (i == 0x7fffffff || ov > v || (ov == v && oi < i))) { v = ov; i = oi; }
 }
-__device__ __forceinline__ void warp_argmax(double& v, int& i) {
+__device__ __forceinline__ void warp_argmax(ukey& v, int& i) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    double ov = __shfl_xor_sync(0xffffffffu, v, o);
-    int oi = __shfl_xor_sync(0xffffffffu, i, o);
+    const ukey ov = __shfl_xor_sync(0xffffffffu, v, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, i, o);
     argmax_combine(v, i, ov, oi);
   }
 }
 
+#ifdef LA_PANEL_TRACE
+__device__ long long g_panel_trace[64 * 8];
+#define TRACE(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && j < 64) g_panel_trace[j * 8 + (slot)] = clock64(); } while (0)
+#else
+#define TRACE(slot) do { } while (0)
+#endif
+
+// 64-bit key arg-max over a warp with three REDUX steps (max of the high word, max of the low
+// word among the lanes that tie on it, smallest index among the lanes that tie on both).
+__device__ __forceinline__ void warp_argmax_redux(ukey& v, int& i) {
+  const unsigned hi = (unsigned)(v >> 32), lo = (unsigned)v;
+  const bool valid = i != 0x7fffffff;
+  const unsigned mh = __reduce_max_sync(0xffffffffu, valid ? hi : 0u);
+  const bool t1 = valid && hi == mh;
+  const unsigned ml = __reduce_max_sync(0xffffffffu, t1 ? lo : 0u);
+  const bool t2 = t1 && lo == ml;
+  const unsigned mi = __reduce_min_sync(0xffffffffu, t2 ? (unsigned)i : 0x7fffffffu);
+  v = ((ukey)mh << 32) | ml;
+  i = (int)mi;
+}
+
+// One elimination step on a row held in registers: l = a[J] / pivot, a[c] -= l * prow[c] for
+// c > J, and the key of the next column's entry.  J is a compile-time constant so that a[]
+// never leaves the register file.
+template <typename T, int JBM, int J>
+__device__ __forceinline__ void eliminate(T (&a)[JBM], const T* __restrict__ prow, T rinv, T pivot,
+                                          bool use_recip, ukey& next_key) {
+  const T l = use_recip ? mul(a[J], rinv) : div_(a[J], pivot);
+  a[J] = l;
+#pragma unroll
+  for (int c = J + 1; c < JBM; c++) a[c] = fnma_(l, prow[c], a[c]);
+  if (J + 1 < JBM) next_key = key_of((double)abs1(a[J + 1 < JBM ? J + 1 : J]));
+}
+
+template <typename T, int JBM, int J>
+struct Dispatch {
+  __device__ __forceinline__ static void run(int j, T (&a)[JBM], const T* prow, T rinv, T pivot,
+                                             bool use_recip, ukey& nk) {
+    if (j == J) eliminate<T, JBM, J>(a, prow, rinv, pivot, use_recip, nk);
+    else Dispatch<T, JBM, J + 1>::run(j, a, prow, rinv, pivot, use_recip, nk);
+  }
+};
+template <typename T, int JBM>
+struct Dispatch<T, JBM, JBM> {
+  __device__ __forceinline__ static void run(int, T (&)[JBM], const T*, T, T, bool, ukey&) {}
+};
+
+template <typename T, int JBM, int J>
+struct KeyAt {
+  __device__ __forceinline__ static ukey get(int j, const T (&a)[JBM]) {
+    return j == J ? key_of((double)abs1(a[J])) : KeyAt<T, JBM, J + 1>::get(j, a);
+  }
+};
+template <typename T, int JBM>
+struct KeyAt<T, JBM, JBM> {
+  __device__ __forceinline__ static ukey get(int, const T (&)[JBM]) { return 0; }
+};
+
+// LU with partial pivoting of an m x jb panel (m >= jb, jb <= MaxJb<T>), one row per thread,
+// rows in REGISTERS for the whole launch (the elimination would otherwise be bound by the
+// shared-memory bandwidth of the few SMs that hold the panel).
 template <typename T>
 __global__ void __launch_bounds__(LU_NT)
 lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__ ipiv, int row0,
@@ -113,157 +182,144 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   using R = typename Traits<T>::real;
   constexpr int W = Words<T>::N;
   constexpr int NW = LU_NT / 32;
+  constexpr int JBM = MaxJb<T>::N;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int G = gridDim.x;
-  T* S = reinterpret_cast<T*>(smem_raw);         // S[c * rpc + r]: this CTA's row slice
-  T* rows_all = S + (size_t)jb * rpc;            // rows_all[g * jb + c]: every CTA's candidate row
-  T* rj = rows_all + (size_t)G * jb;             // rj[c]: row j of the panel
-  double* hv = reinterpret_cast<double*>(((uintptr_t)(rj + LU_MAX_JB) + 7) & ~(uintptr_t)7);  // headers
+  T* cand = reinterpret_cast<T*>(smem_raw);      // cand[w * JBM + c]: each warp's best row
+  T* rows_all = cand + NW * JBM;                 // rows_all[g * JBM + c]: every CTA's candidate
+  T* rj = rows_all + (size_t)G * JBM;            // rj[c]: row j of the panel
+  ukey* hv = reinterpret_cast<ukey*>(((uintptr_t)(rj + JBM) + 7) & ~(uintptr_t)7);
   int* hi = reinterpret_cast<int*>(hv + G);
-  __shared__ double sval[NW];
+  __shared__ ukey sval[NW];
   __shared__ int sidx[NW];
-  __shared__ int s_pg;
+  __shared__ int s_pg, s_pi;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int rs = blockIdx.x * rpc;
-  const int nr = max(0, min(m - rs, rpc));
+  const int rs = blockIdx.x * rpc;                 // rpc == LU_NT: one row per thread
+  const int gr = rs + tid;                         // this thread's row
+  const bool have_row = gr < m;
 
-  // each thread stages its rows with several independent loads in flight (coalesced over r)
-  for (int r = tid; r < nr; r += LU_NT) {
-    const T* src = A + (int64_t)(rs + r);
-#pragma unroll 8
-    for (int c = 0; c < jb; c++) S[c * rpc + r] = src[(int64_t)c * lda];
-  }
-  // arg-max of column 0 over owned rows (each thread only ever touches its own rows of S)
-  double bv = -1.0;
-  int bi = 0x7fffffff;
-  for (int r = tid; r < nr; r += LU_NT) {
-    double v = (double)abs1(S[r]);
-    if (v > bv || bi == 0x7fffffff) { bv = v; bi = rs + r; }  // NaN-safe: first row always taken
-  }
+  T a[JBM];
+#pragma unroll
+  for (int c = 0; c < JBM; c++)
+    a[c] = (have_row && c < jb) ? A[(int64_t)gr + (int64_t)c * lda] : zero<T>();
+  ukey nk = have_row ? key_of((double)abs1(a[0])) : 0;
 
   for (int j = 0; j < jb; j++) {
     const int par = j & 1;
     const unsigned seq = seq_base + (unsigned)j + 1u;
-    // ---- CTA-level arg-max: warps reduce, warp 0 finishes and publishes
-    warp_argmax(bv, bi);
+    TRACE(0);
+    // ---- arg-max of column j over the rows gr >= j: per warp, then across warps
+    ukey bv = nk;
+    int bi = (have_row && gr >= j) ? gr : 0x7fffffff;
+    warp_argmax_redux(bv, bi);
+    if (bi == gr && have_row) {     // this lane owns the warp's best row: stage its contents
+#pragma unroll
+      for (int c = 0; c < JBM; c++) cand[warp * JBM + c] = a[c];
+    }
+    if (gr == j) {                  // this lane owns row j
+#pragma unroll
+      for (int c = 0; c < JBM; c++) rj[c] = a[c];
+    }
     if (lane == 0) { sval[warp] = bv; sidx[warp] = bi; }
     __syncthreads();
+    TRACE(1);
     if (warp == 0) {
-      double cv = lane < NW ? sval[lane] : -2.0;
+      ukey cv = lane < NW ? sval[lane] : 0;
       int ci = lane < NW ? sidx[lane] : 0x7fffffff;
-      warp_argmax(cv, ci);
+      const int myw = lane;
+      warp_argmax_redux(cv, ci);
+      // the warp whose entry won (smallest warp among equals holds the smallest row)
       const bool have = ci != 0x7fffffff;
-      const T crow = (have && lane < jb) ? S[lane * rpc + (ci - rs)] : zero<T>();
-      const bool own_j = j >= rs && j < rs + nr;
+      const unsigned wm = __ballot_sync(0xffffffffu, lane < NW && sidx[myw < NW ? myw : 0] == ci && have);
+      const int wwin = have ? __ffs(wm) - 1 : 0;
+      const T crow = (have && lane < JBM) ? cand[wwin * JBM + lane] : zero<T>();
+      const bool own_j = j >= rs && j < rs + LU_NT && j < m;
       if (G == 1) {  // single CTA: no global exchange
         if (lane == 0) { hv[0] = cv; hi[0] = ci; }
-        if (lane < jb) { rows_all[lane] = crow; rj[lane] = S[lane * rpc + (j - rs)]; }
+        if (lane < JBM) rows_all[lane] = crow;
       } else {
         if (lane == 0)
-          ll_store(&xch->hdr[par][blockIdx.x], (unsigned long long)__double_as_longlong(cv),
+          ll_store(&xch->hdr[par][blockIdx.x], cv,
                    ((unsigned long long)seq << 32) | (unsigned)(have ? ci : 0xffffffffu));
-        if (lane < jb) ll_put<T>(&xch->row[par][blockIdx.x][lane * W], crow, seq);
-        if (own_j && lane < jb) ll_put<T>(&xch->rowj[par][lane * W], S[lane * rpc + (j - rs)], seq);
+        if (lane < JBM) ll_put<T>(&xch->row[par][blockIdx.x][lane * W], crow, seq);
+        if (own_j && lane < JBM) ll_put<T>(&xch->rowj[par][lane * W], rj[lane], seq);
       }
     }
+    TRACE(2);
     // ---- all warps gather: warp w lands the packets of CTAs w, w+NW, ... in shared memory
     if (G > 1) {
       for (int g = warp; g < G; g += NW) {
-        if (lane < jb) rows_all[g * jb + lane] = ll_get<T>(&xch->row[par][g][lane * W], seq);
+        if (lane < JBM) rows_all[g * JBM + lane] = ll_get<T>(&xch->row[par][g][lane * W], seq);
         if (lane == 31) {
           unsigned long long d, t;
           ll_wait(&xch->hdr[par][g], seq, d, t);
-          hv[g] = __longlong_as_double((long long)d);
+          hv[g] = d;
           const unsigned uidx = (unsigned)(t & 0xffffffffull);
           hi[g] = uidx == 0xffffffffu ? 0x7fffffff : (int)uidx;
         }
       }
-      if (warp == NW - 1 && lane < jb) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
+      // row j comes from its owner CTA (which may be this one: then rj is already in place)
+      const bool own_j = j >= rs && j < rs + LU_NT;
+      if (!own_j && warp == NW - 1 && lane < JBM) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
     }
     __syncthreads();
-    // ---- warp 0 derives the winner from the landed headers, interchanges rows j <-> pi inside
-    //      the slices that own them (one lane per column) and posts (pi, pg) for the others
+    TRACE(3);
+    // ---- warp 0 derives the winner and posts (pi, pg)
     if (warp == 0) {
-      double pv = -1.0;
+      ukey pv = 0;
       int pi = 0x7fffffff, pg = 0;
       for (int g = lane; g < G; g += 32) {
-        const double v = hv[g];
+        const ukey v = hv[g];
         const int idx = hi[g];
         if (idx != 0x7fffffff && (pi == 0x7fffffff || v > pv || (v == pv && idx < pi))) {
           pv = v; pi = idx; pg = g;
         }
       }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const double ov = __shfl_xor_sync(0xffffffffu, pv, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, pi, o);
-        const int og = __shfl_xor_sync(0xffffffffu, pg, o);
-        if (oi != 0x7fffffff && (pi == 0x7fffffff || ov > pv || (ov == pv && oi < pi))) {
-          pv = ov; pi = oi; pg = og;
-        }
-      }
-      const T* pr = rows_all + pg * jb;
-      if (pi != j && lane < jb) {
-        if (pi >= rs && pi < rs + nr) S[lane * rpc + (pi - rs)] = rj[lane];
-        if (j >= rs && j < rs + nr) S[lane * rpc + (j - rs)] = pr[lane];
-      }
+      int pi_w = pi;
+      warp_argmax_redux(pv, pi_w);
+      const unsigned gm = __ballot_sync(0xffffffffu, pi == pi_w && pi_w != 0x7fffffff);
+      const int src = gm ? __ffs(gm) - 1 : 0;
+      pg = __shfl_sync(0xffffffffu, pg, src);
       if (lane == 0) {
         s_pg = pg;
-        if (blockIdx.x == 0) ipiv[j] = row0 + pi + 1;
+        s_pi = pi_w;
+        if (blockIdx.x == 0) ipiv[j] = row0 + pi_w + 1;
       }
     }
     __syncthreads();
-    const T* prow = rows_all + s_pg * jb;
-    // ---- scale column j, rank-1 update of the columns to its right, and the arg-max of
-    //      column j+1 in the same pass; each thread works on its own rows only
+    TRACE(4);
+    const T* prow = rows_all + s_pg * JBM;
+    const int pi = s_pi;
+    // ---- row interchange j <-> pi in the registers of the two owners
+    if (pi != j) {
+      if (gr == pi) {
+#pragma unroll
+        for (int c = 0; c < JBM; c++) a[c] = rj[c];
+      } else if (gr == j) {
+#pragma unroll
+        for (int c = 0; c < JBM; c++) a[c] = prow[c];
+      }
+    }
+    // ---- eliminate: scale column j, rank-1 update, key of the next column's entry
     const T pivot = prow[j];
     const bool zero_pivot = is_zero(pivot);
     if (zero_pivot && blockIdx.x == 0 && tid == 0) atomicCAS(info, 0, row0 + j + 1);
     const bool use_recip = (R)abs1(pivot) >= sfmin<R>();
     const T rinv = zero_pivot ? zero<T>() : recip(pivot);
-    bv = -1.0;
-    bi = 0x7fffffff;
-    for (int r = tid; r < nr; r += LU_NT) {
-      const int gr = rs + r;
-      if (gr <= j) continue;
-      T* row = S + r;
-      if (zero_pivot) {  // as ?getf2: nothing to scale, the update is a no-op
-        if (j + 1 < jb) {
-          const double av = (double)abs1(row[(j + 1) * rpc]);
-          if (av > bv || bi == 0x7fffffff) { bv = av; bi = gr; }
-        }
-        continue;
-      }
-      const T a = row[j * rpc];
-      const T l = use_recip ? mul(a, rinv) : div_(a, pivot);
-      row[j * rpc] = l;
-      int c = j + 1;
-      if (c < jb) {
-        const T x = fnma_(l, prow[c], row[c * rpc]);
-        row[c * rpc] = x;
-        const double av = (double)abs1(x);
-        if (av > bv || bi == 0x7fffffff) { bv = av; bi = gr; }
-        c++;
-      }
-      for (; c + 3 < jb; c += 4) {  // loads first, so that four updates are in flight
-        const T x0 = row[c * rpc], x1 = row[(c + 1) * rpc], x2 = row[(c + 2) * rpc],
-                x3 = row[(c + 3) * rpc];
-        const T p0 = prow[c], p1 = prow[c + 1], p2 = prow[c + 2], p3 = prow[c + 3];
-        row[c * rpc] = fnma_(l, p0, x0);
-        row[(c + 1) * rpc] = fnma_(l, p1, x1);
-        row[(c + 2) * rpc] = fnma_(l, p2, x2);
-        row[(c + 3) * rpc] = fnma_(l, p3, x3);
-      }
-      for (; c < jb; c++) row[c * rpc] = fnma_(l, prow[c], row[c * rpc]);
+    nk = 0;
+    if (have_row && gr > j) {
+      if (!zero_pivot) Dispatch<T, JBM, 0>::run(j, a, prow, rinv, pivot, use_recip, nk);
+      else nk = KeyAt<T, JBM, 0>::get(j + 1, a);   // as ?getf2: no scaling, update is a no-op
     }
-    // landing areas and sval are rewritten only after the next column's first __syncthreads
+    TRACE(5);
+    // cand / rj / landing areas are rewritten only after the next column's first __syncthreads
+    __syncthreads();
   }
-  __syncthreads();
-  for (int r = tid; r < nr; r += LU_NT) {
-    T* dst = A + (int64_t)(rs + r);
-#pragma unroll 8
-    for (int c = 0; c < jb; c++) dst[(int64_t)c * lda] = S[c * rpc + r];
+  if (have_row) {
+#pragma unroll
+    for (int c = 0; c < JBM; c++)
+      if (c < jb) A[(int64_t)gr + (int64_t)c * lda] = a[c];
   }
 }
 
@@ -297,12 +353,12 @@ void lu_panel_adopt_exchange(Context& ctx, void* device_mem, void* state_storage
   ctx.lu_state = st;
 }
 
+// Widest leaf the panel kernel takes for an m-row panel (0: the panel is too tall for one
+// cooperative launch with a row per thread).
 int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
-  int64_t rpc = round_up(ceil_div(m, ctx.sm_count), 2);
-  int64_t nb0 = (int64_t)(LU_SMEM_BUDGET / (rpc * elem_bytes));
-  const int64_t cap = elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
-  if (nb0 > cap) nb0 = cap;
-  return (int)nb0;
+  const int64_t G = ceil_div(m, LU_NT);
+  if (G > ctx.sm_count || G > LU_MAX_CTAS) return 0;
+  return elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
 }
 
 template <typename T>
@@ -316,24 +372,16 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
     attr = true;
   }
   LuPanelState* st = panel_state(ctx);
-  // as few CTAs as keep the slice resident and the per-column work short
-  int64_t G = ceil_div(m, 512);
-  if (G > ctx.sm_count) G = ctx.sm_count;
-  if (G < 1) G = 1;
-  int64_t rpc = ceil_div(m, G);
-  while ((size_t)rpc * jb * sizeof(T) > LU_SMEM_BUDGET && G < ctx.sm_count) {
-    G++;
-    rpc = ceil_div(m, G);
-  }
-  rpc = round_up(rpc, 2);
-  G = ceil_div(m, rpc);
-  size_t smem = (size_t)rpc * jb * sizeof(T);
-  if (smem > LU_SMEM_BUDGET || G > LU_MAX_CTAS) {
+  // one row per thread
+  const int64_t rpc = LU_NT;
+  const int64_t G = ceil_div(m, rpc);
+  if (G > LU_MAX_CTAS || G > ctx.sm_count || jb > MaxJb<T>::N) {
     fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
     abort();
   }
-  // landing areas: every CTA's candidate row, row j, headers
-  smem += ((size_t)G * jb + LU_MAX_JB) * sizeof(T) + (size_t)G * (sizeof(double) + sizeof(int)) + 16;
+  constexpr int JBM = MaxJb<T>::N;
+  size_t smem = ((size_t)(LU_NT / 32) * JBM + (size_t)G * JBM + JBM) * sizeof(T) +
+                (size_t)G * (sizeof(unsigned long long) + sizeof(int)) + 16;
   int mi = (int)m, row0i = (int)row0, rpci = (int)rpc;
   unsigned seq_base = st->seq;
   st->seq += 64;
@@ -342,6 +390,13 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
   LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lu_panel_kernel<T>, dim3((unsigned)G),
                                             dim3(LU_NT), args, smem, ctx.stream));
 }
+
+#ifdef LA_PANEL_TRACE
+extern "C" void la_b200_debug_panel_trace(long long* out) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, g_panel_trace, sizeof(long long) * 64 * 8);
+}
+#endif
 
 template void lu_panel<float>(Context&, int64_t, int, float*, int64_t, int*, int64_t, int*);
 template void lu_panel<double>(Context&, int64_t, int, double*, int64_t, int*, int64_t, int*);
