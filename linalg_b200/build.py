@@ -44,7 +44,7 @@ def _defines():
     have = []
     if (CSRC / "gemm_dmma.cu").exists():
         have.append("-DLA_HAVE_DMMA_F64")
-    if (CSRC / "gemm_dmma_z.cu").exists():
+    if (CSRC / "gemm_z.cu").exists():
         have.append("-DLA_HAVE_DMMA_Z")
     if (CSRC / "gemm_tf32x3.cu").exists():
         have.append("-DLA_HAVE_TF32X3")

@@ -85,6 +85,8 @@ struct GemmParams {
   int64_t ldc;
   int tri;
   int tiles_m, tiles_n, num_tiles;
+  int zmode;      // 1: rows are interleaved (re, im) parts of a complex matrix (gemm_z.cu)
+  int herm_diag;  // zmode only: store 0 in the imaginary part of the diagonal
 };
 
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
@@ -158,6 +160,14 @@ __device__ __forceinline__ void tile_coords(int tri, int t, int tiles_m, int til
   tn = r / gsz;
 }
 
+// zmode products enumerate all tiles and skip those entirely outside the stored triangle of the
+// COMPLEX matrix (complex row = real row >> 1).
+__device__ __forceinline__ bool tile_active(const GemmParams& p, int tm, int tn) {
+  if (!p.zmode || p.tri == TriFull) return true;
+  if (p.tri == TriLower) return ((tm * BM + BM - 1) >> 1) >= tn * BN;
+  return ((tm * BM) >> 1) <= tn * BN + BN - 1;
+}
+
 template <bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NTHREADS, 1)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -193,7 +203,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         int tm, tn;
-        tile_coords(p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+        tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+        if (!tile_active(p, tm, tn)) continue;
         const int m0 = tm * BM, n0 = tn * BN;
         for (int kb = 0; kb < kblocks; kb++) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -233,7 +244,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
     int tm, tn;
-    tile_coords(p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+    tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+    if (!tile_active(p, tm, tn)) continue;
 
     double acc[8][4][2];
 #pragma unroll
@@ -279,10 +291,12 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int i = 0; i < 8; i++) {
           const int64_t row = row_base + i * 8;
           if (row >= p.m) continue;
-          if (p.tri == TriLower && row < col) continue;
-          if (p.tri == TriUpper && row > col) continue;
+          const int64_t mrow = p.zmode ? (row >> 1) : row;
+          if (p.tri == TriLower && mrow < col) continue;
+          if (p.tri == TriUpper && mrow > col) continue;
           double v = p.alpha * acc[i][j][c];
           if (!beta_zero) v = fma(p.beta, Ccol[row], v);
+          if (p.herm_diag && mrow == col && (row & 1)) v = 0.0;
           Ccol[row] = v;
         }
       }
@@ -310,6 +324,12 @@ void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const 
 bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
                    const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                    double* C, int64_t ldc, int tri) {
+  return gemm_dmma_f64_ex(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri, 0, false);
+}
+
+bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
+                      const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
+                      double* C, int64_t ldc, int tri, int zmode, bool herm_diag) {
   if (ta == OpC) ta = OpT;
   if (tb == OpC) tb = OpT;
   if (m <= 0 || n <= 0) return true;
@@ -342,7 +362,10 @@ bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, 
   p.tiles_m = (int)ceil_div(m, BM);
   p.tiles_n = (int)ceil_div(n, BN);
   if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
-  if (tri == TriLower) p.num_tiles = tri_tile_count(p.tiles_m, p.tiles_n);
+  p.zmode = zmode;
+  p.herm_diag = herm_diag ? 1 : 0;
+  if (zmode) p.num_tiles = p.tiles_m * p.tiles_n;
+  else if (tri == TriLower) p.num_tiles = tri_tile_count(p.tiles_m, p.tiles_n);
   else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
   else p.num_tiles = p.tiles_m * p.tiles_n;
   if (p.num_tiles <= 0) return true;

@@ -1,0 +1,151 @@
+// la_b200 — complex128 GEMM on the FP64 tensor cores.
+//
+// cblas_zgemm / zhemm / zherk and every complex trailing update (zgetrf, zpotrf, zgeqrf) end
+// here (src/linalg/mult.cr:35-69 -> libCBLAS.cr:178,201).  A complex product is four real ones;
+// they are folded into ONE real DMMA GEMM by a change of layout that costs two O(n^2) passes:
+//
+//   C~ (2m x n, the interleaved re/im rows of C, i.e. C's own storage read as real)
+//      = [ A~ | J A~ ] (2m x 2k)  *  [ Re(alpha op(B)) ; Im(alpha op(B)) ] (2k x n)
+//
+// where A~ is op(A) with interleaved (re, im) rows and J A~ has rows (-im, re).  The real GEMM
+// performs 2*(2m)*n*(2k) = 8mnk flops — exactly the complex flop count — and writes C in place
+// in its native complex layout.  op(A)/op(B) (N, T, C) are absorbed by the two packing kernels,
+// so the DMMA kernel always runs NN.  beta is applied by a complex scaling pass when it is not
+// 0 or 1.  Workspace: 2x the bytes of A plus 1x the bytes of B.
+#include "la_internal.h"
+
+namespace la {
+
+namespace {
+
+// A2 (2m x 2k real, ld2) from op(A) (m x k complex)
+__global__ void pack_a_kernel(int op, int64_t m, int64_t k, const zcomplex* __restrict__ A,
+                              int64_t lda, double* __restrict__ A2, int64_t ld2) {
+  __shared__ zcomplex tile[32][33];
+  const int64_t nbx = ceil_div(m, 32), nby = ceil_div(k, 32);
+  for (int64_t blk = blockIdx.x; blk < nbx * nby; blk += gridDim.x) {
+    const int64_t i0 = (blk % nbx) * 32, l0 = (blk / nbx) * 32;
+    // load a 32x32 block of op(A) into tile[l][i] with coalesced reads of the stored matrix
+    if (op == OpN) {
+      for (int ll = threadIdx.y; ll < 32; ll += blockDim.y) {
+        const int64_t i = i0 + threadIdx.x, l = l0 + ll;
+        if (i < m && l < k) tile[ll][threadIdx.x] = A[i + l * lda];
+      }
+    } else {
+      for (int ii = threadIdx.y; ii < 32; ii += blockDim.y) {
+        const int64_t l = l0 + threadIdx.x, i = i0 + ii;  // stored element (l, i)
+        if (i < m && l < k) {
+          zcomplex v = A[l + i * lda];
+          if (op == OpC) v.y = -v.y;
+          tile[threadIdx.x][ii] = v;
+        }
+      }
+    }
+    __syncthreads();
+    for (int ll = threadIdx.y; ll < 32; ll += blockDim.y) {
+      const int64_t i = i0 + threadIdx.x, l = l0 + ll;
+      if (i < m && l < k) {
+        const zcomplex v = tile[ll][threadIdx.x];
+        double2* d0 = reinterpret_cast<double2*>(A2 + 2 * i + l * ld2);
+        double2* d1 = reinterpret_cast<double2*>(A2 + 2 * i + (k + l) * ld2);
+        *d0 = make_double2(v.x, v.y);
+        *d1 = make_double2(-v.y, v.x);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// B2 (2k x n real, ld2) from alpha * op(B) (k x n complex)
+__global__ void pack_b_kernel(int op, int64_t k, int64_t n, zcomplex alpha,
+                              const zcomplex* __restrict__ B, int64_t ldb,
+                              double* __restrict__ B2, int64_t ld2) {
+  __shared__ zcomplex tile[32][33];
+  const int64_t nbx = ceil_div(k, 32), nby = ceil_div(n, 32);
+  for (int64_t blk = blockIdx.x; blk < nbx * nby; blk += gridDim.x) {
+    const int64_t l0 = (blk % nbx) * 32, j0 = (blk / nbx) * 32;
+    if (op == OpN) {
+      for (int jj = threadIdx.y; jj < 32; jj += blockDim.y) {
+        const int64_t l = l0 + threadIdx.x, j = j0 + jj;
+        if (l < k && j < n) tile[jj][threadIdx.x] = B[l + j * ldb];
+      }
+    } else {
+      for (int ll = threadIdx.y; ll < 32; ll += blockDim.y) {
+        const int64_t j = j0 + threadIdx.x, l = l0 + ll;  // stored element (j, l)
+        if (l < k && j < n) {
+          zcomplex v = B[j + l * ldb];
+          if (op == OpC) v.y = -v.y;
+          tile[threadIdx.x][ll] = v;
+        }
+      }
+    }
+    __syncthreads();
+    for (int jj = threadIdx.y; jj < 32; jj += blockDim.y) {
+      const int64_t l = l0 + threadIdx.x, j = j0 + jj;
+      if (l < k && j < n) {
+        const zcomplex v = mul(alpha, tile[jj][threadIdx.x]);
+        B2[l + j * ld2] = v.x;
+        B2[k + l + j * ld2] = v.y;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void zscale_kernel(int tri, int64_t m, int64_t n, zcomplex beta, zcomplex* C,
+                              int64_t ldc) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  for (int64_t j = blockIdx.y; j < n; j += gridDim.y) {
+    if (tri == TriLower && i < j) continue;
+    if (tri == TriUpper && i > j) continue;
+    C[i + j * ldc] = mul(beta, C[i + j * ldc]);
+  }
+}
+
+}  // namespace
+
+bool gemm_dmma_z(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, zcomplex alpha,
+                 const zcomplex* A, int64_t lda, const zcomplex* B, int64_t ldb, zcomplex beta,
+                 zcomplex* C, int64_t ldc, int tri, bool herm_diag) {
+  if (m <= 0 || n <= 0) return true;
+  if (k <= 0 || is_zero(alpha)) return false;
+  if ((double)m * (double)n * (double)k < 48.0 * 48.0 * 48.0) return false;
+  if (m > (int64_t)1 << 29 || n > (int64_t)1 << 29 || k > (int64_t)1 << 29) return false;
+  Arena::Mark mk = ctx.arena.mark();
+  const int64_t lda2 = round_up(2 * m, 16), ldb2 = round_up(2 * k, 16);
+  double* A2 = ctx.alloc<double>((size_t)lda2 * (size_t)(2 * k));
+  double* B2 = ctx.alloc<double>((size_t)ldb2 * (size_t)n);
+  {
+    int64_t nblk = ceil_div(m, 32) * ceil_div(k, 32);
+    unsigned g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
+    pack_a_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>((int)ta, m, k, A, lda, A2, lda2);
+    nblk = ceil_div(k, 32) * ceil_div(n, 32);
+    g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
+    pack_b_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>((int)tb, k, n, alpha, B, ldb, B2, ldb2);
+    LA_CUDA_CHECK(cudaGetLastError());
+  }
+  double beta_r = 1.0;
+  if (is_zero(beta)) {
+    beta_r = 0.0;
+  } else if (!is_one(beta)) {
+    dim3 g((unsigned)ceil_div(m, 256), (unsigned)(n < 1024 ? n : 1024));
+    zscale_kernel<<<g, 256, 0, ctx.stream>>>(tri, m, n, beta, C, ldc);
+    LA_CUDA_CHECK(cudaGetLastError());
+  }
+  const bool ok = gemm_dmma_f64_ex(ctx, OpN, OpN, 2 * m, n, 2 * k, 1.0, A2, lda2, B2, ldb2, beta_r,
+                                   reinterpret_cast<double*>(C), 2 * ldc, tri, 1, herm_diag);
+  ctx.arena.release(mk);
+  if (!ok) {
+    // nothing was enqueued by the real GEMM; undo the beta scaling semantics by reporting
+    // failure only when C has not been touched
+    if (!is_zero(beta) && !is_one(beta)) {
+      fprintf(stderr, "la_b200: internal error: complex GEMM fallback after scaling\n");
+      abort();
+    }
+    return false;
+  }
+  return true;
+}
+
+}  // namespace la

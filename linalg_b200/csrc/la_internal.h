@@ -32,6 +32,10 @@ void gemm_simt(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T al
 bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
                    const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                    double* C, int64_t ldc, int tri);
+// same kernel with the complex-interleaved row mask / diagonal rule used by gemm_z.cu
+bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
+                      const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
+                      double* C, int64_t ldc, int tri, int zmode, bool herm_diag);
 bool gemm_dmma_z(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, zcomplex alpha,
                  const zcomplex* A, int64_t lda, const zcomplex* B, int64_t ldb, zcomplex beta,
                  zcomplex* C, int64_t ldc, int tri, bool herm_diag);

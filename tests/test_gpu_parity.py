@@ -121,6 +121,8 @@ def test_large_gemm_takes_the_pipelined_host_path(rng, tb, product_abi, oracle_a
     C0 = _rand(rng, (m, n), np.float64, -0.5)
     got = _gemm_call(product_abi, np.float64, ffi.NO_TRANS, tb, m, n, k, 1.0, A, B, 1.0, C0)
     ref = _gemm_call(oracle_abi, np.float64, ffi.NO_TRANS, tb, m, n, k, 1.0, A, B, 1.0, C0)
+    bad = np.argwhere(np.abs(got - ref) > 1e-9)
+    assert len(bad) == 0, (len(bad), bad[:8].tolist(), bad[-4:].tolist())
     assert checks.rel(got - ref, ref) < 8 * _eps(np.float64) * np.sqrt(k)
 
 

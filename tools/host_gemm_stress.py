@@ -1,0 +1,23 @@
+import sys
+import numpy as np
+sys.path.insert(0, ".")
+import linalg_b200
+from linalg_b200 import ffi
+abi = linalg_b200.abi()
+m, n, k = 2200, 2500, 1600
+nbad = 0
+for it in range(25):
+    rng = np.random.default_rng(20261106)
+    for tb in (ffi.NO_TRANS, ffi.TRANS):
+        A = np.asfortranarray(rng.random((m, k)) - 0.5)
+        B = np.asfortranarray(rng.random((k, n) if tb == ffi.NO_TRANS else (n, k)) - 0.5)
+        C0 = np.asfortranarray(rng.random((m, n)) - 0.5)
+        ref = A @ (B if tb == ffi.NO_TRANS else B.T) + C0
+        C = C0.copy(order="F")
+        abi.gemm("d")(ffi.COL_MAJOR, ffi.NO_TRANS, tb, m, n, k, 1.0, ffi.ptr(A), m, ffi.ptr(B), B.shape[0], 1.0, ffi.ptr(C), m)
+        bad = np.argwhere(np.abs(C - ref) > 1e-9)
+        if len(bad):
+            nbad += 1
+            i, j = bad[0]
+            print("iter", it, "tb", tb, "nbad", len(bad), bad[:6].tolist(), "got", C[i, j], "ref", ref[i, j], "C0", C0[i, j], flush=True)
+print("failures:", nbad)
