@@ -6,6 +6,7 @@
 // Blocked right-looking driver around a recursive panel factorisation; the leaf panel kernel
 // is in lu_panel.cu, the row interchanges (net-permutation laswp) are here.
 #include "la_internal.h"
+#include <type_traits>
 #include <cooperative_groups.h>
 
 namespace la {
@@ -191,7 +192,14 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   // factored on a side stream (a chain of latency-bound leaf launches that needs only a few
   // SMs) while the main stream finishes the trailing update on the remaining SMs.
   const int64_t leaf_ctas = ceil_div(m, 512);
-  const bool lookahead = ctx.allow_side_stream && k >= 4096 && leaf_ctas <= 40 && k > NB;
+  // Only when the overlapped trailing update is exactly ONE persistent kernel with a capped
+  // grid (the FP64 DMMA GEMM on TMA-legal operands): a trailing update made of many ordinary
+  // launches (SIMT GEMM, complex packing passes) gives the side stream's cooperative leaf no
+  // stable set of free SMs, and the leaf's CTAs then wait for one another forever.
+  const bool dmma_ok = std::is_same<T, double>::value && (lda % 2 == 0) &&
+                       (((uintptr_t)A & 15) == 0);
+  const bool lookahead = ctx.allow_side_stream && dmma_ok && k >= 4096 && leaf_ctas <= 40 &&
+                         k > NB;
   Context* side = lookahead ? side_context(ctx) : nullptr;
   const int side_sms = (int)(leaf_ctas < 16 ? 16 : leaf_ctas);
   bool panel_done = false;  // panel of the current j0 already factored (on the side stream)?
