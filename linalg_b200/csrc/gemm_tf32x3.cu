@@ -1,0 +1,354 @@
+// la_b200 — FP32 GEMM on the 5th-generation tensor cores with FP32-level accuracy (3xTF32).
+//
+// cblas_sgemm (src/linalg/mult.cr:64-69 -> libCBLAS.cr:174) and every FP32 trailing update.
+// tcgen05.mma.kind::tf32 keeps 10 mantissa bits of its inputs; each operand is therefore split
+// once into hi = tf32(x) and lo = tf32(x - hi) and the product is accumulated in FP32 (TMEM) as
+//        A*B ~= Ahi*Bhi + Ahi*Blo + Alo*Bhi            (the lo*lo term is below FP32 rounding).
+// Design:
+//   * a packing pass writes the four K-major ("k contiguous") operands Ahi, Alo (m x k) and
+//     Bhi, Blo (n x k) into workspace, absorbing op(A)/op(B); the main kernel is a pure
+//     K-major x K-major product;
+//   * persistent kernel, one CTA per SM, tile 128 x 256 x 32, 2-stage ring of TMA loads
+//     (128-byte swizzle) -> 12 tcgen05.mma (M=128, N=256, K=8) per stage issued by one thread
+//     -> accumulator in TMEM, double buffered (2 x 256 columns) so that the epilogue of tile t
+//     overlaps the MMAs of tile t+1;
+//   * warp roles: 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue
+//     (tcgen05.ld 32 lanes x 32 columns per warp, alpha/beta, coalesced column-major stores).
+// Algorithmic work 2*m*n*k flops; the tensor pipe executes 3x that in TF32.
+#include "la_internal.h"
+#include "tma_utils.cuh"
+
+namespace la {
+
+namespace {
+
+constexpr int SM_ = 128, SN_ = 256, SK_ = 32;         // CTA tile (K in floats = 128 bytes)
+constexpr int S_STAGES = 2;
+constexpr int S_A_BYTES = SM_ * SK_ * 4;               // 16 KB per (hi or lo)
+constexpr int S_B_BYTES = SN_ * SK_ * 4;               // 32 KB per (hi or lo)
+constexpr int S_STAGE_BYTES = 2 * S_A_BYTES + 2 * S_B_BYTES;  // 96 KB
+constexpr int S_SMEM_BYTES = S_STAGES * S_STAGE_BYTES + 1024 + 256;
+constexpr int S_THREADS = 256;
+constexpr int S_TMEM_COLS = 512;                       // two 256-column accumulators
+
+struct SParams {
+  int64_t m, n, k;
+  float alpha, beta;
+  float* C;
+  int64_t ldc;
+  int tri;
+  int tiles_m, tiles_n;
+};
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+
+// hi/lo split of op(X) into K-major storage: out(r, c) at out[r * ldo + c], r = row of op(X)
+// for A (m rows) or column of op(B) for B (n rows), c = k index.  `kcontig` says whether the
+// stored matrix already has k contiguous for a fixed r (no transposition needed).
+__global__ void split_kernel(int kcontig, int64_t rows, int64_t k, float scale,
+                             const float* __restrict__ X, int64_t ldx, float* __restrict__ hi,
+                             float* __restrict__ lo, int64_t ldo) {
+  __shared__ float tile[32][33];
+  const int64_t nbr = ceil_div(rows, 32), nbk = ceil_div(k, 32);
+  for (int64_t blk = blockIdx.x; blk < nbr * nbk; blk += gridDim.x) {
+    const int64_t r0 = (blk % nbr) * 32, c0 = (blk / nbr) * 32;
+    if (kcontig) {  // element (r, c) stored at X[c + r * ldx]
+      for (int rr = threadIdx.y; rr < 32; rr += blockDim.y) {
+        const int64_t r = r0 + rr, c = c0 + threadIdx.x;
+        if (r < rows && c < k) tile[rr][threadIdx.x] = X[c + r * ldx];
+      }
+    } else {        // element (r, c) stored at X[r + c * ldx]
+      for (int cc = threadIdx.y; cc < 32; cc += blockDim.y) {
+        const int64_t r = r0 + threadIdx.x, c = c0 + cc;
+        if (r < rows && c < k) tile[threadIdx.x][cc] = X[r + c * ldx];
+      }
+    }
+    __syncthreads();
+    for (int rr = threadIdx.y; rr < 32; rr += blockDim.y) {
+      const int64_t r = r0 + rr, c = c0 + threadIdx.x;
+      if (r < rows && c < k) {
+        const float x = tile[rr][threadIdx.x] * scale;
+        const float h = __uint_as_float(to_tf32(x));
+        const float l = __uint_as_float(to_tf32(x - h));
+        hi[r * ldo + c] = h;
+        lo[r * ldo + c] = l;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- tcgen05 helpers -------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+  // start address (>>4), LBO = 1 (unused for swizzled K-major), SBO = 1024 B between 8-row
+  // groups, version = 1 (sm_100), layout = SWIZZLE_128B (2)
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+constexpr uint32_t make_idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_c, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_c),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ bool s_tile_skipped(int tri, int tm, int tn) {
+  if (tri == TriLower) return tm * SM_ + SM_ - 1 < tn * SN_;
+  if (tri == TriUpper) return tm * SM_ > tn * SN_ + SN_ - 1;
+  return false;
+}
+
+__device__ __forceinline__ void s_tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
+  constexpr int GROUP = 8;
+  const int per_group = GROUP * tiles_n;
+  const int g = t / per_group;
+  const int first_m = g * GROUP;
+  const int gsz = min(tiles_m - first_m, GROUP);
+  const int r = t - g * per_group;
+  tm = first_m + r % gsz;
+  tn = r / gsz;
+}
+
+__global__ void __launch_bounds__(S_THREADS, 1)
+sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
+                    const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo,
+                    const SParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = (uint64_t*)(smem + S_STAGES * S_STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + S_STAGES;
+  uint64_t* tfull_bar = empty_bar + S_STAGES;   // accumulator ready for the epilogue
+  uint64_t* tempty_bar = tfull_bar + 2;         // accumulator drained by the epilogue
+  uint32_t* tmem_ptr = (uint32_t*)(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S_STAGES; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; a++) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_ptr)),
+                 "n"(S_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int kblocks = (int)((p.k + SK_ - 1) / SK_);
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      tma_prefetch_desc(&tmAhi); tma_prefetch_desc(&tmAlo);
+      tma_prefetch_desc(&tmBhi); tma_prefetch_desc(&tmBlo);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int tm, tn;
+        s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+        if (s_tile_skipped(p.tri, tm, tn)) continue;
+        const int m0 = tm * SM_, n0 = tn * SN_;
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], S_STAGE_BYTES);
+          unsigned char* s = smem + stage * S_STAGE_BYTES;
+          const int k0 = kb * SK_;
+          tma_load_2d(s, &tmAhi, &full_bar[stage], k0, m0);
+          tma_load_2d(s + S_A_BYTES, &tmAlo, &full_bar[stage], k0, m0);
+          tma_load_2d(s + 2 * S_A_BYTES, &tmBhi, &full_bar[stage], k0, n0);
+          tma_load_2d(s + 2 * S_A_BYTES + S_B_BYTES, &tmBlo, &full_bar[stage], k0, n0);
+          if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_tf32(SM_, SN_);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int tm, tn;
+        s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+        if (s_tile_skipped(p.tri, tm, tn)) continue;
+        mbar_wait(&tempty_bar[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + (uint32_t)(as * SN_);
+        for (int kb = 0; kb < kblocks; kb++) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t s = smem_u32(smem + stage * S_STAGE_BYTES);
+#pragma unroll
+          for (int ks = 0; ks < SK_ / 8; ks++) {
+            const uint32_t ko = ks * 32;  // 8 floats
+            const uint64_t ahi = make_kmajor_sw128_desc(s + ko);
+            const uint64_t alo = make_kmajor_sw128_desc(s + S_A_BYTES + ko);
+            const uint64_t bhi = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + ko);
+            const uint64_t blo = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + S_B_BYTES + ko);
+            umma_tf32(tacc, ahi, blo, idesc, (kb | ks) ? 1u : 0u);
+            umma_tf32(tacc, alo, bhi, idesc, 1u);
+            umma_tf32(tacc, ahi, bhi, idesc, 1u);
+          }
+          umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
+          if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[as]);        // accumulator complete
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> C =====================
+    const int q = warp & 3;                 // TMEM lane quarter of this warp
+    int as = 0;
+    uint32_t aphase = 0;
+    const bool beta_zero = p.beta == 0.f;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      int tm, tn;
+      s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
+      if (s_tile_skipped(p.tri, tm, tn)) continue;
+      mbar_wait(&tfull_bar[as], aphase);
+      tc_fence_after();
+      const int64_t row = (int64_t)tm * SM_ + q * 32 + lane;
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * SN_);
+#pragma unroll 1
+      for (int cc = 0; cc < SN_ / 32; cc++) {
+        uint32_t v[32];
+        tmem_ld32(tbase + cc * 32, v);
+        const int64_t col0 = (int64_t)tn * SN_ + cc * 32;
+        if (row < p.m) {
+#pragma unroll
+          for (int j = 0; j < 32; j++) {
+            const int64_t col = col0 + j;
+            if (col >= p.n) break;
+            if (p.tri == TriLower && row < col) continue;
+            if (p.tri == TriUpper && row > col) continue;
+            float* dst = p.C + row + col * p.ldc;
+            float r = p.alpha * __uint_as_float(v[j]);
+            if (!beta_zero) r = fmaf(p.beta, *dst, r);
+            *dst = r;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "n"(S_TMEM_COLS)
+                 : "memory");
+  }
+}
+
+}  // namespace
+
+bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, float alpha,
+                 const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
+                 int64_t ldc, int tri) {
+  if (ta == OpC) ta = OpT;
+  if (tb == OpC) tb = OpT;
+  if (m <= 0 || n <= 0) return true;
+  if (k <= 0 || alpha == 0.f) return false;
+  // below this the packing passes and the 128x256 tiles do not pay off
+  if ((double)m * (double)n * (double)k < 256.0 * 256.0 * 256.0) return false;
+  if (m > (int64_t)1 << 30 || n > (int64_t)1 << 30 || k > (int64_t)1 << 30) return false;
+  static bool attr = false;
+  if (!attr) {
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, S_SMEM_BYTES));
+    attr = true;
+  }
+  Arena::Mark mk = ctx.arena.mark();
+  const int64_t ldk = round_up(k, 32);
+  float* Ahi = ctx.alloc<float>((size_t)ldk * (size_t)m);
+  float* Alo = ctx.alloc<float>((size_t)ldk * (size_t)m);
+  float* Bhi = ctx.alloc<float>((size_t)ldk * (size_t)n);
+  float* Blo = ctx.alloc<float>((size_t)ldk * (size_t)n);
+  {
+    // op(A)(r, c): ta == N -> A[r + c*lda] (r contiguous); else A[c + r*lda] (k contiguous)
+    int64_t nblk = ceil_div(m, 32) * ceil_div(k, 32);
+    unsigned g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
+    split_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>(ta != OpN, m, k, 1.0f, A, lda, Ahi, Alo, ldk);
+    // op(B)(c, r) with r the column: tb == N -> B[c + r*ldb] (k contiguous); else B[r + c*ldb]
+    nblk = ceil_div(n, 32) * ceil_div(k, 32);
+    g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
+    split_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>(tb == OpN, n, k, 1.0f, B, ldb, Bhi, Blo, ldk);
+    LA_CUDA_CHECK(cudaGetLastError());
+  }
+  CUtensorMap tAh, tAl, tBh, tBl;
+  bool ok = make_tensor_map_2d(&tAh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Ahi, k, m, ldk * 4, SK_, SM_, CU_TENSOR_MAP_SWIZZLE_128B) &&
+            make_tensor_map_2d(&tAl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Alo, k, m, ldk * 4, SK_, SM_, CU_TENSOR_MAP_SWIZZLE_128B) &&
+            make_tensor_map_2d(&tBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Bhi, k, n, ldk * 4, SK_, SN_, CU_TENSOR_MAP_SWIZZLE_128B) &&
+            make_tensor_map_2d(&tBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Blo, k, n, ldk * 4, SK_, SN_, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (!ok) {
+    ctx.arena.release(mk);
+    return false;
+  }
+  SParams p;
+  p.m = m; p.n = n; p.k = k;
+  p.alpha = alpha; p.beta = beta;
+  p.C = C; p.ldc = ldc; p.tri = tri;
+  p.tiles_m = (int)ceil_div(m, SM_);
+  p.tiles_n = (int)ceil_div(n, SN_);
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+  const int grid = tiles < sms ? tiles : sms;
+  sgemm_tf32x3_kernel<<<grid, S_THREADS, S_SMEM_BYTES, ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+  LA_CUDA_CHECK(cudaGetLastError());
+  ctx.arena.release(mk);
+  return true;
+}
+
+}  // namespace la
