@@ -85,6 +85,10 @@ struct GemmParams {
   int64_t ldc;
   int tri;
   int tiles_m, tiles_n, num_tiles;
+  int ksplit;     // > 1: split-K, raw partial sums go to `partial` (one m x n slab per split)
+  int kchunk;     // k-blocks per split
+  double* partial;
+  int64_t ld_part;
   int zmode;      // 1: rows are interleaved (re, im) parts of a complex matrix (gemm_z.cu)
   int herm_diag;  // zmode only: store 0 in the imaginary part of the diagonal
 };
@@ -201,12 +205,14 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tma_prefetch_desc(&tmB);
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
+        const int t = w % num_tiles, split = w / num_tiles;
         int tm, tn;
         tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
         if (!tile_active(p, tm, tn)) continue;
         const int m0 = tm * BM, n0 = tn * BN;
-        for (int kb = 0; kb < kblocks; kb++) {
+        const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
+        for (int kb = kb0; kb < kb1; kb++) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           unsigned char* sA = smem + stage * STAGE_BYTES;
@@ -242,10 +248,12 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint32_t phase = 0;
   const bool beta_zero = p.beta == 0.0;
 
-  for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+  for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
+    const int t = w % num_tiles, split = w / num_tiles;
     int tm, tn;
     tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
     if (!tile_active(p, tm, tn)) continue;
+    const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
 
     double acc[8][4][2];
 #pragma unroll
@@ -253,7 +261,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
       for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    for (int kb = 0; kb < kblocks; kb++) {
+    for (int kb = kb0; kb < kb1; kb++) {
       mbar_wait(&full_bar[stage], phase);
       const unsigned char* sA = smem + stage * STAGE_BYTES;
       const unsigned char* sB = sA + A_STAGE_BYTES;
@@ -286,6 +294,15 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int c = 0; c < 2; c++) {
         const int64_t col = col_base + j * 8 + c;
         if (col >= p.n) continue;
+        if (p.ksplit > 1) {  // raw partial sums; alpha/beta are applied by the reduction pass
+          double* Pcol = p.partial + ((int64_t)split * p.n + col) * p.ld_part;
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int64_t row = row_base + i * 8;
+            if (row < p.m) Pcol[row] = acc[i][j][c];
+          }
+          continue;
+        }
         double* Ccol = p.C + col * p.ldc;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
@@ -304,6 +321,21 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
 }
 
+// C = alpha * sum_s partial_s + beta * C   (split-K reduction)
+__global__ void splitk_reduce_kernel(int64_t m, int64_t n, int ksplit, const double* __restrict__ part,
+                                     int64_t ld_part, double alpha, double beta,
+                                     double* __restrict__ C, int64_t ldc) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  for (int64_t j = blockIdx.y; j < n; j += gridDim.y) {
+    double s = 0.0;
+    for (int sp = 0; sp < ksplit; sp++) s += part[((int64_t)sp * n + j) * ld_part + i];
+    double v = alpha * s;
+    if (beta != 0.0) v = fma(beta, C[i + j * ldc], v);
+    C[i + j * ldc] = v;
+  }
+}
+
 template <bool A_MN, bool B_MN>
 void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p) {
   static bool attr = false;
@@ -312,7 +344,7 @@ void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     LA_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr = true;
   }
-  int tiles = p.num_tiles;
+  int tiles = p.num_tiles * p.ksplit;
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
   int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NTHREADS, SMEM_BYTES, ctx.stream>>>(tmA, tmB, p);
@@ -369,10 +401,38 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
   else p.num_tiles = p.tiles_m * p.tiles_n;
   if (p.num_tiles <= 0) return true;
+  // split-K for products with few output tiles and a long k (V^H C in QR, Gram matrices)
+  p.ksplit = 1;
+  p.kchunk = (int)ceil_div(k, BK);
+  p.partial = nullptr;
+  p.ld_part = 0;
+  Arena::Mark mk = ctx.arena.mark();
+  {
+    const int kblocks = (int)ceil_div(k, BK);
+    const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+    // (contexts that must not allocate — allow_side_stream == false — never split)
+    if (ctx.allow_side_stream && tri == TriFull && p.num_tiles * 4 <= sms && kblocks >= 128) {
+      int S = sms / p.num_tiles;
+      if (S > kblocks / 32) S = kblocks / 32;
+      if (S >= 2) {
+        p.kchunk = (int)ceil_div(kblocks, S);
+        p.ksplit = (int)ceil_div(kblocks, p.kchunk);
+        p.ld_part = round_up(m, 2);
+        p.partial = ctx.alloc<double>((size_t)p.ksplit * (size_t)n * (size_t)p.ld_part);
+      }
+    }
+  }
   if (a_mn && b_mn) launch<true, true>(ctx, tmA, tmB, p);
   else if (a_mn && !b_mn) launch<true, false>(ctx, tmA, tmB, p);
   else if (!a_mn && b_mn) launch<false, true>(ctx, tmA, tmB, p);
   else launch<false, false>(ctx, tmA, tmB, p);
+  if (p.ksplit > 1) {
+    dim3 g((unsigned)ceil_div(m, 128), (unsigned)(n < 1024 ? n : 1024));
+    splitk_reduce_kernel<<<g, 128, 0, ctx.stream>>>(m, n, p.ksplit, p.partial, p.ld_part, alpha,
+                                                    beta, C, ldc);
+    LA_CUDA_CHECK(cudaGetLastError());
+  }
+  ctx.arena.release(mk);
   return true;
 }
 

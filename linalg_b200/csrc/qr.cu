@@ -212,6 +212,137 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tall panels (the row slice of a CTA does not fit shared memory, e.g. 2^20 x 32): streaming
+// variant.  Same mathematics and the same one-grid-barrier-per-column exchange, but the
+// application of reflector j and the partial sums that define reflector j+1 are FUSED into a
+// single pass over the CTA's rows: each row is read once and written once per column, every
+// thread keeps one row of the panel in registers with all its loads in flight, so a column step
+// costs 2*(jb-j)*rows*sizeof(T) bytes of HBM traffic and runs at memory bandwidth.
+template <typename T> struct StreamJb { static constexpr int N = 32; };
+template <> struct StreamJb<zcomplex> { static constexpr int N = 16; };
+
+template <typename T>
+__global__ void __launch_bounds__(QR_NT)
+qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
+                       QrExchange<T>* xch, int64_t rpc) {
+  constexpr int JB = StreamJb<T>::N;
+  __shared__ T s_f[QR_MAX_JB];
+  __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
+  __shared__ T s_scale, s_beta;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = gridDim.x;
+  const int64_t rs = (int64_t)blockIdx.x * rpc;
+  int64_t nr = mp - rs; if (nr > rpc) nr = rpc; if (nr < 0) nr = 0;
+  T* base = A + rs;
+  const int kmax = (int)(mp < jb ? mp : jb);
+  unsigned target = 0;
+
+  // pass(ja): apply reflector ja (ja >= 0; scale/f/beta in shared memory) to the owned rows and
+  // accumulate, for the next reflector js = ja+1, the sums s_c = sum_{r > js} conj(a(r,js)) a(r,c)
+  for (int ja = -1; ja < kmax; ja++) {
+    const int js = ja + 1;
+    T acc[JB];
+#pragma unroll
+    for (int c = 0; c < JB; c++) acc[c] = zero<T>();
+    const T scale = ja >= 0 ? s_scale : zero<T>();
+    for (int64_t r = tid; r < nr; r += QR_NT) {
+      const int64_t gr = rs + r;
+      if (gr < ja) continue;                      // finished rows of R
+      if (ja < 0 && gr < 0) continue;
+      T a[JB];
+      const int c_lo = ja >= 0 ? ja : 0;
+#pragma unroll
+      for (int c = 0; c < JB; c++)
+        a[c] = (c >= c_lo && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
+      if (ja >= 0) {
+        if (gr == ja) {                           // the reflector's own row: v = 1
+#pragma unroll
+          for (int c = 0; c < JB; c++) {
+            if (c == ja) a[c] = s_beta;
+            else if (c > ja && c < jb) a[c] = sub(a[c], s_f[c]);
+          }
+        } else {                                  // gr > ja: v = x * scale
+          T v = zero<T>();
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c == ja) { v = mul(a[c], scale); a[c] = v; }
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c > ja && c < jb) a[c] = fnma_(v, s_f[c], a[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < JB; c++)
+          if (c >= ja && c < jb) base[(int64_t)c * lda + r] = a[c];
+      }
+      if (js < kmax) {
+        if (gr == js) {                           // next reflector's own row: publish it
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c >= js && c < jb) st_cg<T>(&xch->rowj[js & 1][c], a[c]);
+        } else if (gr > js) {
+          T x = zero<T>();
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c == js) x = conj_(a[c]);
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c >= js && c < jb) acc[c] = fma_(x, a[c], acc[c]);
+        }
+      }
+    }
+    if (js >= kmax) break;
+    // ---- block reduction of the partial sums, publication, grid barrier, global reduction
+    const int par = js & 1;
+#pragma unroll
+    for (int c = 0; c < JB; c++) {
+      const T s = warp_sum<T>(acc[c]);
+      if (lane == 0) s_red[warp][c] = s;
+    }
+    __syncthreads();
+    if (tid < jb && tid >= js) {
+      T s = zero<T>();
+      for (int w = 0; w < QR_NT / 32; w++) s = add(s, s_red[w][tid]);
+      st_cg<T>(&xch->part[par][blockIdx.x][tid], s);
+    }
+    target += (unsigned)G;
+    grid_barrier(&xch->barrier, target);
+    {
+      const int c = tid & 31, grp = tid >> 5;
+      T s = zero<T>();
+      if (c >= js && c < jb)
+        for (int g = grp; g < G; g += QR_NT / 32) s = add(s, ld_cg<T>(&xch->part[par][g][c]));
+      s_red[grp][c] = s;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      const int c = tid;
+      T s = zero<T>();
+      if (c >= js && c < jb)
+        for (int g = 0; g < QR_NT / 32; g++) s = add(s, s_red[g][c]);
+      T rj = (c >= js && c < jb) ? ld_cg<T>(&xch->rowj[par][c]) : zero<T>();
+      T alpha, sj;
+      if constexpr (Traits<T>::is_complex) {
+        alpha.x = __shfl_sync(0xffffffffu, rj.x, js); alpha.y = __shfl_sync(0xffffffffu, rj.y, js);
+        sj.x = __shfl_sync(0xffffffffu, s.x, js); sj.y = 0.0;
+      } else {
+        alpha = __shfl_sync(0xffffffffu, rj, js);
+        sj = __shfl_sync(0xffffffffu, s, js);
+      }
+      T beta, tj, sc;
+      householder<T>(alpha, (double)real_(sj), beta, tj, sc);
+      const T w = fma_(conj_(sc), s, rj);        // w_c = a(js,c) + conj(scale) * s_c
+      s_f[c] = mul(conj_(tj), w);                // f_c = conj(tau) * w_c
+      if (c == js) {
+        s_scale = sc;
+        s_beta = beta;
+        if (blockIdx.x == 0) tau[js] = tj;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // T factor of a block reflector from G = V^H V and tau (forward, columnwise ?larft):
 //   T(i,i) = tau_i,  T(0:i,i) = -tau_i * T(0:i,0:i) * G(0:i,i);  strictly lower part = 0.
 template <typename T>
@@ -266,6 +397,12 @@ void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
     if (smem > QR_SMEM_BUDGET) { use_smem = 0; smem = 0; }
   }
   LA_CUDA_CHECK(cudaMemsetAsync(&xch->barrier, 0, sizeof(unsigned), ctx.stream));
+  if (!use_smem) {
+    void* sargs[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc};
+    LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_stream_kernel<T>, dim3((unsigned)G),
+                                              dim3(QR_NT), sargs, 0, ctx.stream));
+    return;
+  }
   void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem};
   LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_kernel<T>, dim3((unsigned)G),
                                             dim3(QR_NT), args, smem, ctx.stream));
@@ -336,8 +473,13 @@ void geqrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau) {
   ensure_attrs<T>();
   Arena::Mark mk = ctx.arena.mark();
   QrWork<T> w = make_work<T>(ctx, m, QR_MAX_JB, n);
-  for (int64_t j0 = 0; j0 < k; j0 += QR_MAX_JB) {
-    const int jb = (int)((k - j0) < QR_MAX_JB ? (k - j0) : QR_MAX_JB);
+  // panels too tall for the shared-memory kernel go through the streaming kernel, which holds
+  // a row of the panel in registers: narrower panels for complex
+  const bool tall = (size_t)round_up(ceil_div(m, ctx.sm_count), 2) * QR_MAX_JB * sizeof(T) >
+                    QR_SMEM_BUDGET;
+  const int64_t nb = tall ? StreamJb<T>::N : QR_MAX_JB;
+  for (int64_t j0 = 0; j0 < k; j0 += nb) {
+    const int jb = (int)((k - j0) < nb ? (k - j0) : nb);
     const int64_t mp = m - j0;
     T* P = A + j0 + j0 * lda;
     qr_panel<T>(ctx, mp, jb, P, lda, d_tau + j0, w.xch);

@@ -332,6 +332,26 @@ def test_geqrf_matches_lapack_conventions(rng, dt, shape, product_abi, oracle_ab
     assert checks.rel(tau[:k] - rtau[:k], rtau[:k]) < 100 * max(shape) * _eps(dt)
 
 
+@pytest.mark.parametrize("dt,m,n", [(np.float64, 150000, 40), (np.complex128, 70000, 24),
+                                    (np.float32, 250000, 20)], ids=IDS[1:] + IDS[:1])
+def test_tall_skinny_qr_streaming_panels(rng, dt, m, n, product_abi, oracle_abi):
+    # panels whose row slices exceed shared memory take the streaming panel kernel and the
+    # split-K products V^H C / V^H V (BASELINE config c5 is 2^20 x 512)
+    A = _rand(rng, (m, n), dt, -0.5)
+    B = _rand(rng, (m, 2), dt, -0.5)
+
+    def run():
+        a, tau = la.GeneralMatrix(A).qr_raw()
+        x = la.solvels(la.GeneralMatrix(A), la.GeneralMatrix(B)).raw[:n]
+        return np.triu(a.raw[:n]), tau[:n], x
+
+    (r, tau, x), (rr, rtau, xr) = _both(run, product_abi, oracle_abi)
+    tol = 2e3 * _eps(dt) * np.sqrt(m)
+    assert checks.rel(r - rr, rr) < tol
+    assert checks.rel(tau - rtau, rtau) < tol
+    assert checks.rel(x - xr, xr) < 100 * tol
+
+
 @pytest.mark.parametrize("dt", DTYPES, ids=IDS)
 def test_qr_orgqr_ormqr(rng, dt, product_abi, oracle_abi):
     m, n = 120, 50
