@@ -20,6 +20,7 @@ template <typename T>
 void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
               int* d_info);
 int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes);
+void lu_panel_prepare(Context& ctx);
 
 namespace {
 
@@ -198,9 +199,20 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   // stable set of free SMs, and the leaf's CTAs then wait for one another forever.
   const bool dmma_ok = std::is_same<T, double>::value && (lda % 2 == 0) &&
                        (((uintptr_t)A & 15) == 0);
-  const bool lookahead = ctx.allow_side_stream && dmma_ok && k >= 4096 && leaf_ctas <= 40 &&
-                         k > NB;
+  static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
+  const bool lookahead = !la_disabled && ctx.allow_side_stream && dmma_ok && k >= 8192 &&
+                         leaf_ctas <= 40 && k > NB;
   Context* side = lookahead ? side_context(ctx) : nullptr;
+  if (side) {
+    // every first-use allocation of the side context (stream, arena block, pivot-exchange
+    // area) is made here, before anything is enqueued: creating them while the cooperative
+    // leaf kernel of an earlier step is running has been seen to hang the device
+    Arena::Mark smk = side->arena.mark();
+    (void)side->arena.alloc(1 << 20);
+    side->arena.release(smk);
+    lu_panel_prepare(*side);
+    LA_CUDA_CHECK(cudaStreamSynchronize(side->stream));
+  }
   const int side_sms = (int)(leaf_ctas < 16 ? 16 : leaf_ctas);
   bool panel_done = false;  // panel of the current j0 already factored (on the side stream)?
   for (int64_t j0 = 0; j0 < k; j0 += NB) {

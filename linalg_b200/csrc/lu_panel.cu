@@ -353,6 +353,9 @@ void lu_panel_adopt_exchange(Context& ctx, void* device_mem, void* state_storage
   ctx.lu_state = st;
 }
 
+// Make sure the context owns its exchange area (allocates on first use).
+void lu_panel_prepare(Context& ctx) { (void)panel_state(ctx); }
+
 // Widest leaf the panel kernel takes for an m-row panel (0: the panel is too tall for one
 // cooperative launch with a row per thread).
 int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
