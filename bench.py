@@ -39,6 +39,7 @@ sys.path.insert(0, str(ROOT))
 
 FP64_DMMA_PEAK_TFLOPS = 37.0   # measured: tools/microbench/peak_fp64.cu on this pool's B200
 CPU_SAMPLE_N = 8192
+DGEMM_DRAM_BYTES_PER_LAUNCH = 85.27e9   # N = 16384, measured with ncu (see profiles/README.md)
 WORKLOAD = "dgemm N={n} NoTrans/NoTrans alpha=1 beta=1 on zeroed C (Matrix#*)"
 
 
@@ -214,9 +215,68 @@ def time_factorizations(n, steps):
     Lx = Lm @ (Lm.T @ xm)
     Ax = A0.T @ xm
     out["dpotrf_probe_residual"] = float(((Ax - Lx).norm() / (A0.norm() * xm.norm())).item())
+    del A0, W
+    torch.cuda.empty_cache()
+    out.update(time_other_types())
     out["fp64_peak_tflops"] = FP64_DMMA_PEAK_TFLOPS
     out["dgetrf_frac_of_peak"] = out["dgetrf_tflops"] / FP64_DMMA_PEAK_TFLOPS
     out["dpotrf_frac_of_peak"] = out["dpotrf_tflops"] / FP64_DMMA_PEAK_TFLOPS
+    return out
+
+
+def time_other_types():
+    """Float32 (3xTF32 tcgen05) and complex128 (DMMA) GEMM and the tall-skinny least squares of
+    BASELINE config c5, device resident, one size each."""
+    import torch
+
+    from linalg_b200 import dev, ffi
+    out = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def best(fn, reps=3):
+        b = 1e30
+        for i in range(reps + 1):
+            torch.cuda.synchronize()
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            if i:
+                b = min(b, e0.elapsed_time(e1))
+        return b
+
+    for dt, name, n, fl, want in ((torch.float32, "sgemm", 16384, 2, 3), (torch.complex128, "zgemm", 8192, 8, 2)):
+        A = torch.rand((n, n), dtype=dt, device="cuda")
+        B = torch.rand((n, n), dtype=dt, device="cuda")
+        Cm = torch.zeros((n, n), dtype=dt, device="cuda")
+        ms = best(lambda: dev.gemm(ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, 1.0, A, n, B, n, 0.0, Cm, n))
+        assert dev.last_gemm_path() == want, f"{name}: tensor-core path not taken"
+        # probe-vector check: C x == A (B x)
+        x = torch.rand(n, dtype=dt, device="cuda")
+        lhs = Cm.T @ x
+        rhs = A.T @ (B.T @ x)
+        out[f"{name}_n"] = n
+        out[f"{name}_tflops"] = fl * n ** 3 / (ms * 1e-3) * 1e-12
+        out[f"{name}_probe_relerr"] = float(((lhs - rhs).norm() / rhs.norm()).item())
+        del A, B, Cm
+        torch.cuda.empty_cache()
+    m, n = 1 << 20, 512
+    A = torch.rand((n, m), dtype=torch.float64, device="cuda")
+    b = torch.rand((1, m), dtype=torch.float64, device="cuda")
+    W, X = torch.empty_like(A), torch.empty_like(b)
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def ls():
+        W.copy_(A)
+        X.copy_(b)
+        dev.gels(ffi.NO_TRANS, m, n, 1, W, m, X, m, info)
+
+    tcopy = best(lambda: (W.copy_(A), X.copy_(b)), reps=2)
+    ms = best(ls, reps=2) - tcopy
+    r = A.T @ X[0, :n] - b[0]
+    out["dgels_1Mx512_ms"] = ms
+    out["dgels_1Mx512_tflops"] = (2.0 * m * n * n - (2.0 / 3.0) * n ** 3) / (ms * 1e-3) * 1e-12
+    out["dgels_1Mx512_normal_eq_residual"] = float(((A @ r).norm() / (A.norm() * r.norm())).item())
     return out
 
 
@@ -341,7 +401,10 @@ def run_ours(args):
             "e2e": e2e, "gpu_launches": args.steps, "clocks": clk.summary(),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": FP64_DMMA_PEAK_TFLOPS,
                          "unit": "TFLOP/s", "frac": achieved / FP64_DMMA_PEAK_TFLOPS,
-                         "traffic": None, "kernel": "dgemm_dmma_kernel<A_MN=1,B_MN=0>",
+                         "traffic": DGEMM_DRAM_BYTES_PER_LAUNCH if (world == 1 and n == 16384) else None,
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, "
+                                           "ncu --set full (profiles/r1_dgemm16384_ncu_raw.csv)",
+                         "kernel": "dgemm_dmma_kernel<A_MN=1,B_MN=0>",
                          "kernel_ms": kern_ms,
                          "peak_source": "FP64 DMMA (mma.sync m8n8k4) register-resident peak measured "
                                         "by tools/microbench/peak_fp64.cu on this pool; "

@@ -12,8 +12,9 @@
 //     (128-byte swizzle) -> 12 tcgen05.mma (M=128, N=256, K=8) per stage issued by one thread
 //     -> accumulator in TMEM, double buffered (2 x 256 columns) so that the epilogue of tile t
 //     overlaps the MMAs of tile t+1;
-//   * warp roles: 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = epilogue
-//     (tcgen05.ld 32 lanes x 32 columns per warp, alpha/beta, coalesced column-major stores).
+//   * warp roles: 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..11 = epilogue (two
+//     warps per TMEM lane quarter; tcgen05.ld 32 lanes x 32 columns, alpha/beta, coalesced
+//     column-major loads/stores issued 32 at a time).
 // Algorithmic work 2*m*n*k flops; the tensor pipe executes 3x that in TF32.
 #include "la_internal.h"
 #include "tma_utils.cuh"
@@ -28,8 +29,13 @@ constexpr int S_A_BYTES = SM_ * SK_ * 4;               // 16 KB per (hi or lo)
 constexpr int S_B_BYTES = SN_ * SK_ * 4;               // 32 KB per (hi or lo)
 constexpr int S_STAGE_BYTES = 2 * S_A_BYTES + 2 * S_B_BYTES;  // 96 KB
 constexpr int S_SMEM_BYTES = S_STAGES * S_STAGE_BYTES + 1024 + 256;
-constexpr int S_THREADS = 256;
+constexpr int S_THREADS = 384;                         // 4 control warps + 8 epilogue warps
 constexpr int S_TMEM_COLS = 512;                       // two 256-column accumulators
+// The tensor core truncates when it adds into its FP32 accumulator; on same-signed data that is a
+// bias of ~1e-8 per accumulated term.  k is therefore processed in chunks of S_KCHUNK: each chunk
+// is accumulated in TMEM from zero and added to C in FP32 (round to nearest) by the epilogue,
+// which the double-buffered accumulator overlaps with the next chunk's MMAs.
+constexpr int S_KCHUNK_BLOCKS = 16;                    // 16 x 32 = 512 terms per chunk
 
 struct SParams {
   int64_t m, n, k;
@@ -166,7 +172,7 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < S_STAGES; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; a++) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
+    for (int a = 0; a < 2; a++) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 8); }
     mbar_fence_init();
   }
   if (warp == 2) {
@@ -219,34 +225,38 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
         int tm, tn;
         s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
         if (s_tile_skipped(p.tri, tm, tn)) continue;
-        mbar_wait(&tempty_bar[as], aphase ^ 1);
-        tc_fence_after();
-        const uint32_t tacc = tmem_base + (uint32_t)(as * SN_);
-        for (int kb = 0; kb < kblocks; kb++) {
-          mbar_wait(&full_bar[stage], phase);
+        for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
+          const int kb1 = min(kblocks, kb0 + S_KCHUNK_BLOCKS);
+          mbar_wait(&tempty_bar[as], aphase ^ 1);
           tc_fence_after();
-          const uint32_t s = smem_u32(smem + stage * S_STAGE_BYTES);
+          const uint32_t tacc = tmem_base + (uint32_t)(as * SN_);
+          for (int kb = kb0; kb < kb1; kb++) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const uint32_t s = smem_u32(smem + stage * S_STAGE_BYTES);
 #pragma unroll
-          for (int ks = 0; ks < SK_ / 8; ks++) {
-            const uint32_t ko = ks * 32;  // 8 floats
-            const uint64_t ahi = make_kmajor_sw128_desc(s + ko);
-            const uint64_t alo = make_kmajor_sw128_desc(s + S_A_BYTES + ko);
-            const uint64_t bhi = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + ko);
-            const uint64_t blo = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + S_B_BYTES + ko);
-            umma_tf32(tacc, ahi, blo, idesc, (kb | ks) ? 1u : 0u);
-            umma_tf32(tacc, alo, bhi, idesc, 1u);
-            umma_tf32(tacc, ahi, bhi, idesc, 1u);
+            for (int ks = 0; ks < SK_ / 8; ks++) {
+              const uint32_t ko = ks * 32;  // 8 floats
+              const uint64_t ahi = make_kmajor_sw128_desc(s + ko);
+              const uint64_t alo = make_kmajor_sw128_desc(s + S_A_BYTES + ko);
+              const uint64_t bhi = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + ko);
+              const uint64_t blo = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + S_B_BYTES + ko);
+              umma_tf32(tacc, ahi, blo, idesc, (kb > kb0 || ks) ? 1u : 0u);
+              umma_tf32(tacc, alo, bhi, idesc, 1u);
+              umma_tf32(tacc, ahi, bhi, idesc, 1u);
+            }
+            umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
+            if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
           }
-          umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
-          if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+          umma_commit(&tfull_bar[as]);        // chunk accumulator complete
+          if (++as == 2) { as = 0; aphase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);        // accumulator complete
-        if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> C =====================
     const int q = warp & 3;                 // TMEM lane quarter of this warp
+    const int half = (warp - 4) >> 2;       // which half of the column chunks it drains
     int as = 0;
     uint32_t aphase = 0;
     const bool beta_zero = p.beta == 0.f;
@@ -254,33 +264,44 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
       int tm, tn;
       s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
       if (s_tile_skipped(p.tri, tm, tn)) continue;
-      mbar_wait(&tfull_bar[as], aphase);
-      tc_fence_after();
       const int64_t row = (int64_t)tm * SM_ + q * 32 + lane;
-      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * SN_);
+      for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
+        const bool first = kb0 == 0;
+        mbar_wait(&tfull_bar[as], aphase);
+        tc_fence_after();
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * SN_);
 #pragma unroll 1
-      for (int cc = 0; cc < SN_ / 32; cc++) {
-        uint32_t v[32];
-        tmem_ld32(tbase + cc * 32, v);
-        const int64_t col0 = (int64_t)tn * SN_ + cc * 32;
-        if (row < p.m) {
+        for (int cc = half; cc < SN_ / 32; cc += 2) {
+          uint32_t v[32];
+          tmem_ld32(tbase + cc * 32, v);
+          const int64_t col0 = (int64_t)tn * SN_ + cc * 32;
+          if (row < p.m) {
+            float* dst0 = p.C + row + col0 * p.ldc;
+            const bool need_c = !first || !beta_zero;
+            float cold[32];
+            if (need_c) {  // all loads first: 32 independent requests in flight
 #pragma unroll
-          for (int j = 0; j < 32; j++) {
-            const int64_t col = col0 + j;
-            if (col >= p.n) break;
-            if (p.tri == TriLower && row < col) continue;
-            if (p.tri == TriUpper && row > col) continue;
-            float* dst = p.C + row + col * p.ldc;
-            float r = p.alpha * __uint_as_float(v[j]);
-            if (!beta_zero) r = fmaf(p.beta, *dst, r);
-            *dst = r;
+              for (int j = 0; j < 32; j++)
+                cold[j] = (col0 + j < p.n) ? dst0[(int64_t)j * p.ldc] : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+              const int64_t col = col0 + j;
+              if (col >= p.n) break;
+              if (p.tri == TriLower && row < col) continue;
+              if (p.tri == TriUpper && row > col) continue;
+              float r = p.alpha * __uint_as_float(v[j]);
+              if (!first) r += cold[j];                     // later chunks accumulate into C
+              else if (!beta_zero) r = fmaf(p.beta, cold[j], r);
+              dst0[(int64_t)j * p.ldc] = r;
+            }
           }
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[as]);
-      if (++as == 2) { as = 0; aphase ^= 1; }
     }
   }
   tc_fence_before();

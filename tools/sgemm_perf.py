@@ -10,11 +10,12 @@ def timeit(fn, reps=3):
         best = min(best, e0.elapsed_time(e1))
     return best
 torch.manual_seed(0)
+POS = True
 for (m, n, k) in [(512, 384, 256), (1000, 777, 333), (2048, 2048, 2048), (8192, 8192, 8192), (16384, 16384, 16384)]:
     for (ta, tb) in [(dev.NO_TRANS, dev.NO_TRANS), (dev.TRANS, dev.NO_TRANS), (dev.NO_TRANS, dev.TRANS)]:
         if m > 4096 and ta != dev.NO_TRANS: continue
-        A = torch.rand((k, m) if ta == dev.NO_TRANS else (m, k), dtype=torch.float32, device="cuda") - 0.5
-        B = torch.rand((n, k) if tb == dev.NO_TRANS else (k, n), dtype=torch.float32, device="cuda") - 0.5
+        A = torch.rand((k, m) if ta == dev.NO_TRANS else (m, k), dtype=torch.float32, device="cuda")
+        B = torch.rand((n, k) if tb == dev.NO_TRANS else (k, n), dtype=torch.float32, device="cuda")
         C = torch.zeros((n, m), dtype=torch.float32, device="cuda")
         ms = timeit(lambda: dev.gemm(ta, tb, m, n, k, 1.0, A, A.shape[1], B, B.shape[1], 0.0, C, m))
         err = float("nan")
