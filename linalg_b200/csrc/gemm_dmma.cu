@@ -16,8 +16,10 @@
 //   * both operand layouts per side (contiguous along M/N or along K), so NN/NT/TN/TT need
 //     no transposition pass;
 //   * k-slot permutation: the 16 k of a stage are assigned to (tig, step) as
-//     k = (tig&1) + 8*(tig>>1) + 2*step, which makes K-major fragment loads conflict free
-//     and MN-major ones 2-way (shared-memory bandwidth is ~30% utilised at DMMA peak);
+//     k = (tig&1) + 4*(tig>>1) + {0,2,8,10}[step].  Two of a warp's four k have bit 0 set and
+//     two have bit 2 set, which spreads a fragment load over all 32 banks in BOTH swizzled
+//     layouts (K-major: chunk = (k>>1)^(mn&7), half = k&1; MN-major: chunk = (mn>>1)^(k&7)),
+//     i.e. the minimum two wavefronts per 64-bit warp load;
 //   * epilogue straight from registers: alpha/beta, optional triangle mask (SYRK-style).
 // Algorithmic work: 2*m*n*k flops per call; HBM traffic ~ (m*k + k*n)*8*(reuse factor) +
 // m*n*8*(1 or 2) bytes, tensor-pipe bound for k >= 64.
@@ -243,7 +245,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
   const int gid = lane >> 2, tig = lane & 3;
   const int wm = warp & 1, wn = warp >> 1;     // 2 x 4 warps -> 64 x 32 warp tiles
-  const int kslot = (tig & 1) + 8 * (tig >> 1);  // + 2*step
+  const int kslot = (tig & 1) + 4 * (tig >> 1);  // + kstep(ks) = {0, 2, 8, 10}
   int stage = 0;
   uint32_t phase = 0;
   const bool beta_zero = p.beta == 0.0;
@@ -255,6 +257,18 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (!tile_active(p, tm, tn)) continue;
     const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
 
+    if (!beta_zero && p.ksplit == 1) {
+      // pull the C tile into L2 while the main loop runs: thread t covers column t/2, four
+      // 128-byte lines of its 128 rows
+      const int64_t col = (int64_t)tn * BN + (threadIdx.x >> 1);
+      if (col < p.n) {
+        const double* cp = p.C + col * p.ldc + (int64_t)tm * BM + (threadIdx.x & 1) * 64;
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if ((int64_t)tm * BM + (threadIdx.x & 1) * 64 + q * 16 < p.m)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(cp + q * 16));
+      }
+    }
     double acc[8][4][2];
 #pragma unroll
     for (int i = 0; i < 8; i++)
@@ -267,7 +281,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const unsigned char* sB = sA + A_STAGE_BYTES;
 #pragma unroll
       for (int ks = 0; ks < 4; ks++) {
-        const int kk = kslot + 2 * ks;
+        const int kk = kslot + 2 * (ks & 1) + 8 * (ks >> 1);
         double a[8], b[4];
 #pragma unroll
         for (int i = 0; i < 8; i++)
@@ -304,16 +318,25 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           continue;
         }
         double* Ccol = p.C + col * p.ldc;
+        // all loads of a column first (independent, in flight together), then the stores: a
+        // load-store chain per element would expose one memory round trip per row
+        bool act[8];
+        double cin[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
           const int64_t row = row_base + i * 8;
-          if (row >= p.m) continue;
           const int64_t mrow = p.zmode ? (row >> 1) : row;
-          if (p.tri == TriLower && mrow < col) continue;
-          if (p.tri == TriUpper && mrow > col) continue;
+          act[i] = row < p.m && !(p.tri == TriLower && mrow < col) &&
+                   !(p.tri == TriUpper && mrow > col);
+          cin[i] = (act[i] && !beta_zero) ? __ldcg(Ccol + row) : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          if (!act[i]) continue;
+          const int64_t row = row_base + i * 8;
           double v = p.alpha * acc[i][j][c];
-          if (!beta_zero) v = fma(p.beta, Ccol[row], v);
-          if (p.herm_diag && mrow == col && (row & 1)) v = 0.0;
+          if (!beta_zero) v = fma(p.beta, cin[i], v);
+          if (p.herm_diag && (p.zmode ? (row >> 1) : row) == col && (row & 1)) v = 0.0;
           Ccol[row] = v;
         }
       }

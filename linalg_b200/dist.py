@@ -44,14 +44,17 @@ class DevOps:
         from . import dev
         self.dev = dev
         self.info = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.first = torch.zeros(1, dtype=torch.int32, device="cuda")   # first failing column
 
     @staticmethod
     def _ld(t):
         return t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1)
 
-    def potrf_lower(self, a):                      # a: n x n view
+    def potrf_lower(self, a, k0=0):                # a: n x n view at global offset k0
         n = a.shape[0]
         self.dev.potrf(self.dev.LOWER, n, a, self._ld(a), self.info)
+        # keep LAPACK's meaning of info (first non-positive pivot, global index) without a sync
+        self.first = torch.where((self.first == 0) & (self.info != 0), self.info + k0, self.first)
 
     def trsm_right_lower_ct(self, tri, b):         # b <- b * tri^-H ; b: m x n view, tri: n x n
         m, n = b.shape[1], b.shape[0]
@@ -64,7 +67,7 @@ class DevOps:
                       self._ld(b), 1.0, c, self._ld(c))
 
     def info_value(self):
-        return int(self.info.item())
+        return int(self.first.item())
 
     def geqrf(self, a):                            # in-place QR of the m x n view, returns tau
         m, n = a.shape[1], a.shape[0]
@@ -104,7 +107,7 @@ def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, group=None):
         if rank == owner:
             col = a_local[offs[k]: offs[k] + kb]       # n x kb view
             diag = col[:, k0: k0 + kb]
-            ops.potrf_lower(diag)
+            ops.potrf_lower(diag, k0)
             if n - k0 - kb > 0:
                 ops.trsm_right_lower_ct(diag, col[:, k0 + kb:])
             panel.copy_(col[:, k0:])
@@ -125,8 +128,13 @@ def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, group=None):
             jb = min(nb, n - j0)
             c = a_local[offs[j]: offs[j] + jb][:, j0:]             # (n - j0) x jb
             ops.gemm_nt_sub(c, panel[:, j0 - k0:], panel[:, j0 - k0: j0 - k0 + jb])
-    if hasattr(ops, "info_value"):
-        info = ops.info_value()
+    info = ops.info_value()
+    if world > 1:                                   # smallest non-zero info over the ranks
+        big = 2 ** 31 - 1
+        t = torch.tensor([info if info > 0 else big], dtype=torch.int64, device=a_local.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+        info = int(t.item())
+        info = 0 if info == big else info
     return info
 
 

@@ -20,10 +20,10 @@ class CpuOps:
     def __init__(self):
         self._info = 0
 
-    def potrf_lower(self, a):
+    def potrf_lower(self, a, k0=0):
         from oracle import c_ref
         F, info = c_ref.potrf("L", np.asfortranarray(a.numpy().T))
-        self._info = self._info or info
+        self._info = self._info or (info + k0 if info else 0)
         a.copy_(torch.from_numpy(np.ascontiguousarray(F.T)))
 
     def trsm_right_lower_ct(self, tri, b):
