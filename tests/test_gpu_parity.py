@@ -122,7 +122,14 @@ def test_large_gemm_takes_the_pipelined_host_path(rng, tb, product_abi, oracle_a
     got = _gemm_call(product_abi, np.float64, ffi.NO_TRANS, tb, m, n, k, 1.0, A, B, 1.0, C0)
     ref = _gemm_call(oracle_abi, np.float64, ffi.NO_TRANS, tb, m, n, k, 1.0, A, B, 1.0, C0)
     bad = np.argwhere(np.abs(got - ref) > 1e-9)
-    assert len(bad) == 0, (len(bad), bad[:8].tolist(), bad[-4:].tolist())
+    if len(bad):
+        # say which side is off: a third, independent product (numpy's own BLAS, one thread of
+        # python per row block so that no threaded kernel is involved)
+        Bop = B if tb == ffi.NO_TRANS else B.T
+        ref2 = C0 + np.vstack([A[i:i + 64] @ Bop for i in range(0, m, 64)])
+        raise AssertionError(("pipelined host gemm mismatch", len(bad), bad[:6].tolist(),
+                              bad[-3:].tolist(), "max|got-ref2|", float(np.abs(got - ref2).max()),
+                              "max|oracle-ref2|", float(np.abs(ref - ref2).max())))
     assert checks.rel(got - ref, ref) < 8 * _eps(np.float64) * np.sqrt(k)
 
 
