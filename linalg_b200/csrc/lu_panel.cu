@@ -186,13 +186,11 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int G = gridDim.x;
   T* cand = reinterpret_cast<T*>(smem_raw);      // cand[w * JBM + c]: each warp's best row
-  T* rows_all = cand + NW * JBM;                 // rows_all[g * JBM + c]: every CTA's candidate
-  T* rj = rows_all + (size_t)G * JBM;            // rj[c]: row j of the panel
-  ukey* hv = reinterpret_cast<ukey*>(((uintptr_t)(rj + JBM) + 7) & ~(uintptr_t)7);
-  int* hi = reinterpret_cast<int*>(hv + G);
+  T* prow2 = cand + NW * JBM;                    // prow2[par][c]: the pivot row of column j
+  T* rj2 = prow2 + 2 * JBM;                      // rj2[par][c]: row j of the panel
   __shared__ ukey sval[NW];
   __shared__ int sidx[NW];
-  __shared__ int s_pg, s_pi;
+  __shared__ int s_pi[2];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rs = blockIdx.x * rpc;                 // rpc == LU_NT: one row per thread
@@ -205,9 +203,16 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
     a[c] = (have_row && c < jb) ? A[(int64_t)gr + (int64_t)c * lda] : zero<T>();
   ukey nk = have_row ? key_of((double)abs1(a[0])) : 0;
 
+  // Two block barriers per column.  Everything the barriers separate is double-buffered by
+  // column parity (prow2, rj2, s_pi, the exchange packets) or is only touched by warp 0 between
+  // them (cand, sval, sidx), so column j+1's first phase may start while slower warps are still
+  // eliminating column j.
   for (int j = 0; j < jb; j++) {
     const int par = j & 1;
     const unsigned seq = seq_base + (unsigned)j + 1u;
+    T* prow = prow2 + par * JBM;
+    T* rj = rj2 + par * JBM;
+    const bool own_j = j >= rs && j < rs + LU_NT;
     TRACE(0);
     // ---- arg-max of column j over the rows gr >= j: per warp, then across warps
     ukey bv = nk;
@@ -234,63 +239,50 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
       const unsigned wm = __ballot_sync(0xffffffffu, lane < NW && sidx[myw < NW ? myw : 0] == ci && have);
       const int wwin = have ? __ffs(wm) - 1 : 0;
       const T crow = (have && lane < JBM) ? cand[wwin * JBM + lane] : zero<T>();
-      const bool own_j = j >= rs && j < rs + LU_NT && j < m;
       if (G == 1) {  // single CTA: no global exchange
-        if (lane == 0) { hv[0] = cv; hi[0] = ci; }
-        if (lane < JBM) rows_all[lane] = crow;
+        if (lane < JBM) prow[lane] = crow;
+        if (lane == 0) { s_pi[par] = ci; ipiv[j] = row0 + ci + 1; }
       } else {
+        // publish this CTA's candidate (|value|, row) with the row's contents, and row j
         if (lane == 0)
           ll_store(&xch->hdr[par][blockIdx.x], cv,
                    ((unsigned long long)seq << 32) | (unsigned)(have ? ci : 0xffffffffu));
         if (lane < JBM) ll_put<T>(&xch->row[par][blockIdx.x][lane * W], crow, seq);
         if (own_j && lane < JBM) ll_put<T>(&xch->rowj[par][lane * W], rj[lane], seq);
-      }
-    }
-    TRACE(2);
-    // ---- all warps gather: warp w lands the packets of CTAs w, w+NW, ... in shared memory
-    if (G > 1) {
-      for (int g = warp; g < G; g += NW) {
-        if (lane < JBM) rows_all[g * JBM + lane] = ll_get<T>(&xch->row[par][g][lane * W], seq);
-        if (lane == 31) {
+        TRACE(2);
+        // every CTA's header, one (or a few) per lane -> the same winner everywhere
+        ukey pv = 0;
+        int pi = 0x7fffffff, pg = 0;
+        for (int g = lane; g < G; g += 32) {
           unsigned long long d, t;
           ll_wait(&xch->hdr[par][g], seq, d, t);
-          hv[g] = d;
           const unsigned uidx = (unsigned)(t & 0xffffffffull);
-          hi[g] = uidx == 0xffffffffu ? 0x7fffffff : (int)uidx;
+          const int idx = uidx == 0xffffffffu ? 0x7fffffff : (int)uidx;
+          if (idx != 0x7fffffff && (pi == 0x7fffffff || d > pv || (d == pv && idx < pi))) {
+            pv = d; pi = idx; pg = g;
+          }
+        }
+        int pi_w = pi;
+        warp_argmax_redux(pv, pi_w);
+        const unsigned gm = __ballot_sync(0xffffffffu, pi == pi_w && pi_w != 0x7fffffff);
+        const int src = gm ? __ffs(gm) - 1 : 0;
+        pg = __shfl_sync(0xffffffffu, pg, src);
+        TRACE(3);
+        // only the winner's row is fetched (it was published together with its header)
+        if (lane < JBM)
+          prow[lane] = pg == (int)blockIdx.x ? crow : ll_get<T>(&xch->row[par][pg][lane * W], seq);
+        if (lane == 0) {
+          s_pi[par] = pi_w;
+          if (blockIdx.x == 0) ipiv[j] = row0 + pi_w + 1;
         }
       }
-      // row j comes from its owner CTA (which may be this one: then rj is already in place)
-      const bool own_j = j >= rs && j < rs + LU_NT;
-      if (!own_j && warp == NW - 1 && lane < JBM) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
-    }
-    __syncthreads();
-    TRACE(3);
-    // ---- warp 0 derives the winner and posts (pi, pg)
-    if (warp == 0) {
-      ukey pv = 0;
-      int pi = 0x7fffffff, pg = 0;
-      for (int g = lane; g < G; g += 32) {
-        const ukey v = hv[g];
-        const int idx = hi[g];
-        if (idx != 0x7fffffff && (pi == 0x7fffffff || v > pv || (v == pv && idx < pi))) {
-          pv = v; pi = idx; pg = g;
-        }
-      }
-      int pi_w = pi;
-      warp_argmax_redux(pv, pi_w);
-      const unsigned gm = __ballot_sync(0xffffffffu, pi == pi_w && pi_w != 0x7fffffff);
-      const int src = gm ? __ffs(gm) - 1 : 0;
-      pg = __shfl_sync(0xffffffffu, pg, src);
-      if (lane == 0) {
-        s_pg = pg;
-        s_pi = pi_w;
-        if (blockIdx.x == 0) ipiv[j] = row0 + pi_w + 1;
-      }
+    } else if (warp == 1 && G > 1 && !own_j) {
+      // row j comes from its owner CTA
+      if (lane < JBM) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
     }
     __syncthreads();
     TRACE(4);
-    const T* prow = rows_all + s_pg * JBM;
-    const int pi = s_pi;
+    const int pi = s_pi[par];
     // ---- row interchange j <-> pi in the registers of the two owners
     if (pi != j) {
       if (gr == pi) {
@@ -313,8 +305,6 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
       else nk = KeyAt<T, JBM, 0>::get(j + 1, a);   // as ?getf2: no scaling, update is a no-op
     }
     TRACE(5);
-    // cand / rj / landing areas are rewritten only after the next column's first __syncthreads
-    __syncthreads();
   }
   if (have_row) {
 #pragma unroll
@@ -383,8 +373,7 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
     abort();
   }
   constexpr int JBM = MaxJb<T>::N;
-  size_t smem = ((size_t)(LU_NT / 32) * JBM + (size_t)G * JBM + JBM) * sizeof(T) +
-                (size_t)G * (sizeof(unsigned long long) + sizeof(int)) + 16;
+  size_t smem = ((size_t)(LU_NT / 32) * JBM + 4 * (size_t)JBM) * sizeof(T) + 16;
   int mi = (int)m, row0i = (int)row0, rpci = (int)rpc;
   unsigned seq_base = st->seq;
   st->seq += 64;
