@@ -213,7 +213,6 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     lu_panel_prepare(*side);
     LA_CUDA_CHECK(cudaStreamSynchronize(side->stream));
   }
-  const int side_sms = (int)(leaf_ctas < 16 ? 16 : leaf_ctas);
   bool panel_done = false;  // panel of the current j0 already factored (on the side stream)?
   for (int64_t j0 = 0; j0 < k; j0 += NB) {
     const int64_t jb = NB < k - j0 ? NB : k - j0;
@@ -232,6 +231,10 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     const int64_t j1 = j0 + jb;
     const int64_t jb1 = j1 < k ? (NB < k - j1 ? NB : k - j1) : 0;
     if (lookahead && jb1 > 0 && nr > jb1) {
+      // the next panel has m - j1 rows: its cooperative leaf needs that many SMs / 512, the rest
+      // of the side stream's work is happy with 16
+      const int64_t ctas1 = ceil_div(m - j1, (int64_t)512);
+      const int side_sms = (int)(ctas1 < 16 ? 16 : ctas1);
       gemm<T>(ctx, OpN, OpN, mr, jb1, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
       LA_CUDA_CHECK(cudaEventRecord(ctx.ev[0], ctx.stream));
       LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));

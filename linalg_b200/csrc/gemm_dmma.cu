@@ -11,7 +11,7 @@
 //   * CTA tile 128x128x16, 4-stage ring of TMA loads (cp.async.bulk.tensor.2d, 128-byte
 //     swizzle, zero fill at ragged edges) signalled through mbarriers;
 //   * 1 producer warpgroup (one elected lane issues TMA; a whole warpgroup because register
-//     allocation is per 4 warps: 384 threads x 168 registers fill the SM) + 8 consumer warps (2x4), warp tile 64x32 = 8x4 DMMA tiles, 64 FP64
+//     allocation is per 4 warps) + 1 epilogue warpgroup + 8 consumer warps (2x4), warp tile 64x32 = 8x4 DMMA tiles, 64 FP64
 //     accumulators per thread;
 //   * both operand layouts per side (contiguous along M/N or along K), so NN/NT/TN/TT need
 //     no transposition pass;
@@ -20,7 +20,11 @@
 //     two have bit 2 set, which spreads a fragment load over all 32 banks in BOTH swizzled
 //     layouts (K-major: chunk = (k>>1)^(mn&7), half = k&1; MN-major: chunk = (mn>>1)^(k&7)),
 //     i.e. the minimum two wavefronts per 64-bit warp load;
-//   * epilogue straight from registers: alpha/beta, optional triangle mask (SYRK-style).
+//   * epilogue off the critical path: the consumers park the accumulators of a finished tile in
+//     TENSOR MEMORY (tcgen05.st, 128 KB per tile, two buffers = the SM's whole 256 KB) and start
+//     the next tile at once; four epilogue warps read them back (tcgen05.ld) and do the
+//     alpha/beta read-modify-write of C (optional triangle mask, SYRK-style) meanwhile.  In the
+//     rank-128..1024 updates of the factorisations the C round trip was 10-30% of a tile.
 // Algorithmic work: 2*m*n*k flops per call; HBM traffic ~ (m*k + k*n)*8*(reuse factor) +
 // m*n*8*(1 or 2) bytes, tensor-pipe bound for k >= 64.
 #include "la_internal.h"
@@ -73,11 +77,13 @@ namespace {
 constexpr int BM = 128, BN = 128, BK = 16, STAGES = 4;
 constexpr int CONSUMER_WARPS = 8;
 constexpr int PRODUCER_WARPS = 4;  // warps are allocated in groups of four
-constexpr int NTHREADS = (CONSUMER_WARPS + PRODUCER_WARPS) * 32;
+constexpr int EPILOGUE_WARPS = 4;  // one per tensor-memory lane quarter
+constexpr int NTHREADS = (CONSUMER_WARPS + PRODUCER_WARPS + EPILOGUE_WARPS) * 32;
+constexpr int TMEM_COLS = 512;     // 2 accumulator buffers x 2 consumer warps per quarter x 128
 constexpr int A_STAGE_BYTES = BM * BK * 8;  // 16 KB
 constexpr int B_STAGE_BYTES = BN * BK * 8;  // 16 KB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers, tmem*/;
 constexpr int GROUP_M = 16;  // tile rows per rasterisation group
 
 struct GemmParams {
@@ -99,6 +105,39 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c[0]), "+d"(c[1])
                : "d"(a), "d"(b));
+}
+
+// ---- tensor memory as a staging buffer for the accumulators (no tcgen05.mma involved: FP64
+// has no tcgen05 kind).  A warp may touch the 32 TMEM lanes of its quarter (warp index % 4);
+// lane l of the warp owns TMEM lane 32 * quarter + l, a 32x32b access moves one 32-bit column
+// per register.
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+#define LA_R8(v, o) "r"(v[o]), "r"(v[o + 1]), "r"(v[o + 2]), "r"(v[o + 3]), "r"(v[o + 4]), "r"(v[o + 5]), "r"(v[o + 6]), "r"(v[o + 7])
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      :
+      : "r"(taddr), LA_R8(v, 0), LA_R8(v, 8), LA_R8(v, 16), LA_R8(v, 24)
+      : "memory");
+}
+#undef LA_R8
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
 // byte offset of element (mn, k) inside one operand stage
@@ -182,6 +221,9 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = (uint64_t*)(smem + STAGES * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* acc_full = empty_bar + STAGES;   // [2] accumulators of a tile are in tensor memory
+  uint64_t* acc_empty = acc_full + 2;        // [2] the epilogue has read them back
+  uint32_t* tmem_ptr = (uint32_t*)(acc_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -189,18 +231,112 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], CONSUMER_WARPS);
     }
+    for (int a = 0; a < 2; a++) {
+      mbar_init(&acc_full[a], CONSUMER_WARPS);
+      mbar_init(&acc_empty[a], EPILOGUE_WARPS);
+    }
     mbar_fence_init();
   }
+  if (warp == CONSUMER_WARPS + 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_ptr)),
+                 "n"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
   __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
 
   const int num_tiles = p.num_tiles;
   const int kblocks = (int)((p.k + BK - 1) / BK);
 
-  if (warp >= CONSUMER_WARPS) {
+  if (warp >= CONSUMER_WARPS + PRODUCER_WARPS) {
+    // ===================== epilogue warps: tensor memory -> alpha/beta -> C ===============
+    // They run one tile behind the consumers, so the read-modify-write of C (an HBM round trip
+    // per tile that nothing else can hide in a short-k product) overlaps the next main loop.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
+    const int q = warp & 3;
+    const int gid = lane >> 2, tig = lane & 3;
+    const bool beta_zero = p.beta == 0.0, beta_one = p.beta == 1.0;
+    int abuf = 0;
+    uint32_t aphase = 0;
+    for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
+      const int t = w % num_tiles, split = w / num_tiles;
+      int tm, tn;
+      tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+      if (!tile_active(p, tm, tn)) continue;
+      mbar_wait(&acc_full[abuf], aphase);
+      tc_fence_after();
+      // 16 chunks (2 consumer warps x 8 columns of C each), rolled: this code runs beside the
+      // main loop and must stay small in registers and instructions.
+      //  * beta == 1 (every trailing update of the factorisations): C += alpha * acc is sent
+      //    to the L2 as fire-and-forget red.global.add.f64 — one rounding, the same result as
+      //    the load / fma / store sequence, every element is touched once so the order does not
+      //    matter, and no load latency is exposed at all;
+      //  * otherwise the 8 loads of a column are issued together, then the stores.
+#pragma unroll 1
+      for (int n = 0; n < 16; n++) {
+        const int cw = q + 4 * (n >> 3);          // the consumer warp whose fragment this is
+        const int jc = n & 7;                     // jc = 2 * j + c
+        const int64_t row_base = (int64_t)tm * BM + (cw & 1) * 64 + gid;
+        const int64_t col = (int64_t)tn * BN + (cw >> 1) * 32 + 2 * tig + (jc >> 1) * 8 + (jc & 1);
+        uint32_t v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + abuf * 256 + n * 16, v);
+        if (col >= p.n) continue;
+        if (p.ksplit > 1) {  // raw partial sums; alpha/beta are applied by the reduction pass
+          double* Pcol = p.partial + ((int64_t)split * p.n + col) * p.ld_part;
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int64_t row = row_base + i * 8;
+            if (row < p.m) Pcol[row] = __hiloint2double((int)v[2 * i + 1], (int)v[2 * i]);
+          }
+          continue;
+        }
+        double* Ccol = p.C + col * p.ldc;
+        if (beta_one) {
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int64_t row = row_base + i * 8;
+            const int64_t mrow = p.zmode ? (row >> 1) : row;
+            if (row >= p.m || (p.tri == TriLower && mrow < col) || (p.tri == TriUpper && mrow > col))
+              continue;
+            const double r = p.alpha * __hiloint2double((int)v[2 * i + 1], (int)v[2 * i]);
+            if (p.herm_diag && mrow == col && (row & 1)) { Ccol[row] = 0.0; continue; }
+            asm volatile("red.global.add.f64 [%0], %1;" ::"l"(Ccol + row), "d"(r) : "memory");
+          }
+          continue;
+        }
+        bool act[8];
+        double cin[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          const int64_t row = row_base + i * 8;
+          const int64_t mrow = p.zmode ? (row >> 1) : row;
+          act[i] = row < p.m && !(p.tri == TriLower && mrow < col) &&
+                   !(p.tri == TriUpper && mrow > col);
+          cin[i] = (act[i] && !beta_zero) ? __ldcg(Ccol + row) : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          if (!act[i]) continue;
+          const int64_t row = row_base + i * 8;
+          double r = p.alpha * __hiloint2double((int)v[2 * i + 1], (int)v[2 * i]);
+          if (!beta_zero) r = fma(p.beta, cin[i], r);
+          if (p.herm_diag && (p.zmode ? (row >> 1) : row) == col && (row & 1)) r = 0.0;
+          Ccol[row] = r;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[abuf]);
+      if (++abuf == 2) { abuf = 0; aphase ^= 1; }
+    }
+  } else if (warp >= CONSUMER_WARPS) {
     // ===================== TMA producer (one elected lane of the producer warpgroup) =======
     // The producer warpgroup hands registers to the consumers.  Its own code must then fit in
-    // what it keeps (a larger footprint silently corrupts other warps' registers), hence the
-    // generous 56 and the rolled issue loops below.
+    // what it keeps, hence the generous 56 and the rolled issue loops below.
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (warp == CONSUMER_WARPS && lane == 0) {
       tma_prefetch_desc(&tmA);
@@ -238,109 +374,99 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       }
     }
-    return;
-  }
+  } else {
+    // ===================== DMMA consumers =====================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 184;");
+    const int gid = lane >> 2, tig = lane & 3;
+    const int wm = warp & 1, wn = warp >> 1;     // 2 x 4 warps -> 64 x 32 warp tiles
+    const int kslot = (tig & 1) + 4 * (tig >> 1);  // + kstep(ks) = {0, 2, 8, 10}
+    int stage = 0;
+    uint32_t phase = 0;
+    int abuf = 0;
+    uint32_t aphase = 0;
+    const bool beta_zero = p.beta == 0.0;
+    // this warp's slot in tensor memory: lane quarter warp % 4, columns (warp / 4) * 128
+    const uint32_t tslot = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 128;
 
-  // ===================== DMMA consumers =====================
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
-  const int gid = lane >> 2, tig = lane & 3;
-  const int wm = warp & 1, wn = warp >> 1;     // 2 x 4 warps -> 64 x 32 warp tiles
-  const int kslot = (tig & 1) + 4 * (tig >> 1);  // + kstep(ks) = {0, 2, 8, 10}
-  int stage = 0;
-  uint32_t phase = 0;
-  const bool beta_zero = p.beta == 0.0;
+    for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
+      const int t = w % num_tiles, split = w / num_tiles;
+      int tm, tn;
+      tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+      if (!tile_active(p, tm, tn)) continue;
+      const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
 
-  for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
-    const int t = w % num_tiles, split = w / num_tiles;
-    int tm, tn;
-    tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
-    if (!tile_active(p, tm, tn)) continue;
-    const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
-
-    if (!beta_zero && p.ksplit == 1) {
-      // pull the C tile into L2 while the main loop runs: thread t covers column t/2, four
-      // 128-byte lines of its 128 rows
-      const int64_t col = (int64_t)tn * BN + (threadIdx.x >> 1);
-      if (col < p.n) {
-        const double* cp = p.C + col * p.ldc + (int64_t)tm * BM + (threadIdx.x & 1) * 64;
+      if (!beta_zero && p.ksplit == 1) {
+        // pull the C tile into L2 while the main loop runs: thread t covers column t/2, four
+        // 128-byte lines of its 128 rows
+        const int64_t col = (int64_t)tn * BN + (threadIdx.x >> 1);
+        if (col < p.n) {
+          const double* cp = p.C + col * p.ldc + (int64_t)tm * BM + (threadIdx.x & 1) * 64;
 #pragma unroll
-        for (int q = 0; q < 4; q++)
-          if ((int64_t)tm * BM + (threadIdx.x & 1) * 64 + q * 16 < p.m)
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(cp + q * 16));
+          for (int qq = 0; qq < 4; qq++)
+            if ((int64_t)tm * BM + (threadIdx.x & 1) * 64 + qq * 16 < p.m)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(cp + qq * 16));
+        }
       }
-    }
-    double acc[8][4][2];
+      double acc[8][4][2];
 #pragma unroll
-    for (int i = 0; i < 8; i++)
+      for (int i = 0; i < 8; i++)
 #pragma unroll
-      for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    for (int kb = kb0; kb < kb1; kb++) {
-      mbar_wait(&full_bar[stage], phase);
-      const unsigned char* sA = smem + stage * STAGE_BYTES;
-      const unsigned char* sB = sA + A_STAGE_BYTES;
+      for (int kb = kb0; kb < kb1; kb++) {
+        mbar_wait(&full_bar[stage], phase);
+        const unsigned char* sA = smem + stage * STAGE_BYTES;
+        const unsigned char* sB = sA + A_STAGE_BYTES;
 #pragma unroll
-      for (int ks = 0; ks < 4; ks++) {
-        const int kk = kslot + 2 * (ks & 1) + 8 * (ks >> 1);
-        double a[8], b[4];
+        for (int ks = 0; ks < 4; ks++) {
+          const int kk = kslot + 2 * (ks & 1) + 8 * (ks >> 1);
+          double a[8], b[4];
 #pragma unroll
-        for (int i = 0; i < 8; i++)
-          a[i] = *reinterpret_cast<const double*>(sA + frag_off<A_MN>(wm * 64 + i * 8 + gid, kk));
+          for (int i = 0; i < 8; i++)
+            a[i] = *reinterpret_cast<const double*>(sA + frag_off<A_MN>(wm * 64 + i * 8 + gid, kk));
 #pragma unroll
-        for (int j = 0; j < 4; j++)
-          b[j] = *reinterpret_cast<const double*>(sB + frag_off<B_MN>(wn * 32 + j * 8 + gid, kk));
+          for (int j = 0; j < 4; j++)
+            b[j] = *reinterpret_cast<const double*>(sB + frag_off<B_MN>(wn * 32 + j * 8 + gid, kk));
 #pragma unroll
-        for (int i = 0; i < 8; i++)
+          for (int i = 0; i < 8; i++)
 #pragma unroll
-          for (int j = 0; j < 4; j++) dmma884(acc[i][j], a[i], b[j]);
+            for (int j = 0; j < 4; j++) dmma884(acc[i][j], a[i], b[j]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty_bar[stage]);
-      if (++stage == STAGES) { stage = 0; phase ^= 1; }
-    }
 
-    // ---- epilogue: C(row, col..col+1) for row = gid, col = 2*tig of each 8x8 tile
-    const int64_t row_base = (int64_t)tm * BM + wm * 64 + gid;
-    const int64_t col_base = (int64_t)tn * BN + wn * 32 + 2 * tig;
+      // ---- hand the accumulators to the epilogue warps through tensor memory: column
+      // (2 * j + c) * 16 + 2 * i (+1) of this warp's slot holds the low (high) word of
+      // acc[i][j][c], so that a 16-column read returns the 8 rows of one column of C
+      mbar_wait(&acc_empty[abuf], aphase ^ 1);
+      tc_fence_after();
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
+      for (int j = 0; j < 4; j++) {
+        uint32_t v[32];
 #pragma unroll
-      for (int c = 0; c < 2; c++) {
-        const int64_t col = col_base + j * 8 + c;
-        if (col >= p.n) continue;
-        if (p.ksplit > 1) {  // raw partial sums; alpha/beta are applied by the reduction pass
-          double* Pcol = p.partial + ((int64_t)split * p.n + col) * p.ld_part;
+        for (int c = 0; c < 2; c++)
 #pragma unroll
           for (int i = 0; i < 8; i++) {
-            const int64_t row = row_base + i * 8;
-            if (row < p.m) Pcol[row] = acc[i][j][c];
+            v[(c * 8 + i) * 2] = (uint32_t)__double2loint(acc[i][j][c]);
+            v[(c * 8 + i) * 2 + 1] = (uint32_t)__double2hiint(acc[i][j][c]);
           }
-          continue;
-        }
-        double* Ccol = p.C + col * p.ldc;
-        // all loads of a column first (independent, in flight together), then the stores: a
-        // load-store chain per element would expose one memory round trip per row
-        bool act[8];
-        double cin[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          const int64_t row = row_base + i * 8;
-          const int64_t mrow = p.zmode ? (row >> 1) : row;
-          act[i] = row < p.m && !(p.tri == TriLower && mrow < col) &&
-                   !(p.tri == TriUpper && mrow > col);
-          cin[i] = (act[i] && !beta_zero) ? __ldcg(Ccol + row) : 0.0;
-        }
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-          if (!act[i]) continue;
-          const int64_t row = row_base + i * 8;
-          double v = p.alpha * acc[i][j][c];
-          if (!beta_zero) v = fma(p.beta, cin[i], v);
-          if (p.herm_diag && (p.zmode ? (row >> 1) : row) == col && (row & 1)) v = 0.0;
-          Ccol[row] = v;
-        }
+        tmem_st32(tslot + abuf * 256 + j * 32, v);
       }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_full[abuf]);
+      if (++abuf == 2) { abuf = 0; aphase ^= 1; }
     }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == CONSUMER_WARPS + 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "n"(TMEM_COLS)
+                 : "memory");
   }
 }
 

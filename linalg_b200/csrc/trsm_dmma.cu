@@ -19,7 +19,7 @@ namespace la {
 namespace {
 
 constexpr int TB = 8;            // block order
-constexpr int TNB = 64;          // largest triangle
+constexpr int TNB = 64;          // largest triangle (the staging code assumes 64)
 constexpr int TLD = TNB + 1;     // shared-memory pitch
 constexpr int TWARPS = 4;        // warps per CTA
 constexpr int TGROUPS = 2;       // 8-vector groups per warp (independent chains)
@@ -43,18 +43,36 @@ trsm_dmma_kernel(int upper, int unit, int na, int64_t nvec, double alpha,
   const int gid = lane >> 2, tig = lane & 3;
   const int nblk = (na + TB - 1) / TB;
   const int npad = nblk * TB;
-  // ---- stage U (padded with the identity), negated
-  for (int idx = tid; idx < npad * npad; idx += blockDim.x) {
-    const int i = idx / npad, j = idx % npad;
-    double v = 0.0;
-    if (i < na && j < na) {
-      const bool stored = upper ? (i <= j) : (i >= j);
-      if (stored) v = (i == j && unit) ? 1.0 : U[i * ur + j * uc];
-    } else if (i == j) {
-      v = 1.0;
+  // ---- stage U (padded with the identity), negated.  All global loads of a thread are issued
+  // before the first shared-memory store (one memory round trip instead of one per element),
+  // and the fast thread index follows the contiguous direction of the stored matrix.
+  {
+    constexpr int PER = TNB * TNB / (TWARPS * 32);
+    const bool row_contig = (uc == 1);
+    double v[PER];
+#pragma unroll
+    for (int q = 0; q < PER; q++) {
+      const int idx = tid + q * (TWARPS * 32);
+      const int fa = idx & (TNB - 1), sl = idx >> 6;   // TNB == 64
+      const int i = row_contig ? sl : fa, j = row_contig ? fa : sl;
+      double x = (i == j) ? 1.0 : 0.0;
+      if (i < na && j < na) {
+        const bool stored = upper ? (i <= j) : (i >= j);
+        x = 0.0;
+        if (stored) x = (i == j && unit) ? 1.0 : U[i * ur + j * uc];
+      }
+      v[q] = x;
     }
-    Us[i * TLD + j] = -v;
-    if (i / TB == j / TB) Dg[(i / TB) * (TB * TB) + (i % TB) * TB + (j % TB)] = v;
+#pragma unroll
+    for (int q = 0; q < PER; q++) {
+      const int idx = tid + q * (TWARPS * 32);
+      const int fa = idx & (TNB - 1), sl = idx >> 6;
+      const int i = row_contig ? sl : fa, j = row_contig ? fa : sl;
+      if (i < npad && j < npad) {
+        Us[i * TLD + j] = -v[q];
+        if (i / TB == j / TB) Dg[(i / TB) * (TB * TB) + (i % TB) * TB + (j % TB)] = v[q];
+      }
+    }
   }
   __syncthreads();
   // ---- invert the diagonal blocks: thread (b, c) computes column c of inv(U_bb)
