@@ -241,11 +241,25 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       side->sm_limit = side_sms;
       getrf_rec<T>(*side, m, A, lda, d_ipiv, d_info, j1, jb1, plan);
       LA_CUDA_CHECK(cudaEventRecord(side->ev[0], side->stream));
+      // The trailing update runs on the SMs the side stream leaves free — but only for as long
+      // as the panel is expected to take (a model of the panel's duration, biased long: an
+      // update that outlasts the panel merely keeps a few SMs idle, one that ends early stalls
+      // the whole device); the rest of it is launched on all SMs once the panel is done.
+      const int64_t rest = nr - jb1;
+      static const double model_scale = getenv("LA_B200_LU_MODEL") ? atof(getenv("LA_B200_LU_MODEL")) : 1.25;
+      const double panel_ms = model_scale * (1.6 + 1.5 * (double)(m - j1) / 16384.0);
+      const double flop_per_ms = 31.0e9 * (double)(ctx.sm_count - side_sms) / 148.0;
+      int64_t c1 = (int64_t)(panel_ms * flop_per_ms / (2.0 * (double)mr * (double)jb));
+      c1 = round_up(c1 > 0 ? c1 : 1, (int64_t)128);
+      if (c1 + 1024 >= rest) c1 = rest;
       ctx.sm_limit = ctx.sm_count - side_sms;
-      gemm<T>(ctx, OpN, OpN, mr, nr - jb1, jb, from_real<T>(-1.0), A21, lda, A12 + jb1 * lda, lda,
+      gemm<T>(ctx, OpN, OpN, mr, c1, jb, from_real<T>(-1.0), A21, lda, A12 + jb1 * lda, lda,
               one<T>(), A22 + jb1 * lda, lda);
       ctx.sm_limit = 0;
       LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, side->ev[0], 0));
+      if (c1 < rest)
+        gemm<T>(ctx, OpN, OpN, mr, rest - c1, jb, from_real<T>(-1.0), A21, lda,
+                A12 + (jb1 + c1) * lda, lda, one<T>(), A22 + (jb1 + c1) * lda, lda);
       panel_done = true;
     } else {
       gemm<T>(ctx, OpN, OpN, mr, nr, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
