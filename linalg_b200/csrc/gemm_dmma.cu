@@ -30,6 +30,7 @@
 #include "la_internal.h"
 #include "tma_utils.cuh"
 #include <mutex>
+#include <type_traits>
 
 namespace la {
 
@@ -99,6 +100,7 @@ struct GemmParams {
   int64_t ld_part;
   int zmode;      // 1: rows are interleaved (re, im) parts of a complex matrix (gemm_z.cu)
   int herm_diag;  // zmode only: store 0 in the imaginary part of the diagonal
+  int use_red;    // beta == 1: accumulate into C with red.global.add instead of load/fma/store
 };
 
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
@@ -138,6 +140,26 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
       : "r"(taddr)
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Fragment loads are explicit ld.shared with a 32-bit address and an immediate offset: through
+// a generic pointer the compiler could not tell that the staged tiles live in shared memory and
+// emitted generic 64-bit loads with two integer adds each.
+template <int I, int N, typename F>
+__device__ __forceinline__ void static_for_impl(F&& f) {
+  if constexpr (I < N) {
+    f(std::integral_constant<int, I>{});
+    static_for_impl<I + 1, N>(f);
+  }
+}
+template <typename F> __device__ __forceinline__ void static_for4(F&& f) { static_for_impl<0, 4>(f); }
+template <typename F> __device__ __forceinline__ void static_for8(F&& f) { static_for_impl<0, 8>(f); }
+
+template <int IMM>
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(addr), "n"(IMM));
+  return v;
 }
 
 // byte offset of element (mn, k) inside one operand stage
@@ -237,7 +259,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     mbar_fence_init();
   }
-  if (warp == CONSUMER_WARPS + 1) {
+  if (warp == CONSUMER_WARPS + 2) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                      smem_u32(tmem_ptr)),
                  "n"(TMEM_COLS)
@@ -259,7 +281,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
     const int q = warp & 3;
     const int gid = lane >> 2, tig = lane & 3;
-    const bool beta_zero = p.beta == 0.0, beta_one = p.beta == 1.0;
+    const bool beta_zero = p.beta == 0.0, beta_one = p.beta == 1.0 && p.use_red;
     int abuf = 0;
     uint32_t aphase = 0;
     for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
@@ -338,7 +360,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // The producer warpgroup hands registers to the consumers.  Its own code must then fit in
     // what it keeps, hence the generous 56 and the rolled issue loops below.
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
-    if (warp == CONSUMER_WARPS && lane == 0) {
+    if (warp == CONSUMER_WARPS + 1 && lane == 0) {
       tma_prefetch_desc(&tmA);
       tma_prefetch_desc(&tmB);
       int stage = 0;
@@ -385,6 +407,19 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     int abuf = 0;
     uint32_t aphase = 0;
     const bool beta_zero = p.beta == 0.0;
+    // Per-thread parts of the fragment addresses.  With mn = w*.. + 8*i + gid and
+    // k = kslot + {0, 2, 8, 10}[ks], frag_off() splits into a compile-time part (i, ks) and a
+    // thread part that only depends on the parities the 128-byte swizzle mixes in:
+    //   MN-major: (i & 1, ks & 1)      K-major: ks
+    uint32_t offA[4], offB[4];
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+      if (A_MN) offA[v] = frag_off<true>(wm * 64 + (v >> 1) * 8 + gid, kslot + 2 * (v & 1));
+      else      offA[v] = frag_off<false>(wm * 64 + gid, kslot + 2 * (v & 1) + 8 * (v >> 1));
+      if (B_MN) offB[v] = frag_off<true>(wn * 32 + (v >> 1) * 8 + gid, kslot + 2 * (v & 1));
+      else      offB[v] = frag_off<false>(wn * 32 + gid, kslot + 2 * (v & 1) + 8 * (v >> 1));
+    }
+    const uint32_t smem_base = smem_u32(smem);
     // this warp's slot in tensor memory: lane quarter warp % 4, columns (warp / 4) * 128
     const uint32_t tslot = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 128;
 
@@ -415,23 +450,36 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
       for (int kb = kb0; kb < kb1; kb++) {
         mbar_wait(&full_bar[stage], phase);
-        const unsigned char* sA = smem + stage * STAGE_BYTES;
-        const unsigned char* sB = sA + A_STAGE_BYTES;
-#pragma unroll
-        for (int ks = 0; ks < 4; ks++) {
-          const int kk = kslot + 2 * (ks & 1) + 8 * (ks >> 1);
+        const uint32_t sA = smem_base + stage * STAGE_BYTES;
+        const uint32_t sB = sA + A_STAGE_BYTES;
+        static_for4([&](auto KS) {
+          constexpr int ks = decltype(KS)::value;
           double a[8], b[4];
-#pragma unroll
-          for (int i = 0; i < 8; i++)
-            a[i] = *reinterpret_cast<const double*>(sA + frag_off<A_MN>(wm * 64 + i * 8 + gid, kk));
-#pragma unroll
-          for (int j = 0; j < 4; j++)
-            b[j] = *reinterpret_cast<const double*>(sB + frag_off<B_MN>(wn * 32 + j * 8 + gid, kk));
+          static_for8([&](auto I) {
+            constexpr int i = decltype(I)::value;
+            // MN-major: k adds (2*(ks&1) + 8*(ks>>1)) * 128 bytes, the 8-row group i adds
+            // (i>>1) * 2048; K-major: row group i adds i * 8 * 128 bytes
+            if (A_MN) a[i] = lds_f64<(8 * (ks >> 1)) * 128 + (i >> 1) * (BK * 128)>(sA + offA[(i & 1) * 2 + (ks & 1)]);
+            else      a[i] = lds_f64<i * 8 * 128>(sA + offA[ks]);
+          });
+          static_for4([&](auto J) {
+            constexpr int j = decltype(J)::value;
+            if (B_MN) b[j] = lds_f64<(8 * (ks >> 1)) * 128 + (j >> 1) * (BK * 128)>(sB + offB[(j & 1) * 2 + (ks & 1)]);
+            else      b[j] = lds_f64<j * 8 * 128>(sB + offB[ks]);
+          });
 #pragma unroll
           for (int i = 0; i < 8; i++)
 #pragma unroll
             for (int j = 0; j < 4; j++) dmma884(acc[i][j], a[i], b[j]);
-        }
+        });
+        // The stage may only be handed back once every fragment load of this warp has been
+        // PERFORMED, not merely issued: ptxas schedules the last loads of the k-block right
+        // before the arrive and the DMMAs that consume them after it, and the refill by the
+        // TMA unit (async proxy) was observed to overtake those loads (wrong A fragments in the
+        // last k-step of a stage, in the warps that share a scheduler with the producer).
+        // The proxy fence orders this warp's generic-proxy reads before the async-proxy write
+        // that the arrive enables.
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -463,7 +511,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == CONSUMER_WARPS + 1) {
+  if (warp == CONSUMER_WARPS + 2) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
                  "n"(TMEM_COLS)
                  : "memory");
@@ -545,6 +593,8 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
   p.zmode = zmode;
   p.herm_diag = herm_diag ? 1 : 0;
+  static const bool no_red = getenv("LA_B200_NO_RED") != nullptr;
+  p.use_red = no_red ? 0 : 1;
   if (zmode) p.num_tiles = p.tiles_m * p.tiles_n;
   else if (tri == TriLower) p.num_tiles = tri_tile_count(p.tiles_m, p.tiles_n);
   else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
