@@ -39,7 +39,8 @@ sys.path.insert(0, str(ROOT))
 
 FP64_DMMA_PEAK_TFLOPS = 37.0   # measured: tools/microbench/peak_fp64.cu on this pool's B200
 CPU_SAMPLE_N = 8192
-DGEMM_DRAM_BYTES_PER_LAUNCH = 85.27e9   # N = 16384, measured with ncu (see profiles/README.md)
+DGEMM_KCHUNK = 4096                     # the library runs long-k products as k-chunks (gemm_dmma.cu)
+DGEMM_DRAM_BYTES_PER_LAUNCH = 18.82e9   # one k-chunk launch at N = 16384: 16.69 GB read + 2.14 GB written (ncu)
 WORKLOAD = "dgemm N={n} NoTrans/NoTrans alpha=1 beta=1 on zeroed C (Matrix#*)"
 
 
@@ -335,8 +336,10 @@ def run_ours(args):
         barrier()
     ms = allmax(e0.elapsed_time(e1) / args.steps)
     value = 2.0 * n ** 3 / (ms * 1e-3) * 1e-12
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
-    achieved = 2.0 * n * n * nc / (kern_ms * 1e-3) * 1e-12
+    # one dev.gemm call = `launches` launches of the same kernel (k-chunks of 4096 when k >= 8192)
+    launches = -(-n // DGEMM_KCHUNK) if (n >= 2 * DGEMM_KCHUNK and n * nc >= 4096 * 4096) else 1
+    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in kev])) / launches
+    achieved = 2.0 * n * nc * (n / launches) / (kern_ms * 1e-3) * 1e-12
 
     # spot check: three columns of C against numpy in float64
     cols = [0, nc // 2, nc - 1]
@@ -398,14 +401,15 @@ def run_ours(args):
             "config": {"workload": WORKLOAD.format(n=n),
                        "shard": f"block columns of B and C over {world} rank(s), A replicated",
                        "l2": "operands (3 x 2 GiB) exceed L2; no flush needed"},
-            "e2e": e2e, "gpu_launches": args.steps, "clocks": clk.summary(),
+            "e2e": e2e, "gpu_launches": args.steps * launches, "clocks": clk.summary(),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": FP64_DMMA_PEAK_TFLOPS,
                          "unit": "TFLOP/s", "frac": achieved / FP64_DMMA_PEAK_TFLOPS,
                          "traffic": DGEMM_DRAM_BYTES_PER_LAUNCH if (world == 1 and n == 16384) else None,
-                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, "
-                                           "ncu --set full (profiles/r1_dgemm16384_ncu_raw.csv)",
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu "
+                                           "metrics pass (profiles/r1e_dgemm16384_chunk_launches.csv); "
+                                           "algorithmic bytes per launch 3.22e9 (A, B chunk once, C read+write)",
                          "kernel": "dgemm_dmma_kernel<A_MN=1,B_MN=0>",
-                         "kernel_ms": kern_ms,
+                         "kernel_ms": kern_ms, "launches_per_step": launches,
                          "peak_source": "FP64 DMMA (mma.sync m8n8k4) register-resident peak measured "
                                         "by tools/microbench/peak_fp64.cu on this pool; "
                                         "MEASURED_PEAKS.json has no FP64 figure; nominal 37.2 at 1965 MHz",

@@ -567,6 +567,27 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   if (m * n * k < (int64_t)64 * 64 * 64) return false;
   if (m > (int64_t)1 << 30 || n > (int64_t)1 << 30 || k > (int64_t)1 << 30) return false;
   const bool a_mn = (ta == OpN), b_mn = (tb != OpN);
+  // Long-k products of large matrices run as a sequence of k-chunks accumulating into C.  With
+  // the whole k range per tile, a wave of 148 tiles streams ~400 MB of operands and the CTAs of
+  // a wave drift apart in k, so the 126 MB L2 caught only ~3/4 of the operand re-reads (ncu:
+  // 108 GB of DRAM traffic per N = 16384 product against 8.6 GB algorithmic).  A 4096-wide
+  // chunk keeps a wave's operands (~100 MB) and the A panel of a tile-row group resident, and
+  // the extra passes over C cost nothing now that the epilogue is off the critical path.
+  constexpr int64_t KCHUNK = 4096;
+  if (k >= 2 * KCHUNK && (double)m * (double)n >= 4096.0 * 4096.0) {
+    for (int64_t l0 = 0; l0 < k; l0 += KCHUNK) {
+      const int64_t kc = KCHUNK < k - l0 ? KCHUNK : k - l0;
+      const double* Ac = a_mn ? A + l0 * lda : A + l0;
+      const double* Bc = b_mn ? B + l0 * ldb : B + l0;
+      if (!gemm_dmma_f64_ex(ctx, ta, tb, m, n, kc, alpha, Ac, lda, Bc, ldb, l0 == 0 ? beta : 1.0, C,
+                            ldc, tri, zmode, herm_diag)) {
+        if (l0 == 0) return false;
+        fprintf(stderr, "la_b200: internal error: k-chunked GEMM fell back after the first chunk\n");
+        abort();
+      }
+    }
+    return true;
+  }
   CUtensorMap tmA, tmB;
   // operand A as op(A) (m x k): stored m x k (lda) when ta == N, else k x m
   if (a_mn) {
