@@ -172,17 +172,19 @@ struct KeyAt<T, JBM, JBM> {
   __device__ __forceinline__ static ukey get(int, const T (&)[JBM]) { return 0; }
 };
 
-// LU with partial pivoting of an m x jb panel (m >= jb, jb <= MaxJb<T>), one row per thread,
-// rows in REGISTERS for the whole launch (the elimination would otherwise be bound by the
-// shared-memory bandwidth of the few SMs that hold the panel).
-template <typename T>
+// LU with partial pivoting of an m x jb panel (m >= jb, jb <= JBM), R rows per thread (rows
+// rs + r * LU_NT + tid of the CTA's slice of R * LU_NT rows), rows in REGISTERS for the whole
+// launch (the elimination would otherwise be bound by the shared-memory bandwidth of the few SMs
+// that hold the panel).  R * JBM is constant (MaxJb<T>): the common case is one row of 32 columns
+// per thread; panels taller than sm_count * LU_NT rows trade leaf width for rows per thread.
+template <typename T, int R>
 __global__ void __launch_bounds__(LU_NT)
 lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__ ipiv, int row0,
                 int* info, LuExchange* xch, int rpc, unsigned seq_base) {
-  using R = typename Traits<T>::real;
+  using Real = typename Traits<T>::real;
   constexpr int W = Words<T>::N;
   constexpr int NW = LU_NT / 32;
-  constexpr int JBM = MaxJb<T>::N;
+  constexpr int JBM = MaxJb<T>::N / R;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int G = gridDim.x;
   T* cand = reinterpret_cast<T*>(smem_raw);      // cand[w * JBM + c]: each warp's best row
@@ -193,15 +195,19 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   __shared__ int s_pi[2];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int rs = blockIdx.x * rpc;                 // rpc == LU_NT: one row per thread
-  const int gr = rs + tid;                         // this thread's row
-  const bool have_row = gr < m;
+  const int rs = blockIdx.x * rpc;                 // rpc == R * LU_NT rows per CTA
+  const int gr0 = rs + tid;                        // this thread's rows: gr0 + r * LU_NT
 
-  T a[JBM];
+  T a[R][JBM];
+  ukey nk[R];
 #pragma unroll
-  for (int c = 0; c < JBM; c++)
-    a[c] = (have_row && c < jb) ? A[(int64_t)gr + (int64_t)c * lda] : zero<T>();
-  ukey nk = have_row ? key_of((double)abs1(a[0])) : 0;
+  for (int r = 0; r < R; r++) {
+    const int gr = gr0 + r * LU_NT;
+#pragma unroll
+    for (int c = 0; c < JBM; c++)
+      a[r][c] = (gr < m && c < jb) ? A[(int64_t)gr + (int64_t)c * lda] : zero<T>();
+    nk[r] = gr < m ? key_of((double)abs1(a[r][0])) : 0;
+  }
 
   // Two block barriers per column.  Everything the barriers separate is double-buffered by
   // column parity (prow2, rj2, s_pi, the exchange packets) or is only touched by warp 0 between
@@ -212,19 +218,29 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
     const unsigned seq = seq_base + (unsigned)j + 1u;
     T* prow = prow2 + par * JBM;
     T* rj = rj2 + par * JBM;
-    const bool own_j = j >= rs && j < rs + LU_NT;
+    const bool own_j = j >= rs && j < rs + R * LU_NT;
     TRACE(0);
     // ---- arg-max of column j over the rows gr >= j: per warp, then across warps
-    ukey bv = nk;
-    int bi = (have_row && gr >= j) ? gr : 0x7fffffff;
-    warp_argmax_redux(bv, bi);
-    if (bi == gr && have_row) {     // this lane owns the warp's best row: stage its contents
+    ukey bv = 0;
+    int bi = 0x7fffffff;
 #pragma unroll
-      for (int c = 0; c < JBM; c++) cand[warp * JBM + c] = a[c];
+    for (int r = 0; r < R; r++) {   // this thread's best row (rows ascend with r: ties keep the first)
+      const int gr = gr0 + r * LU_NT;
+      if (gr < m && gr >= j && (bi == 0x7fffffff || nk[r] > bv)) { bv = nk[r]; bi = gr; }
     }
-    if (gr == j) {                  // this lane owns row j
+    const int mine = bi;
+    warp_argmax_redux(bv, bi);
 #pragma unroll
-      for (int c = 0; c < JBM; c++) rj[c] = a[c];
+    for (int r = 0; r < R; r++) {
+      const int gr = gr0 + r * LU_NT;
+      if (gr == bi && mine == bi && gr < m) {   // this lane owns the warp's best row: stage it
+#pragma unroll
+        for (int c = 0; c < JBM; c++) cand[warp * JBM + c] = a[r][c];
+      }
+      if (gr == j) {                            // this lane owns row j
+#pragma unroll
+        for (int c = 0; c < JBM; c++) rj[c] = a[r][c];
+      }
     }
     if (lane == 0) { sval[warp] = bv; sidx[warp] = bi; }
     __syncthreads();
@@ -285,31 +301,43 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
     const int pi = s_pi[par];
     // ---- row interchange j <-> pi in the registers of the two owners
     if (pi != j) {
-      if (gr == pi) {
 #pragma unroll
-        for (int c = 0; c < JBM; c++) a[c] = rj[c];
-      } else if (gr == j) {
+      for (int r = 0; r < R; r++) {
+        const int gr = gr0 + r * LU_NT;
+        if (gr == pi) {
 #pragma unroll
-        for (int c = 0; c < JBM; c++) a[c] = prow[c];
+          for (int c = 0; c < JBM; c++) a[r][c] = rj[c];
+        } else if (gr == j) {
+#pragma unroll
+          for (int c = 0; c < JBM; c++) a[r][c] = prow[c];
+        }
       }
     }
     // ---- eliminate: scale column j, rank-1 update, key of the next column's entry
     const T pivot = prow[j];
     const bool zero_pivot = is_zero(pivot);
     if (zero_pivot && blockIdx.x == 0 && tid == 0) atomicCAS(info, 0, row0 + j + 1);
-    const bool use_recip = (R)abs1(pivot) >= sfmin<R>();
+    const bool use_recip = (Real)abs1(pivot) >= sfmin<Real>();
     const T rinv = zero_pivot ? zero<T>() : recip(pivot);
-    nk = 0;
-    if (have_row && gr > j) {
-      if (!zero_pivot) Dispatch<T, JBM, 0>::run(j, a, prow, rinv, pivot, use_recip, nk);
-      else nk = KeyAt<T, JBM, 0>::get(j + 1, a);   // as ?getf2: no scaling, update is a no-op
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int gr = gr0 + r * LU_NT;
+      nk[r] = 0;
+      if (gr < m && gr > j) {
+        if (!zero_pivot) Dispatch<T, JBM, 0>::run(j, a[r], prow, rinv, pivot, use_recip, nk[r]);
+        else nk[r] = KeyAt<T, JBM, 0>::get(j + 1, a[r]);   // as ?getf2: no scaling, no update
+      }
     }
     TRACE(5);
   }
-  if (have_row) {
 #pragma unroll
-    for (int c = 0; c < JBM; c++)
-      if (c < jb) A[(int64_t)gr + (int64_t)c * lda] = a[c];
+  for (int r = 0; r < R; r++) {
+    const int gr = gr0 + r * LU_NT;
+    if (gr < m) {
+#pragma unroll
+      for (int c = 0; c < JBM; c++)
+        if (c < jb) A[(int64_t)gr + (int64_t)c * lda] = a[r][c];
+    }
   }
 }
 
@@ -346,41 +374,76 @@ void lu_panel_adopt_exchange(Context& ctx, void* device_mem, void* state_storage
 // Make sure the context owns its exchange area (allocates on first use).
 void lu_panel_prepare(Context& ctx) { (void)panel_state(ctx); }
 
-// Widest leaf the panel kernel takes for an m-row panel (0: the panel is too tall for one
-// cooperative launch with a row per thread).
-int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
-  const int64_t G = ceil_div(m, LU_NT);
-  if (G > ctx.sm_count || G > LU_MAX_CTAS) return 0;
-  return elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
+// Rows per thread needed for an m-row panel (a power of two; 0: too tall even for the narrowest
+// leaf).  One row per thread while the panel fits sm_count CTAs of LU_NT rows.
+static int lu_rows_per_thread(Context& ctx, int64_t m, int max_jb) {
+  const int64_t cap = ctx.sm_count < LU_MAX_CTAS ? ctx.sm_count : LU_MAX_CTAS;
+  for (int R = 1; R <= max_jb; R *= 2)
+    if (ceil_div(m, (int64_t)R * LU_NT) <= cap) return R;
+  return 0;
 }
 
-template <typename T>
-void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
-              int* d_info) {
+// Widest leaf the panel kernel takes for an m-row panel (0: the panel is too tall for one
+// cooperative launch: more than sm_count * LU_NT * MaxJb rows).
+int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
+  const int base = elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
+  const int R = lu_rows_per_thread(ctx, m, base);
+  return R ? base / R : 0;
+}
+
+template <typename T, int R>
+static void lu_panel_launch(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv,
+                            int64_t row0, int* d_info) {
   static bool attr = false;
   if (!attr) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T>,
+    LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T, R>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)LU_SMEM_TOTAL));
     attr = true;
   }
   LuPanelState* st = panel_state(ctx);
-  // one row per thread
-  const int64_t rpc = LU_NT;
+  constexpr int JBM = MaxJb<T>::N / R;
+  const int64_t rpc = (int64_t)R * LU_NT;
   const int64_t G = ceil_div(m, rpc);
-  if (G > LU_MAX_CTAS || G > ctx.sm_count || jb > MaxJb<T>::N) {
+  if (G > LU_MAX_CTAS || G > ctx.sm_count || jb > JBM) {
     fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
     abort();
   }
-  constexpr int JBM = MaxJb<T>::N;
   size_t smem = ((size_t)(LU_NT / 32) * JBM + 4 * (size_t)JBM) * sizeof(T) + 16;
   int mi = (int)m, row0i = (int)row0, rpci = (int)rpc;
   unsigned seq_base = st->seq;
   st->seq += 64;
   LuExchange* xch = st->xch;
   void* args[] = {&mi, &jb, &A, &lda, &ipiv, &row0i, &d_info, &xch, &rpci, &seq_base};
-  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lu_panel_kernel<T>, dim3((unsigned)G),
+  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lu_panel_kernel<T, R>, dim3((unsigned)G),
                                             dim3(LU_NT), args, smem, ctx.stream));
+}
+
+template <typename T>
+void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
+              int* d_info) {
+  constexpr int base = MaxJb<T>::N;
+  // the narrowest R that fits the rows AND still takes jb columns
+  int R = lu_rows_per_thread(ctx, m, base);
+  if (R == 0 || jb > base / R) {
+    fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
+    abort();
+  }
+  switch (R) {
+    case 1: lu_panel_launch<T, 1>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 2: lu_panel_launch<T, 2>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 4: lu_panel_launch<T, 4>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 8: lu_panel_launch<T, 8>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    default:
+      if constexpr (base >= 32) {
+        if (R == 16) { lu_panel_launch<T, 16>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
+        if (R == 32) { lu_panel_launch<T, 32>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
+      } else {
+        if (R == 16) { lu_panel_launch<T, 16>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
+      }
+      fprintf(stderr, "la_b200: internal error: LU panel rows-per-thread %d\n", R);
+      abort();
+  }
 }
 
 #ifdef LA_PANEL_TRACE

@@ -220,6 +220,24 @@ def test_getrf_matches_lapack(rng, dt, shape, product_abi, oracle_abi):
     assert checks.rel(lu - rlu, rlu) < 50 * max(shape) * _eps(dt)
 
 
+@pytest.mark.parametrize("dt,shape", [(np.float64, (100000, 40)), (np.float64, (200000, 24)),
+                                      (np.float32, (330000, 9)), (np.complex128, (90000, 20))])
+def test_getrf_tall_panels_take_several_rows_per_thread(rng, dt, shape, product_abi, oracle_abi):
+    # more rows than sm_count * 512: the leaf kernel holds 2, 4, ... rows per thread and narrows
+    # the leaf accordingly (lu_panel.cu); pivots and factors must still match LAPACK's
+    A = _rand(rng, shape, dt, -0.5)
+
+    def run():
+        a = la.GeneralMatrix(A)
+        ipiv = np.zeros(min(shape), dtype=np.int32)
+        la._lapack("getrf", a.letter, shape[0], shape[1], a.raw, shape[0], ipiv)
+        return a.raw, ipiv
+
+    (lu, ipiv), (rlu, ripiv) = _both(run, product_abi, oracle_abi)
+    assert checks.pivots_equal(ipiv, ripiv)[0], checks.pivots_equal(ipiv, ripiv)
+    assert checks.rel(lu - rlu, rlu) < 50 * shape[1] * _eps(dt)
+
+
 @pytest.mark.parametrize("dt", DTYPES, ids=IDS)
 def test_getrf_singular_and_ties(dt, product_abi, oracle_abi):
     # exactly singular: column 3 is zero after elimination -> info = 3, factorisation completes
