@@ -14,7 +14,7 @@ namespace la {
 // =========================================================================== LU
 template <typename T>
 void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
-                const int* d_ipiv);
+                const int* d_ipiv, bool reverse = false);
 // lu_panel.cu
 template <typename T>
 void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
@@ -131,7 +131,7 @@ constexpr int LASWP_MAX_MAP = 49152;     // rows the shared-memory index map can
 // `m` = number of rows of A (upper bound of the pivot indices); 0 = unknown (serial kernel).
 template <typename T>
 void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
-                const int* d_ipiv) {
+                const int* d_ipiv, bool reverse) {
   if (n <= 0 || k2 <= k1) return;
   static bool attr = false;
   if (!attr) {
@@ -141,12 +141,17 @@ void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k
   }
   Arena::Mark mk = ctx.arena.mark();
   int* lists = ctx.alloc<int>(4 * LASWP_CHUNK);
-  for (int64_t c1 = k1; c1 < k2; c1 += LASWP_CHUNK) {
+  // reverse = true undoes the interchanges (last first): the chunks are visited backwards and
+  // each chunk's net permutation is applied inverted (source and destination lists swapped)
+  const int64_t nchunk = ceil_div(k2 - k1, (int64_t)LASWP_CHUNK);
+  for (int64_t ci = 0; ci < nchunk; ci++) {
+    const int64_t c1 = k1 + (reverse ? nchunk - 1 - ci : ci) * LASWP_CHUNK;
     const int64_t c2 = c1 + LASWP_CHUNK < k2 ? c1 + LASWP_CHUNK : k2;
     const int npiv = (int)(c2 - c1);
     const int64_t mapn = m - c1;
     if (m <= 0 || mapn > LASWP_MAX_MAP) {
-      laswp_kernel<T><<<(unsigned)ceil_div(n, 128), 128, 0, ctx.stream>>>(n, A, lda, c1, c2, d_ipiv, 0);
+      laswp_kernel<T><<<(unsigned)ceil_div(n, 128), 128, 0, ctx.stream>>>(n, A, lda, c1, c2, d_ipiv,
+                                                                          reverse ? 1 : 0);
       LA_CUDA_CHECK(cudaGetLastError());
       continue;
     }
@@ -157,7 +162,7 @@ void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k
     const int nent = 2 * npiv;
     int64_t grid = n < (int64_t)ctx.sm_count * 8 ? n : (int64_t)ctx.sm_count * 8;
     laswp_apply_kernel<T><<<(unsigned)grid, 256, (size_t)nent * sizeof(T), ctx.stream>>>(
-        n, A, lda, nent, dst, src);
+        n, A, lda, nent, reverse ? src : dst, reverse ? dst : src);
     LA_CUDA_CHECK(cudaGetLastError());
   }
   ctx.arena.release(mk);
@@ -279,7 +284,7 @@ void getrs(Context& ctx, Op trans, int64_t n, int64_t nrhs, const T* A, int64_t 
   } else {
     trsm<T>(ctx, Left, Upper, trans, NonUnit, n, nrhs, one<T>(), A, lda, B, ldb);
     trsm<T>(ctx, Left, Lower, trans, Unit, n, nrhs, one<T>(), A, lda, B, ldb);
-    laswp<T>(ctx, nrhs, B, ldb, 0, n, d_ipiv, true);
+    laswp_rows<T>(ctx, n, nrhs, B, ldb, 0, n, d_ipiv, true);
   }
 }
 

@@ -48,6 +48,12 @@ template <typename T>
 void herk(Context& ctx, Uplo uplo, Op trans, int64_t n, int64_t k, double alpha, const T* A,
           int64_t lda, double beta, T* C, int64_t ldc);
 
+// op(A) X = alpha B for nrhs <= 8 right-hand sides in one cooperative launch (trsv.cu); returns
+// false when the shape is not for that path.
+template <typename T>
+bool trsv_small(Context& ctx, Uplo uplo, Op op, Diag diag, int64_t n, int64_t nrhs, T alpha,
+                const T* A, int64_t lda, T* B, int64_t ldb);
+
 template <typename T>
 void trsm(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, int64_t n, T alpha,
           const T* A, int64_t lda, T* B, int64_t ldb);

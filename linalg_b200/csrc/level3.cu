@@ -348,6 +348,9 @@ void trsm(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, int64
           const T* A, int64_t lda, T* B, int64_t ldb) {
   if (m <= 0 || n <= 0) return;
   if (!Traits<T>::is_complex && op == OpC) op = OpT;
+  // a vector or a handful of right-hand sides (solve / cho_solve / solvels with a column):
+  // one pass over the triangle in a single launch instead of ~m/32 tiny ones
+  if (side == Left && trsv_small<T>(ctx, uplo, op, diag, m, n, alpha, A, lda, B, ldb)) return;
   trsm_rec<T>(ctx, side, uplo, op, diag, m, n, alpha, A, lda, B, ldb);
 }
 template void trsm<float>(Context&, Side, Uplo, Op, Diag, int64_t, int64_t, float, const float*,

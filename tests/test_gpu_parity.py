@@ -268,7 +268,7 @@ def test_getrf_singular_and_ties(dt, product_abi, oracle_abi):
 
 
 @pytest.mark.parametrize("dt", DTYPES, ids=IDS)
-@pytest.mark.parametrize("n,nrhs", [(1, 1), (50, 3), (300, 1), (300, 40)])
+@pytest.mark.parametrize("n,nrhs", [(1, 1), (50, 3), (300, 1), (300, 40), (1500, 5), (2111, 8)])
 def test_gesv_getrs(rng, dt, n, nrhs, product_abi, oracle_abi):
     A, B = _rand(rng, (n, n), dt), _rand(rng, (n, nrhs), dt)
     with la.use_backend(product_abi):
@@ -327,8 +327,8 @@ def test_potrf_not_positive_definite_info(rng, dt, product_abi, oracle_abi):
 
 
 @pytest.mark.parametrize("dt", DTYPES, ids=IDS)
-def test_posv_potrs_cho_solve(rng, dt, product_abi):
-    n, nrhs = 150, 7
+@pytest.mark.parametrize("n,nrhs", [(150, 7), (1333, 2), (900, 30)])
+def test_posv_potrs_cho_solve(rng, dt, n, nrhs, product_abi):
     A, B = _spd(rng, n, dt), _rand(rng, (n, nrhs), dt)
     with la.use_backend(product_abi):
         a = la.GeneralMatrix(A).assume_(la.MatrixFlags.PositiveDefinite)
