@@ -206,7 +206,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
                        (((uintptr_t)A & 15) == 0);
   static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
   const bool lookahead = !la_disabled && ctx.allow_side_stream && dmma_ok && k >= 8192 &&
-                         leaf_ctas <= 40 && k > NB;
+                         leaf_ctas <= 96 && k > NB;
   Context* side = lookahead ? side_context(ctx) : nullptr;
   if (side) {
     // every first-use allocation of the side context (stream, arena block, pivot-exchange
