@@ -239,7 +239,17 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       // the next panel has m - j1 rows: its cooperative leaf needs that many SMs / 512, the rest
       // of the side stream's work is happy with 16
       const int64_t ctas1 = ceil_div(m - j1, (int64_t)512);
-      const int side_sms = (int)(ctas1 < 16 ? 16 : ctas1);
+      int side_sms = (int)(ctas1 < 16 ? 16 : ctas1);
+      {
+        // late steps: the trailing update is shorter than the panel, so the panel's own
+        // GEMMs / TRSMs get the SMs the update does not need to finish in the panel's time
+        const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / 31.0e9;
+        const double pan_ms = 1.6 + 1.5 * (double)(m - j1) / 16384.0;
+        const int need = (int)(ctx.sm_count * upd_ms / pan_ms) + 1;
+        int spare = ctx.sm_count - (need < 32 ? 32 : need);
+        if (spare > 116) spare = 116;
+        if (spare > side_sms) side_sms = spare;
+      }
       gemm<T>(ctx, OpN, OpN, mr, jb1, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
       LA_CUDA_CHECK(cudaEventRecord(ctx.ev[0], ctx.stream));
       LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));
