@@ -87,6 +87,11 @@ def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, group=None):
     `a_local` has shape (nloc * nb_cols, n): the block columns k with k % world == rank, in
     increasing k, each nb columns wide (the last one may be narrower), full height n.  On return
     the lower triangle of every owned block column holds L.  Returns LAPACK's info (0 = ok).
+
+    Look-ahead: as soon as panel k has arrived, the owner of block column k+1 updates that column
+    alone, factors it and posts its broadcast (asynchronous, on NCCL's stream), and only then do
+    all ranks apply panel k to the rest of their columns — the next panel travels while the
+    tensor cores are busy, and no rank ever waits for a barrier, only for the panel it needs.
     """
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
@@ -97,13 +102,15 @@ def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, group=None):
         if owner_of_block(k, world) == rank:
             offs[k] = pos
             pos += min(nb, n - k * nb)
-    panel_buf = torch.empty((nb, n), dtype=a_local.dtype, device=a_local.device)
-    info = 0
-    for k in range(nblk):
+    bufs = [torch.empty(nb * n, dtype=a_local.dtype, device=a_local.device) for _ in range(2)]
+
+    def factor_and_post(k):
+        """Owner: factor block column k (all updates applied) and stage it; all: post the
+        broadcast.  Returns (panel view (kb, n - k0) with ld = n - k0, pending work or None)."""
         k0 = k * nb
         kb = min(nb, n - k0)
         owner = owner_of_block(k, world)
-        panel = panel_buf[:kb, : n - k0]               # (n - k0) x kb, contiguous rows
+        panel = bufs[k % 2][: kb * (n - k0)].view(kb, n - k0)
         if rank == owner:
             col = a_local[offs[k]: offs[k] + kb]       # n x kb view
             diag = col[:, k0: k0 + kb]
@@ -111,23 +118,31 @@ def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, group=None):
             if n - k0 - kb > 0:
                 ops.trsm_right_lower_ct(diag, col[:, k0 + kb:])
             panel.copy_(col[:, k0:])
+        work = None
         if world > 1:
-            flat = panel_buf[:kb].reshape(-1) if (n - k0) == n else None
-            if flat is not None:
-                dist.broadcast(flat, src=owner, group=group)
-            else:
-                send = panel.contiguous()
-                dist.broadcast(send, src=owner, group=group)
-                if rank != owner:
-                    panel.copy_(send)
-        # rank-kb update of the owned block columns to the right of k
-        for j in range(k + 1, nblk):
-            if owner_of_block(j, world) != rank:
-                continue
-            j0 = j * nb
-            jb = min(nb, n - j0)
-            c = a_local[offs[j]: offs[j] + jb][:, j0:]             # (n - j0) x jb
-            ops.gemm_nt_sub(c, panel[:, j0 - k0:], panel[:, j0 - k0: j0 - k0 + jb])
+            work = dist.broadcast(panel, src=owner, group=group, async_op=True)
+        return panel, work
+
+    def update(j, k, panel):
+        """Block column j (owned) -= panel_k(j0:, :) * panel_k(j0:j0+jb, :)^H."""
+        k0, j0 = k * nb, j * nb
+        jb = min(nb, n - j0)
+        c = a_local[offs[j]: offs[j] + jb][:, j0:]                 # (n - j0) x jb
+        ops.gemm_nt_sub(c, panel[:, j0 - k0:], panel[:, j0 - k0: j0 - k0 + jb])
+
+    panel, work = factor_and_post(0)
+    for k in range(nblk):
+        if work is not None:
+            work.wait()
+        nxt = (None, None)
+        if k + 1 < nblk:
+            if owner_of_block(k + 1, world) == rank:
+                update(k + 1, k, panel)
+            nxt = factor_and_post(k + 1)
+        for j in range(k + 2, nblk):
+            if owner_of_block(j, world) == rank:
+                update(j, k, panel)
+        panel, work = nxt
     info = ops.info_value()
     if world > 1:                                   # smallest non-zero info over the ranks
         big = 2 ** 31 - 1
