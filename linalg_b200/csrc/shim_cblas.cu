@@ -58,9 +58,14 @@ static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, in
     dB = dev_alloc<T>(*ctx, br, bc);
     const int64_t nb = round_up(ceil_div(n, nchunks), 128);
     cudaStream_t up = ctx->copy_stream, down = ctx->d2h_stream;
-    cudaEvent_t ev_up[16], ev_done[16];
-    upload<T>(*ctx, dA, A, lda, up);
-    int nc = 0;
+    cudaEvent_t ev_up[16], ev_done[16], ev_a[16];
+    // A travels in k-chunks BEHIND the first block of B and C, and the first column block is
+    // multiplied chunk by chunk as they land: only B0, C0 and the first k-chunk of A are exposed
+    // instead of the whole of A.
+    const int64_t kc = 4096;
+    const int nka = (k >= 2 * kc) ? (int)(ceil_div(k, kc) < 16 ? ceil_div(k, kc) : 16) : 1;
+    const int64_t kstep = nka == 1 ? k : round_up(ceil_div(k, (int64_t)nka), 128);
+    int nc = 0, na_ev = 0;
     for (int64_t c0 = 0; c0 < n; c0 += nb, nc++) {
       const int64_t cn = nb < n - c0 ? nb : n - c0;
       LA_CUDA_CHECK(cudaEventCreateWithFlags(&ev_up[nc], cudaEventDisableTiming));
@@ -75,7 +80,28 @@ static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, in
       if (!is_zero(beta)) upload<T>(*ctx, vC, C + c0 * (int64_t)ldc, ldc, up);
       LA_CUDA_CHECK(cudaEventRecord(ev_up[nc], up));
       LA_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ev_up[nc], 0));
-      gemm<T>(*ctx, (Op)ta, (Op)tb, m, cn, k, alpha, dA.p, dA.ld, vB.p, dB.ld, beta, vC.p, dC.ld);
+      if (nc == 0) {
+        for (int l = 0; l < nka; l++) {
+          const int64_t l0 = l * kstep;
+          const int64_t kl = kstep < k - l0 ? kstep : k - l0;
+          if (kl <= 0) break;
+          // k-chunk l of op(A): columns of A (ta == N) or rows (otherwise), same for op(B)
+          DevMat<T> vA = dA;
+          const T* hA;
+          if (ta == OpN) { vA.p = dA.p + l0 * dA.ld; vA.rows = m;  vA.cols = kl; hA = A + l0 * (int64_t)lda; }
+          else           { vA.p = dA.p + l0;         vA.rows = kl; vA.cols = m;  hA = A + l0; }
+          upload<T>(*ctx, vA, hA, lda, up);
+          LA_CUDA_CHECK(cudaEventCreateWithFlags(&ev_a[l], cudaEventDisableTiming));
+          na_ev = l + 1;
+          LA_CUDA_CHECK(cudaEventRecord(ev_a[l], up));
+          LA_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ev_a[l], 0));
+          const T* pB = tb == OpN ? vB.p + l0 : vB.p + l0 * dB.ld;
+          gemm<T>(*ctx, (Op)ta, (Op)tb, m, cn, kl, alpha, vA.p, dA.ld, pB, dB.ld,
+                  l == 0 ? beta : one<T>(), vC.p, dC.ld);
+        }
+      } else {
+        gemm<T>(*ctx, (Op)ta, (Op)tb, m, cn, k, alpha, dA.p, dA.ld, vB.p, dB.ld, beta, vC.p, dC.ld);
+      }
       LA_CUDA_CHECK(cudaEventRecord(ev_done[nc], ctx->stream));
       LA_CUDA_CHECK(cudaStreamWaitEvent(down, ev_done[nc], 0));
       download<T>(*ctx, vC, C + c0 * (int64_t)ldc, ldc, down);
@@ -83,6 +109,7 @@ static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, in
     LA_CUDA_CHECK(cudaStreamSynchronize(down));
     sync(*ctx);
     for (int i = 0; i < nc; i++) { cudaEventDestroy(ev_up[i]); cudaEventDestroy(ev_done[i]); }
+    for (int l = 0; l < na_ev; l++) cudaEventDestroy(ev_a[l]);
   }
   ctx->arena.release(mk);
 }
