@@ -194,7 +194,11 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   __shared__ int sidx[NW];
   __shared__ int s_pi[2];
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // broadcast from lane 0: tells the compiler that the warp index is warp-uniform, so that the
+  // reductions / ballots / shuffles under `if (warp == 0)` are emitted inline and not as
+  // re-convergence (WARPSYNC.COLLECTIVE) sequences
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int rs = blockIdx.x * rpc;                 // rpc == R * LU_NT rows per CTA
   const int gr0 = rs + tid;                        // this thread's rows: gr0 + r * LU_NT
 

@@ -113,7 +113,8 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
   __shared__ T s_scale;
   __shared__ T s_beta;
 
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
   const int G = gridDim.x;
   const int64_t rs = (int64_t)blockIdx.x * rpc;
   int64_t nr64 = mp - rs; if (nr64 > rpc) nr64 = rpc; if (nr64 < 0) nr64 = 0;
@@ -230,7 +231,8 @@ qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __
   __shared__ T s_f[QR_MAX_JB];
   __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
   __shared__ T s_scale, s_beta;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
   const int G = gridDim.x;
   const int64_t rs = (int64_t)blockIdx.x * rpc;
   int64_t nr = mp - rs; if (nr > rpc) nr = rpc; if (nr < 0) nr = 0;
