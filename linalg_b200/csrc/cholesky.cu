@@ -272,6 +272,13 @@ static void potrf_twolevel(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda
 //            rest of the trailing matrix -= P' P'^H      (HERK on the remaining SMs, meanwhile)
 // The serial part of the algorithm (n / 128 leaf launches) is thereby hidden behind the tensor
 // core work as long as the trailing update of a step outlasts one diagonal block.
+int64_t potrf_block_width(int64_t n) {
+  static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
+  static const int nbo_env = getenv("LA_B200_CHOL_NBO") ? atoi(getenv("LA_B200_CHOL_NBO")) : 0;
+  if (n < 4096 || la_disabled) return n;
+  return nbo_env > 0 ? nbo_env : (n >= 8192 ? 1024 : 512);
+}
+
 template <typename T>
 void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
   LA_CUDA_CHECK(cudaMemsetAsync(d_info, 0, sizeof(int), ctx.stream));
@@ -297,8 +304,7 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
     side->arena.release(smk);
     LA_CUDA_CHECK(cudaStreamSynchronize(side->stream));
   }
-  static const int nbo_env = getenv("LA_B200_CHOL_NBO") ? atoi(getenv("LA_B200_CHOL_NBO")) : 0;
-  const int64_t NBO = nbo_env > 0 ? nbo_env : (n >= 8192 ? 1024 : 512);
+  const int64_t NBO = potrf_block_width(n);
   auto at = [&](int64_t i, int64_t j) { return A + i + j * lda; };
   const T mone = from_real<T>(-1.0);
   const bool L = uplo == Lower;
@@ -312,10 +318,12 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
     const int64_t r3 = r2 - kb2;  // order of the trailing matrix beyond the next block column
     if (L) {
       trsm<T>(ctx, Right, Lower, OpC, NonUnit, r2, kb, one<T>(), at(K0, K0), lda, at(K1, K0), lda);
+      if (ctx.on_block_final) ctx.on_block_final(K0, K1);
       gemm<T>(ctx, OpN, OpC, r2, kb2, kb, mone, at(K1, K0), lda, at(K1, K0), lda, one<T>(),
               at(K1, K1), lda, TriLower, Traits<T>::is_complex);
     } else {
       trsm<T>(ctx, Left, Upper, OpC, NonUnit, kb, r2, one<T>(), at(K0, K0), lda, at(K0, K1), lda);
+      if (ctx.on_block_final) ctx.on_block_final(K0, K1);
       gemm<T>(ctx, OpC, OpN, kb2, r2, kb, mone, at(K0, K1), lda, at(K0, K1), lda, one<T>(),
               at(K1, K1), lda, TriUpper, Traits<T>::is_complex);
     }

@@ -6,6 +6,7 @@
 // side: every exported symbol checks a Context out of a mutex-protected pool,
 // runs on that context's stream and bump-allocates scratch from its arena.
 #pragma once
+#include <functional>
 #include <cuda_runtime.h>
 #include <cstddef>
 #include <cstdint>
@@ -40,6 +41,10 @@ struct Context {
   int sm_limit = 0;                // > 0: persistent kernels use at most this many CTAs
   bool allow_side_stream = true;   // look-ahead may create `side` (a stream, events, an arena)
   Context* side = nullptr;         // second context for work overlapped with the main stream
+  // Host-pointer shims only: called by a factorisation, in stream order, each time a block of
+  // the result has reached its final value (Cholesky: block column / block row [c0, c1)), so
+  // that the shim can send it home while the factorisation goes on.
+  std::function<void(int64_t c0, int64_t c1)> on_block_final;
   template <typename T> T* alloc(size_t n) { return (T*)arena.alloc(n * sizeof(T)); }
 };
 

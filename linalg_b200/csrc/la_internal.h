@@ -90,6 +90,9 @@ void laswp(Context& ctx, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, c
            bool reverse);
 
 // factorizations / solves
+// Width of the block columns / rows in which potrf reports its result final through
+// Context::on_block_final (n itself when it does not report).
+int64_t potrf_block_width(int64_t n);
 template <typename T>
 void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info);
 template <typename T>

@@ -47,6 +47,33 @@ inline DevMat<T> dev_from_host(Context& ctx, int64_t rows, int64_t cols, const T
   return d;
 }
 
+// Transfer only the named triangle of an n x n matrix (block columns of `bw` columns, each as
+// one 2D copy of its trapezoid): ?potrf / ?posv neither read nor write the other triangle
+// (cholesky.cr:50-64 relies on that), so half of the PCIe traffic can stay at home.
+template <typename T>
+inline void copy_triangle_hd(Context& ctx, bool to_device, bool lower, int64_t n, T* dev,
+                             int64_t ldd, T* host, int64_t ldh, int64_t bw,
+                             cudaStream_t s = nullptr) {
+  // (diagonal blocks of width bw travel whole, so the other triangle inside them makes a
+  // round trip; bw must therefore match the block width the factorisation reports)
+  if (bw <= 0 || bw > n) bw = n;
+  for (int64_t c0 = 0; c0 < n; c0 += bw) {
+    const int64_t w = bw < n - c0 ? bw : n - c0;
+    const int64_t r0 = lower ? c0 : 0;
+    const int64_t rows = lower ? n - c0 : c0 + w;
+    T* d = dev + r0 + c0 * ldd;
+    T* h = host + r0 + c0 * ldh;
+    if (to_device)
+      LA_CUDA_CHECK(cudaMemcpy2DAsync(d, (size_t)ldd * sizeof(T), h, (size_t)ldh * sizeof(T),
+                                      (size_t)rows * sizeof(T), (size_t)w, cudaMemcpyHostToDevice,
+                                      s ? s : ctx.stream));
+    else
+      LA_CUDA_CHECK(cudaMemcpy2DAsync(h, (size_t)ldh * sizeof(T), d, (size_t)ldd * sizeof(T),
+                                      (size_t)rows * sizeof(T), (size_t)w, cudaMemcpyDeviceToHost,
+                                      s ? s : ctx.stream));
+  }
+}
+
 inline void sync(Context& ctx) { LA_CUDA_CHECK(cudaStreamSynchronize(ctx.stream)); }
 
 // Read the device info word after the stream has drained.

@@ -7,6 +7,7 @@
 // touched), info > 0 with LAPACK's meaning (zero pivot / non-PD minor / zero R diagonal).
 // CUDA failures abort the process with a message; they never return success.
 #include "shim_common.h"
+#include <vector>
 
 namespace la {
 
@@ -91,6 +92,41 @@ static void h_gesv(const int* pn, const int* pnrhs, T* A, const int* plda, int* 
   ctx->arena.release(mk);
 }
 
+// potrf on the staged matrix with the factor sent home block by block: every block column (L)
+// or block row (U) is final as soon as its panel has been solved, so its device->host copy runs
+// on the second copy stream while the factorisation continues; only the last block is exposed.
+template <typename T>
+static void potrf_streamed_home(Context& ctx, int uplo, int64_t n, DevMat<T>& dA, T* A, int64_t lda) {
+  const bool lower = uplo == Lower;
+  int64_t done = 0;
+  std::vector<cudaEvent_t> evs;
+  ctx.on_block_final = [&](int64_t c0, int64_t c1) {
+    if (c0 != done) return;  // only contiguous progress is streamed; the rest goes at the end
+    cudaEvent_t e;
+    LA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    LA_CUDA_CHECK(cudaEventRecord(e, ctx.stream));
+    LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.d2h_stream, e, 0));
+    evs.push_back(e);
+    const T* d = dA.p + c0 + c0 * dA.ld;
+    T* h = A + c0 + c0 * lda;
+    // lower: columns [c0, c1), rows c0..n ; upper: rows [c0, c1), columns c0..n
+    const size_t width = (size_t)(lower ? n - c0 : c1 - c0) * sizeof(T);
+    const size_t height = (size_t)(lower ? c1 - c0 : n - c0);
+    LA_CUDA_CHECK(cudaMemcpy2DAsync(h, (size_t)lda * sizeof(T), d, (size_t)dA.ld * sizeof(T), width,
+                                    height, cudaMemcpyDeviceToHost, ctx.d2h_stream));
+    done = c1;
+  };
+  potrf<T>(ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx.d_info);
+  ctx.on_block_final = nullptr;
+  // (streamed blocks and uploaded blocks have the same width, so the part of a diagonal block
+  // that lies in the other triangle only makes a round trip)
+  if (n - done > 0)
+    copy_triangle_hd<T>(ctx, false, lower, n - done, dA.p + done + done * dA.ld, dA.ld,
+                        A + done + done * lda, lda, potrf_block_width(n));
+  LA_CUDA_CHECK(cudaStreamSynchronize(ctx.d2h_stream));
+  for (auto e : evs) cudaEventDestroy(e);
+}
+
 // ------------------------------------------------------------------ potrf / potrs / posv
 template <typename T>
 static void h_potrf(const char* puplo, const int* pn, T* A, const int* plda, int* info) {
@@ -103,11 +139,11 @@ static void h_potrf(const char* puplo, const int* pn, T* A, const int* plda, int
   if (n == 0) return;
   ContextLease ctx;
   Arena::Mark mk = ctx->arena.mark();
-  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
-  potrf<T>(*ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx->d_info);
-  // the kernels touch only the named triangle, so the full download leaves the other one
-  // bit-identical on the host ("other triangle untouched", cholesky.cr:50-64 relies on it)
-  download<T>(*ctx, dA, A, lda);
+  // the kernels touch only the named triangle: only that triangle travels, and the other one
+  // stays bit-identical on the host ("other triangle untouched", cholesky.cr:50-64 relies on it)
+  DevMat<T> dA = dev_alloc<T>(*ctx, n, n);
+  copy_triangle_hd<T>(*ctx, true, uplo == Lower, n, dA.p, dA.ld, A, lda, potrf_block_width(n));
+  potrf_streamed_home<T>(*ctx, uplo, n, dA, A, lda);
   *info = read_info(*ctx, ctx->d_info);
   ctx->arena.release(mk);
 }
@@ -148,10 +184,10 @@ static void h_posv(const char* puplo, const int* pn, const int* pnrhs, T* A, con
   if (n == 0) return;
   ContextLease ctx;
   Arena::Mark mk = ctx->arena.mark();
-  DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
+  DevMat<T> dA = dev_alloc<T>(*ctx, n, n);
+  copy_triangle_hd<T>(*ctx, true, uplo == Lower, n, dA.p, dA.ld, A, lda, potrf_block_width(n));
   DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
-  potrf<T>(*ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx->d_info);
-  download<T>(*ctx, dA, A, lda);
+  potrf_streamed_home<T>(*ctx, uplo, n, dA, A, lda);
   const int inf = read_info(*ctx, ctx->d_info);
   if (inf == 0 && nrhs > 0) {
     potrs<T>(*ctx, (Uplo)uplo, n, nrhs, dA.p, dA.ld, dB.p, dB.ld);

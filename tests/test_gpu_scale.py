@@ -97,3 +97,29 @@ def test_potrf_probe_residual_at_scale(n):
     X = _rand((n, 16), 9)
     rel = ((S @ X - L @ (L.T @ X)).abs().max() / (S.abs().max() * X.abs().sum(dim=0).max())).item()
     assert rel < 1e-13, rel
+
+
+@pytest.mark.parametrize("n,lower", [(4608, True), (4700, False), (8300, True), (8300, False)])
+def test_host_potrf_moves_only_the_named_triangle(n, lower, product_abi):
+    # the host-pointer dpotrf_ uploads and downloads only the named triangle (in block columns
+    # that match the factorisation's blocks) and streams finished blocks home while it works:
+    # the other triangle of the caller's array must come back bit-identical, poison included
+    import ctypes as C
+    from linalg_b200 import ffi
+    rng = np.random.default_rng(12)
+    G = rng.random((n, n)) - 0.5
+    S = G @ G.T / n + np.eye(n)
+    A = np.asfortranarray(S.copy())
+    other = np.triu_indices(n, 1) if lower else np.tril_indices(n, -1)
+    A[other] = np.nan
+    before = A.copy(order="F")
+    info = C.c_int(-99)
+    ni = C.c_int(n)
+    product_abi.lapack("potrf", "d")(C.c_char_p(b"L" if lower else b"U"), C.byref(ni), ffi.ptr(A),
+                                     C.byref(ni), C.byref(info))
+    assert info.value == 0
+    assert np.array_equal(np.isnan(A), np.isnan(before))          # poison where it was, only there
+    F = np.tril(A) if lower else np.triu(np.nan_to_num(A))
+    F = np.nan_to_num(F)
+    R = F @ F.T if lower else F.T @ F
+    assert np.abs(R - S).max() / np.abs(S).max() < 1e-13
