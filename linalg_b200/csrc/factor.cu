@@ -229,6 +229,8 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     T* A12 = A + j0 + (j0 + jb) * lda;
     laswp_rows<T>(ctx, m, nr, A + (j0 + jb) * lda, lda, j0, j0 + jb, d_ipiv);
     trsm<T>(ctx, Left, Lower, OpN, Unit, jb, nr, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
+    // rows [j0, j0 + jb) of the whole matrix are final now: later panels interchange rows below
+    if (ctx.on_block_final) ctx.on_block_final(j0, j0 + jb);
     const int64_t mr = m - j0 - jb;
     if (mr <= 0) continue;
     const T* A21 = A + (j0 + jb) + j0 * lda;

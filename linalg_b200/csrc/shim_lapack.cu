@@ -20,6 +20,39 @@ static void set_work(T* work, double v) {
 }
 
 // ------------------------------------------------------------------ getrf / getrs / gesv
+// getrf on the staged matrix with the factors sent home block row by block row: the rows of a
+// panel's diagonal block are final for the whole matrix width as soon as U12 has been solved
+// (later panels only interchange rows below), so their device->host copy runs on the second copy
+// stream while the factorisation continues; only the last block row is exposed.
+template <typename T>
+static void getrf_streamed_home(Context& ctx, int64_t m, int64_t n, DevMat<T>& dA, int* d_ipiv,
+                                T* A, int64_t lda) {
+  int64_t done = 0;
+  std::vector<cudaEvent_t> evs;
+  if (m >= 4096 && n >= 4096) {
+    ctx.on_block_final = [&](int64_t r0, int64_t r1) {
+      if (r0 != done) return;  // only contiguous progress is streamed; the rest goes at the end
+      cudaEvent_t e;
+      LA_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      LA_CUDA_CHECK(cudaEventRecord(e, ctx.stream));
+      LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.d2h_stream, e, 0));
+      evs.push_back(e);
+      LA_CUDA_CHECK(cudaMemcpy2DAsync(A + r0, (size_t)lda * sizeof(T), dA.p + r0,
+                                      (size_t)dA.ld * sizeof(T), (size_t)(r1 - r0) * sizeof(T),
+                                      (size_t)n, cudaMemcpyDeviceToHost, ctx.d2h_stream));
+      done = r1;
+    };
+  }
+  getrf<T>(ctx, m, n, dA.p, dA.ld, d_ipiv, ctx.d_info);
+  ctx.on_block_final = nullptr;
+  if (m - done > 0)
+    LA_CUDA_CHECK(cudaMemcpy2DAsync(A + done, (size_t)lda * sizeof(T), dA.p + done,
+                                    (size_t)dA.ld * sizeof(T), (size_t)(m - done) * sizeof(T),
+                                    (size_t)n, cudaMemcpyDeviceToHost, ctx.stream));
+  LA_CUDA_CHECK(cudaStreamSynchronize(ctx.d2h_stream));
+  for (auto e : evs) cudaEventDestroy(e);
+}
+
 template <typename T>
 static void h_getrf(const int* pm, const int* pn, T* A, const int* plda, int* ipiv, int* info) {
   const int64_t m = *pm, n = *pn, lda = *plda;
@@ -33,8 +66,7 @@ static void h_getrf(const int* pm, const int* pn, T* A, const int* plda, int* ip
   const int64_t k = imin(m, n);
   DevMat<T> dA = dev_from_host<T>(*ctx, m, n, A, lda);
   int* d_ipiv = ctx->alloc<int>(k);
-  getrf<T>(*ctx, m, n, dA.p, dA.ld, d_ipiv, ctx->d_info);
-  download<T>(*ctx, dA, A, lda);
+  getrf_streamed_home<T>(*ctx, m, n, dA, d_ipiv, A, lda);
   LA_CUDA_CHECK(cudaMemcpyAsync(ipiv, d_ipiv, k * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   *info = read_info(*ctx, ctx->d_info);
   ctx->arena.release(mk);
@@ -79,8 +111,7 @@ static void h_gesv(const int* pn, const int* pnrhs, T* A, const int* plda, int* 
   DevMat<T> dA = dev_from_host<T>(*ctx, n, n, A, lda);
   DevMat<T> dB = dev_from_host<T>(*ctx, n, nrhs, B, ldb);
   int* d_ipiv = ctx->alloc<int>(n);
-  getrf<T>(*ctx, n, n, dA.p, dA.ld, d_ipiv, ctx->d_info);
-  download<T>(*ctx, dA, A, lda);
+  getrf_streamed_home<T>(*ctx, n, n, dA, d_ipiv, A, lda);
   LA_CUDA_CHECK(cudaMemcpyAsync(ipiv, d_ipiv, n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   const int inf = read_info(*ctx, ctx->d_info);
   if (inf == 0 && nrhs > 0) {  // LAPACK solves only when U is non-singular

@@ -123,3 +123,26 @@ def test_host_potrf_moves_only_the_named_triangle(n, lower, product_abi):
     F = np.nan_to_num(F)
     R = F @ F.T if lower else F.T @ F
     assert np.abs(R - S).max() / np.abs(S).max() < 1e-13
+
+
+@pytest.mark.parametrize("m,n", [(4608, 4608), (8300, 8300), (9000, 5000)])
+def test_host_getrf_streams_block_rows_home(m, n, product_abi, oracle_abi):
+    # the host-pointer dgetrf_ sends every finished block row home while it is still factoring
+    # (shim_lapack.cu); factors and pivots must equal LAPACK's as for the small cases
+    import ctypes as C
+    from linalg_b200 import ffi
+    rng = np.random.default_rng(13)
+    A0 = np.asfortranarray(rng.random((m, n)))
+    out = []
+    for abi in (product_abi, oracle_abi):
+        A = A0.copy(order="F")
+        ipiv = np.zeros(min(m, n), dtype=np.int32)
+        info = C.c_int(-99)
+        mi, ni = C.c_int(m), C.c_int(n)
+        abi.lapack("getrf", "d")(C.byref(mi), C.byref(ni), ffi.ptr(A), C.byref(mi), ffi.ptr(ipiv),
+                                 C.byref(info))
+        assert info.value == 0
+        out.append((A, ipiv))
+    (lu, piv), (rlu, rpiv) = out
+    assert np.array_equal(piv, rpiv)
+    assert np.abs(lu - rlu).max() / np.abs(rlu).max() < 1e-10
