@@ -177,6 +177,29 @@ void laswp(Context& ctx, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, c
   LA_CUDA_CHECK(cudaGetLastError());
 }
 
+#ifdef LA_LU_TIMELINE
+#include <vector>
+static std::vector<cudaEvent_t> g_tl;   // per step: start, ev0 (serial part done), side done, part1 done, part2 done
+static cudaEvent_t tl_mark(cudaStream_t s) {
+  cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s); g_tl.push_back(e); return e;
+}
+extern "C" void la_b200_debug_lu_timeline() {
+  cudaDeviceSynchronize();
+  for (size_t i = 0; i + 4 < g_tl.size(); i += 5) {
+    float a, b, c, d;
+    cudaEventElapsedTime(&a, g_tl[i], g_tl[i + 1]);
+    cudaEventElapsedTime(&b, g_tl[i + 1], g_tl[i + 2]);
+    cudaEventElapsedTime(&c, g_tl[i + 1], g_tl[i + 3]);
+    cudaEventElapsedTime(&d, g_tl[i + 1], g_tl[i + 4]);
+    printf("step %2zu: serial %.2f | after ev0: panel done +%.2f, part1 done +%.2f, part2 done +%.2f ms\n", i / 5, a, b, c, d);
+  }
+  g_tl.clear();
+}
+#define TL(s) tl_mark(s)
+#else
+#define TL(s) (void)0
+#endif
+
 template <typename T>
 void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, int* d_info) {
   LA_CUDA_CHECK(cudaMemsetAsync(d_info, 0, sizeof(int), ctx.stream));
@@ -221,6 +244,8 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   bool panel_done = false;  // panel of the current j0 already factored (on the side stream)?
   for (int64_t j0 = 0; j0 < k; j0 += NB) {
     const int64_t jb = NB < k - j0 ? NB : k - j0;
+    const bool tl_on = panel_done || j0 == 0;
+    if (tl_on && lookahead) TL(ctx.stream);
     if (!panel_done) getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
     panel_done = false;
     if (j0 > 0) laswp_rows<T>(ctx, m, j0, A, lda, j0, j0 + jb, d_ipiv);
@@ -253,10 +278,12 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
         if (spare > side_sms) side_sms = spare;
       }
       gemm<T>(ctx, OpN, OpN, mr, jb1, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
+      TL(ctx.stream);
       LA_CUDA_CHECK(cudaEventRecord(ctx.ev[0], ctx.stream));
       LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));
       side->sm_limit = side_sms;
       getrf_rec<T>(*side, m, A, lda, d_ipiv, d_info, j1, jb1, plan);
+      TL(side->stream);
       LA_CUDA_CHECK(cudaEventRecord(side->ev[0], side->stream));
       // The trailing update runs on the SMs the side stream leaves free — but only for as long
       // as the panel is expected to take (a model of the panel's duration, biased long: an
@@ -273,10 +300,12 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       gemm<T>(ctx, OpN, OpN, mr, c1, jb, from_real<T>(-1.0), A21, lda, A12 + jb1 * lda, lda,
               one<T>(), A22 + jb1 * lda, lda);
       ctx.sm_limit = 0;
+      TL(ctx.stream);
       LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, side->ev[0], 0));
       if (c1 < rest)
         gemm<T>(ctx, OpN, OpN, mr, rest - c1, jb, from_real<T>(-1.0), A21, lda,
                 A12 + (jb1 + c1) * lda, lda, one<T>(), A22 + (jb1 + c1) * lda, lda);
+      TL(ctx.stream);
       panel_done = true;
     } else {
       gemm<T>(ctx, OpN, OpN, mr, nr, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
