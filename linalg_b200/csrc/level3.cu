@@ -268,6 +268,12 @@ void trsm_rec(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, i
   const int64_t na = side == Left ? m : n;
   const int64_t nvec = side == Left ? n : m;
   constexpr int TRSM_NB = TrsmCfg<T>::NB;
+  if constexpr (std::is_same<T, double>::value) {
+    // triangles of 65..128 with many vectors: one launch of the 128-wide tensor-core base case
+    if (na > TRSM_NB && na <= 128 &&
+        trsm_base_dmma_f64(ctx, side, uplo, op, diag, m, n, alpha, A, lda, B, ldb))
+      return;
+  }
   if (na <= TRSM_NB) {
     if constexpr (std::is_same<T, double>::value) {
       if (trsm_base_dmma_f64(ctx, side, uplo, op, diag, m, n, alpha, A, lda, B, ldb)) return;

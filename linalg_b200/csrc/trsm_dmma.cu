@@ -19,11 +19,10 @@ namespace la {
 namespace {
 
 constexpr int TB = 8;            // block order
-constexpr int TNB = 64;          // largest triangle (the staging code assumes 64)
-constexpr int TLD = TNB + 1;     // shared-memory pitch
-constexpr int TWARPS = 4;        // warps per CTA
 constexpr int TGROUPS = 2;       // 8-vector groups per warp (independent chains)
-constexpr int TVEC_PER_CTA = TWARPS * TGROUPS * 8;
+// Two instances: triangles up to 64 (4 warps, 64 vectors per CTA) and up to 128 (8 warps, 128
+// vectors per CTA, triangle in dynamic shared memory); the larger one saves a level of the
+// recursion (two base launches and a thin GEMM) wherever there are enough vectors to fill it.
 
 __device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -33,12 +32,15 @@ __device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
 
 // X (nvec x na, element (v,i) at X[v*vs + i*is]) <- alpha * X * U^-1, U = na x na triangular
 // (upper != 0: upper), given as Umat(i,j) = U[i*ur + j*uc] with optional unit diagonal.
+template <int TNB, int TWARPS>
 __global__ void __launch_bounds__(TWARPS * 32)
 trsm_dmma_kernel(int upper, int unit, int na, int64_t nvec, double alpha,
                  const double* __restrict__ U, int64_t ur, int64_t uc, double* __restrict__ X,
                  int64_t vs, int64_t is) {
-  __shared__ double Us[TNB * TLD];   // -U off the diagonal blocks, inv(U_jj) on them
-  __shared__ double Dg[TNB * TB];    // scratch copy of the diagonal blocks
+  constexpr int TLD = TNB + 1;       // shared-memory pitch
+  extern __shared__ __align__(16) unsigned char trsm_smem[];
+  double* Us = reinterpret_cast<double*>(trsm_smem);   // [TNB * TLD] -U off the diagonal blocks, inv(U_jj) on them
+  double* Dg = Us + TNB * TLD;                         // [TNB * TB] scratch copy of the diagonal blocks
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gid = lane >> 2, tig = lane & 3;
   const int nblk = (na + TB - 1) / TB;
@@ -47,30 +49,35 @@ trsm_dmma_kernel(int upper, int unit, int na, int64_t nvec, double alpha,
   // before the first shared-memory store (one memory round trip instead of one per element),
   // and the fast thread index follows the contiguous direction of the stored matrix.
   {
-    constexpr int PER = TNB * TNB / (TWARPS * 32);
+    constexpr int TOTAL = TNB * TNB / (TWARPS * 32);   // elements per thread
+    constexpr int PER = 32;                            // of which 32 are in flight at a time
+    constexpr int SH = TNB == 64 ? 6 : 7;
     const bool row_contig = (uc == 1);
-    double v[PER];
+#pragma unroll 1
+    for (int round = 0; round < TOTAL / PER; round++) {
+      double v[PER];
 #pragma unroll
-    for (int q = 0; q < PER; q++) {
-      const int idx = tid + q * (TWARPS * 32);
-      const int fa = idx & (TNB - 1), sl = idx >> 6;   // TNB == 64
-      const int i = row_contig ? sl : fa, j = row_contig ? fa : sl;
-      double x = (i == j) ? 1.0 : 0.0;
-      if (i < na && j < na) {
-        const bool stored = upper ? (i <= j) : (i >= j);
-        x = 0.0;
-        if (stored) x = (i == j && unit) ? 1.0 : U[i * ur + j * uc];
+      for (int q = 0; q < PER; q++) {
+        const int idx = tid + (round * PER + q) * (TWARPS * 32);
+        const int fa = idx & (TNB - 1), sl = idx >> SH;
+        const int i = row_contig ? sl : fa, j = row_contig ? fa : sl;
+        double x = (i == j) ? 1.0 : 0.0;
+        if (i < na && j < na) {
+          const bool stored = upper ? (i <= j) : (i >= j);
+          x = 0.0;
+          if (stored) x = (i == j && unit) ? 1.0 : U[i * ur + j * uc];
+        }
+        v[q] = x;
       }
-      v[q] = x;
-    }
 #pragma unroll
-    for (int q = 0; q < PER; q++) {
-      const int idx = tid + q * (TWARPS * 32);
-      const int fa = idx & (TNB - 1), sl = idx >> 6;
-      const int i = row_contig ? sl : fa, j = row_contig ? fa : sl;
-      if (i < npad && j < npad) {
-        Us[i * TLD + j] = -v[q];
-        if (i / TB == j / TB) Dg[(i / TB) * (TB * TB) + (i % TB) * TB + (j % TB)] = v[q];
+      for (int q = 0; q < PER; q++) {
+        const int idx = tid + (round * PER + q) * (TWARPS * 32);
+        const int fa = idx & (TNB - 1), sl = idx >> SH;
+        const int i = row_contig ? sl : fa, j = row_contig ? fa : sl;
+        if (i < npad && j < npad) {
+          Us[i * TLD + j] = -v[q];
+          if (i / TB == j / TB) Dg[(i / TB) * (TB * TB) + (i % TB) * TB + (j % TB)] = v[q];
+        }
       }
     }
   }
@@ -180,7 +187,8 @@ bool trsm_base_dmma_f64(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, in
                         double alpha, const double* A, int64_t lda, double* B, int64_t ldb) {
   const int64_t na = side == Left ? m : n;
   const int64_t nvec = side == Left ? n : m;
-  if (na > TNB || na <= 0 || nvec <= 0) return false;
+  // the 128 instance only where its CTAs (128 vectors each) fill the machine's SMs about once
+  if (na <= 0 || nvec <= 0 || na > 128 || (na > 64 && nvec < 4096)) return false;
   // Right: X op(A) = alpha B, vectors are rows of B:         U = op(A),   vs = 1,   is = ldb
   // Left : op(A) X = alpha B  <=>  X^T op(A)^T = alpha B^T:  U = op(A)^T, vs = ldb, is = 1
   const bool trans = op != OpN;
@@ -192,9 +200,25 @@ bool trsm_base_dmma_f64(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, in
   const bool u_upper = u_is_transposed_A ? !a_upper : a_upper;
   const int64_t vs = side == Right ? 1 : ldb;
   const int64_t is = side == Right ? ldb : 1;
-  const unsigned grid = (unsigned)ceil_div(nvec, TVEC_PER_CTA);
-  trsm_dmma_kernel<<<grid, TWARPS * 32, 0, ctx.stream>>>(u_upper ? 1 : 0, diag == Unit ? 1 : 0,
-                                                         (int)na, nvec, alpha, A, ur, uc, B, vs, is);
+  if (na <= 64) {
+    constexpr int W = 4;
+    constexpr size_t smem = sizeof(double) * (64 * 65 + 64 * TB);
+    const unsigned grid = (unsigned)ceil_div(nvec, (int64_t)W * TGROUPS * 8);
+    trsm_dmma_kernel<64, W><<<grid, W * 32, smem, ctx.stream>>>(
+        u_upper ? 1 : 0, diag == Unit ? 1 : 0, (int)na, nvec, alpha, A, ur, uc, B, vs, is);
+  } else {
+    constexpr int W = 8;
+    constexpr size_t smem = sizeof(double) * (128 * 129 + 128 * TB);
+    static bool attr = false;
+    if (!attr) {
+      LA_CUDA_CHECK(cudaFuncSetAttribute(trsm_dmma_kernel<128, W>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr = true;
+    }
+    const unsigned grid = (unsigned)ceil_div(nvec, (int64_t)W * TGROUPS * 8);
+    trsm_dmma_kernel<128, W><<<grid, W * 32, smem, ctx.stream>>>(
+        u_upper ? 1 : 0, diag == Unit ? 1 : 0, (int)na, nvec, alpha, A, ur, uc, B, vs, is);
+  }
   LA_CUDA_CHECK(cudaGetLastError());
   return true;
 }

@@ -146,3 +146,34 @@ def test_host_getrf_streams_block_rows_home(m, n, product_abi, oracle_abi):
     (lu, piv), (rlu, rpiv) = out
     assert np.array_equal(piv, rpiv)
     assert np.abs(lu - rlu).max() / np.abs(rlu).max() < 1e-10
+
+
+@pytest.mark.parametrize("side,uplo,op,diag,na", [
+    ("R", "L", "C", "N", 128), ("L", "L", "N", "U", 128), ("L", "U", "N", "N", 100),
+    ("R", "U", "N", "N", 77), ("L", "L", "T", "N", 128), ("R", "L", "N", "U", 96)])
+def test_trsm_wide_tensor_core_base_case(side, uplo, op, diag, na):
+    # triangles of 65..128 with thousands of vectors take the 128-wide DMMA base kernel
+    nvec = 6000
+    g = torch.Generator(device="cuda").manual_seed(21)
+    T = torch.rand((na, na), dtype=torch.float64, device="cuda", generator=g) - 0.5
+    T += na * torch.eye(na, dtype=torch.float64, device="cuda")
+    Tm = T.T                                             # math view of the column-major triangle
+    tri = torch.tril(Tm) if uplo == "L" else torch.triu(Tm)
+    if diag == "U":
+        tri = tri - torch.diag(torch.diag(tri)) + torch.eye(na, dtype=torch.float64, device="cuda")
+    M = tri if op == "N" else tri.T
+    if side == "L":
+        B = torch.rand((nvec, na), dtype=torch.float64, device="cuda", generator=g)   # na x nvec
+        X = B.clone()
+        dev.trsm(dev.LEFT, dev.LOWER if uplo == "L" else dev.UPPER,
+                 {"N": dev.NO_TRANS, "T": dev.TRANS, "C": dev.CONJ_TRANS}[op],
+                 dev.UNIT if diag == "U" else dev.NON_UNIT, na, nvec, 2.0, T, na, X, na)
+        res = M @ X.T - 2.0 * B.T
+    else:
+        B = torch.rand((na, nvec), dtype=torch.float64, device="cuda", generator=g)   # nvec x na
+        X = B.clone()
+        dev.trsm(dev.RIGHT, dev.LOWER if uplo == "L" else dev.UPPER,
+                 {"N": dev.NO_TRANS, "T": dev.TRANS, "C": dev.CONJ_TRANS}[op],
+                 dev.UNIT if diag == "U" else dev.NON_UNIT, nvec, na, 2.0, T, na, X, nvec)
+        res = X.T @ M - 2.0 * B.T
+    assert res.abs().max().item() < 1e-11
