@@ -235,10 +235,16 @@ __device__ __forceinline__ bool tile_active(const GemmParams& p, int tm, int tn)
   return ((tm * BM) >> 1) <= tn * BN + BN - 1;
 }
 
-template <bool A_MN, bool B_MN>
+// NJ = DMMA tiles per warp along N: 4 -> CTA tile 128 x 128; 1 -> CTA tile 128 x 32 for products
+// with at most 32 columns (W^H = C^H V in QR, Gram matrices), which would otherwise spend 3/4 of
+// the tensor work on padding.
+template <bool A_MN, bool B_MN, int NJ>
 __global__ void __launch_bounds__(NTHREADS, 1)
 dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const GemmParams p) {
+  constexpr int BN = 32 * NJ;
+  constexpr int B_STAGE_BYTES = BN * BK * 8;
+  constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = (uint64_t*)(smem + STAGES * STAGE_BYTES);
@@ -299,13 +305,14 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       //    matter, and no load latency is exposed at all;
       //  * otherwise the 8 loads of a column are issued together, then the stores.
 #pragma unroll 1
-      for (int n = 0; n < 16; n++) {
-        const int cw = q + 4 * (n >> 3);          // the consumer warp whose fragment this is
-        const int jc = n & 7;                     // jc = 2 * j + c
+      for (int n = 0; n < 4 * NJ; n++) {
+        const int h = n / (2 * NJ);               // which of the quarter's two consumer warps
+        const int cw = q + 4 * h;                 // the consumer warp whose fragment this is
+        const int jc = n - h * (2 * NJ);          // jc = 2 * j + c
         const int64_t row_base = (int64_t)tm * BM + (cw & 1) * 64 + gid;
-        const int64_t col = (int64_t)tn * BN + (cw >> 1) * 32 + 2 * tig + (jc >> 1) * 8 + (jc & 1);
+        const int64_t col = (int64_t)tn * BN + (cw >> 1) * (8 * NJ) + 2 * tig + (jc >> 1) * 8 + (jc & 1);
         uint32_t v[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + abuf * 256 + n * 16, v);
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + abuf * 256 + h * 128 + jc * 16, v);
         if (col >= p.n) continue;
         if (p.ksplit > 1) {  // raw partial sums; alpha/beta are applied by the reduction pass
           double* Pcol = p.partial + ((int64_t)split * p.n + col) * p.ld_part;
@@ -416,8 +423,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int v = 0; v < 4; v++) {
       if (A_MN) offA[v] = frag_off<true>(wm * 64 + (v >> 1) * 8 + gid, kslot + 2 * (v & 1));
       else      offA[v] = frag_off<false>(wm * 64 + gid, kslot + 2 * (v & 1) + 8 * (v >> 1));
-      if (B_MN) offB[v] = frag_off<true>(wn * 32 + (v >> 1) * 8 + gid, kslot + 2 * (v & 1));
-      else      offB[v] = frag_off<false>(wn * 32 + gid, kslot + 2 * (v & 1) + 8 * (v >> 1));
+      if (B_MN) offB[v] = frag_off<true>(wn * (8 * NJ) + (v >> 1) * 8 + gid, kslot + 2 * (v & 1));
+      else      offB[v] = frag_off<false>(wn * (8 * NJ) + gid, kslot + 2 * (v & 1) + 8 * (v >> 1));
     }
     const uint32_t smem_base = smem_u32(smem);
     // this warp's slot in tensor memory: lane quarter warp % 4, columns (warp / 4) * 128
@@ -434,7 +441,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // pull the C tile into L2 while the main loop runs: thread t covers column t/2, four
         // 128-byte lines of its 128 rows
         const int64_t col = (int64_t)tn * BN + (threadIdx.x >> 1);
-        if (col < p.n) {
+        if (col < p.n && (int)(threadIdx.x >> 1) < BN) {
           const double* cp = p.C + col * p.ldc + (int64_t)tm * BM + (threadIdx.x & 1) * 64;
 #pragma unroll
           for (int qq = 0; qq < 4; qq++)
@@ -442,11 +449,11 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               asm volatile("prefetch.global.L2 [%0];" ::"l"(cp + qq * 16));
         }
       }
-      double acc[8][4][2];
+      double acc[8][NJ][2];
 #pragma unroll
       for (int i = 0; i < 8; i++)
 #pragma unroll
-        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int j = 0; j < NJ; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
       for (int kb = kb0; kb < kb1; kb++) {
         mbar_wait(&full_bar[stage], phase);
@@ -454,7 +461,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const uint32_t sB = sA + A_STAGE_BYTES;
         static_for4([&](auto KS) {
           constexpr int ks = decltype(KS)::value;
-          double a[8], b[4];
+          double a[8], b[NJ];
           static_for8([&](auto I) {
             constexpr int i = decltype(I)::value;
             // MN-major: k adds (2*(ks&1) + 8*(ks>>1)) * 128 bytes, the 8-row group i adds
@@ -462,7 +469,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             if (A_MN) a[i] = lds_f64<(8 * (ks >> 1)) * 128 + (i >> 1) * (BK * 128)>(sA + offA[(i & 1) * 2 + (ks & 1)]);
             else      a[i] = lds_f64<i * 8 * 128>(sA + offA[ks]);
           });
-          static_for4([&](auto J) {
+          static_for_impl<0, NJ>([&](auto J) {
             constexpr int j = decltype(J)::value;
             if (B_MN) b[j] = lds_f64<(8 * (ks >> 1)) * 128 + (j >> 1) * (BK * 128)>(sB + offB[(j & 1) * 2 + (ks & 1)]);
             else      b[j] = lds_f64<j * 8 * 128>(sB + offB[ks]);
@@ -470,7 +477,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int i = 0; i < 8; i++)
 #pragma unroll
-            for (int j = 0; j < 4; j++) dmma884(acc[i][j], a[i], b[j]);
+            for (int j = 0; j < NJ; j++) dmma884(acc[i][j], a[i], b[j]);
         });
         // The stage may only be handed back once every fragment load of this warp has been
         // PERFORMED, not merely issued: ptxas schedules the last loads of the k-block right
@@ -491,7 +498,7 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_wait(&acc_empty[abuf], aphase ^ 1);
       tc_fence_after();
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
+      for (int j = 0; j < NJ; j++) {
         uint32_t v[32];
 #pragma unroll
         for (int c = 0; c < 2; c++)
@@ -533,10 +540,10 @@ __global__ void splitk_reduce_kernel(int64_t m, int64_t n, int ksplit, const dou
   }
 }
 
-template <bool A_MN, bool B_MN>
+template <bool A_MN, bool B_MN, int NJ>
 void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p) {
   static bool attr = false;
-  auto kern = dgemm_dmma_kernel<A_MN, B_MN>;
+  auto kern = dgemm_dmma_kernel<A_MN, B_MN, NJ>;
   if (!attr) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr = true;
@@ -588,6 +595,9 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     }
     return true;
   }
+  // narrow CTA tile (128 x 32) for products with at most 32 columns
+  const bool narrow = n <= 32 && tri == TriFull && !zmode;
+  const int bn = narrow ? 32 : BN;
   CUtensorMap tmA, tmB;
   // operand A as op(A) (m x k): stored m x k (lda) when ta == N, else k x m
   if (a_mn) {
@@ -602,7 +612,7 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     if (!make_tensor_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, B, n, k, ldb * 8, 16, BK,
                             CU_TENSOR_MAP_SWIZZLE_128B)) return false;
   } else {
-    if (!make_tensor_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, B, k, n, ldb * 8, BK, BN,
+    if (!make_tensor_map_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, B, k, n, ldb * 8, BK, bn,
                             CU_TENSOR_MAP_SWIZZLE_128B)) return false;
   }
   GemmParams p;
@@ -610,7 +620,7 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   p.alpha = alpha; p.beta = beta;
   p.C = C; p.ldc = ldc; p.tri = tri;
   p.tiles_m = (int)ceil_div(m, BM);
-  p.tiles_n = (int)ceil_div(n, BN);
+  p.tiles_n = (int)ceil_div(n, bn);
   if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
   p.zmode = zmode;
   p.herm_diag = herm_diag ? 1 : 0;
@@ -642,10 +652,17 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
       }
     }
   }
-  if (a_mn && b_mn) launch<true, true>(ctx, tmA, tmB, p);
-  else if (a_mn && !b_mn) launch<true, false>(ctx, tmA, tmB, p);
-  else if (!a_mn && b_mn) launch<false, true>(ctx, tmA, tmB, p);
-  else launch<false, false>(ctx, tmA, tmB, p);
+  if (narrow) {
+    if (a_mn && b_mn) launch<true, true, 1>(ctx, tmA, tmB, p);
+    else if (a_mn && !b_mn) launch<true, false, 1>(ctx, tmA, tmB, p);
+    else if (!a_mn && b_mn) launch<false, true, 1>(ctx, tmA, tmB, p);
+    else launch<false, false, 1>(ctx, tmA, tmB, p);
+  } else {
+    if (a_mn && b_mn) launch<true, true, 4>(ctx, tmA, tmB, p);
+    else if (a_mn && !b_mn) launch<true, false, 4>(ctx, tmA, tmB, p);
+    else if (!a_mn && b_mn) launch<false, true, 4>(ctx, tmA, tmB, p);
+    else launch<false, false, 4>(ctx, tmA, tmB, p);
+  }
   if (p.ksplit > 1) {
     dim3 g((unsigned)ceil_div(m, 128), (unsigned)(n < 1024 ? n : 1024));
     splitk_reduce_kernel<<<g, 128, 0, ctx.stream>>>(m, n, p.ksplit, p.partial, p.ld_part, alpha,

@@ -438,11 +438,15 @@ void apply_block_reflector(Context& ctx, Side side, Op trans, int64_t m, int64_t
                            QrWork<T>& w, T* C, int64_t ldc) {
   const T onev = one<T>(), zerov = zero<T>(), mone = from_real<T>(-1.0);
   if (side == Left) {
-    // W = V^H C (jb x n); W2 = op(T) W; C -= V W2
-    gemm<T>(ctx, OpC, OpN, jb, n, m, onev, w.V, w.ldv, C, ldc, zerov, w.W, w.ldw);
-    gemm<T>(ctx, trans == OpN ? OpN : OpC, OpN, jb, n, jb, onev, w.Tm, QR_MAX_JB, w.W, w.ldw,
-            zerov, w.W2, w.ldw);
-    gemm<T>(ctx, OpN, OpN, m, n, jb, mone, w.V, w.ldv, w.W2, w.ldw, onev, C, ldc);
+    // With W = V^H C (jb x n) and W2 = op(T) W the update is C -= V W2.  The products are
+    // formed transposed, Wt = W^H = C^H V (n x jb) and W2t = W2^H = Wt op(T)^H, so that the long
+    // reduction over the m rows has the jb <= 32 columns on the N side of the GEMM, where the
+    // narrow 128 x 32 tile applies (with jb rows on the M side 3/4 of a 128-row tile is padding).
+    const int64_t ldt = round_up(n, 16);
+    gemm<T>(ctx, OpC, OpN, n, jb, m, onev, C, ldc, w.V, w.ldv, zerov, w.W, ldt);
+    gemm<T>(ctx, OpN, trans == OpN ? OpC : OpN, n, jb, jb, onev, w.W, ldt, w.Tm, QR_MAX_JB, zerov,
+            w.W2, ldt);
+    gemm<T>(ctx, OpN, OpC, m, n, jb, mone, w.V, w.ldv, w.W2, ldt, onev, C, ldc);
   } else {
     // W = C V (m x jb); W2 = W op(T); C -= W2 V^H
     gemm<T>(ctx, OpN, OpN, m, jb, n, onev, C, ldc, w.V, w.ldv, zerov, w.W, w.ldw);
@@ -461,8 +465,9 @@ QrWork<T> make_work(Context& ctx, int64_t vrows, int64_t w_rows, int64_t w_cols)
   w.Tm = ctx.alloc<T>(QR_MAX_JB * QR_MAX_JB);
   w.Gm = ctx.alloc<T>(QR_MAX_JB * QR_MAX_JB);
   w.ldw = round_up(w_rows, 16);
-  w.W = ctx.alloc<T>(w.ldw * (w_cols > 0 ? w_cols : 1));
-  w.W2 = ctx.alloc<T>(w.ldw * (w_cols > 0 ? w_cols : 1));
+  // (+16 columns: the Left update stores its jb x n workspaces transposed, n rounded up to 16)
+  w.W = ctx.alloc<T>(w.ldw * ((w_cols > 0 ? w_cols : 1) + 16));
+  w.W2 = ctx.alloc<T>(w.ldw * ((w_cols > 0 ? w_cols : 1) + 16));
   return w;
 }
 
