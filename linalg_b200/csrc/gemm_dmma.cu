@@ -235,8 +235,8 @@ __device__ __forceinline__ bool tile_active(const GemmParams& p, int tm, int tn)
   return ((tm * BM) >> 1) <= tn * BN + BN - 1;
 }
 
-// NJ = DMMA tiles per warp along N: 4 -> CTA tile 128 x 128; 1 -> CTA tile 128 x 32 for products
-// with at most 32 columns (W^H = C^H V in QR, Gram matrices), which would otherwise spend 3/4 of
+// NJ = DMMA tiles per warp along N: 4 -> CTA tile 128 x 128; 2 / 1 -> CTA tile 128 x 64 / 128 x 32
+// for products with at most 64 / 32 columns (W^H = C^H V in QR, Gram matrices), which would otherwise spend 3/4 of
 // the tensor work on padding.
 template <bool A_MN, bool B_MN, int NJ>
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -596,8 +596,8 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     return true;
   }
   // narrow CTA tile (128 x 32) for products with at most 32 columns
-  const bool narrow = n <= 32 && tri == TriFull && !zmode;
-  const int bn = narrow ? 32 : BN;
+  const bool narrow = n <= 64 && tri == TriFull && !zmode;
+  const int bn = narrow ? (n <= 32 ? 32 : 64) : BN;
   CUtensorMap tmA, tmB;
   // operand A as op(A) (m x k): stored m x k (lda) when ta == N, else k x m
   if (a_mn) {
@@ -652,11 +652,16 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
       }
     }
   }
-  if (narrow) {
+  if (bn == 32) {
     if (a_mn && b_mn) launch<true, true, 1>(ctx, tmA, tmB, p);
     else if (a_mn && !b_mn) launch<true, false, 1>(ctx, tmA, tmB, p);
     else if (!a_mn && b_mn) launch<false, true, 1>(ctx, tmA, tmB, p);
     else launch<false, false, 1>(ctx, tmA, tmB, p);
+  } else if (bn == 64) {
+    if (a_mn && b_mn) launch<true, true, 2>(ctx, tmA, tmB, p);
+    else if (a_mn && !b_mn) launch<true, false, 2>(ctx, tmA, tmB, p);
+    else if (!a_mn && b_mn) launch<false, true, 2>(ctx, tmA, tmB, p);
+    else launch<false, false, 2>(ctx, tmA, tmB, p);
   } else {
     if (a_mn && b_mn) launch<true, true, 4>(ctx, tmA, tmB, p);
     else if (a_mn && !b_mn) launch<true, false, 4>(ctx, tmA, tmB, p);
