@@ -100,6 +100,7 @@ struct GemmParams {
   int64_t ld_part;
   int zmode;      // 1: rows are interleaved (re, im) parts of a complex matrix (gemm_z.cu)
   int herm_diag;  // zmode only: store 0 in the imaginary part of the diagonal
+  int full_enum;  // masked product, few tiles: enumerate all tiles and skip the masked-out ones
   int use_red;    // beta == 1: accumulate into C with red.global.add instead of load/fma/store
 };
 
@@ -229,10 +230,16 @@ __device__ __forceinline__ void tile_coords(int tri, int t, int tiles_m, int til
 
 // zmode products enumerate all tiles and skip those entirely outside the stored triangle of the
 // COMPLEX matrix (complex row = real row >> 1).
+template <int BN_>
 __device__ __forceinline__ bool tile_active(const GemmParams& p, int tm, int tn) {
-  if (!p.zmode || p.tri == TriFull) return true;
-  if (p.tri == TriLower) return ((tm * BM + BM - 1) >> 1) >= tn * BN;
-  return ((tm * BM) >> 1) <= tn * BN + BN - 1;
+  if (p.tri == TriFull) return true;
+  if (p.zmode) {
+    if (p.tri == TriLower) return ((tm * BM + BM - 1) >> 1) >= tn * BN_;
+    return ((tm * BM) >> 1) <= tn * BN_ + BN_ - 1;
+  }
+  if (!p.full_enum) return true;   // the triangular enumeration only visits active tiles
+  if (p.tri == TriLower) return tm * BM + BM - 1 >= tn * BN_;
+  return tm * BM <= tn * BN_ + BN_ - 1;
 }
 
 // NJ = DMMA tiles per warp along N: 4 -> CTA tile 128 x 128; 2 / 1 -> CTA tile 128 x 64 / 128 x 32
@@ -293,8 +300,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
       const int t = w % num_tiles, split = w / num_tiles;
       int tm, tn;
-      tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
-      if (!tile_active(p, tm, tn)) continue;
+      tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+      if (!tile_active<BN>(p, tm, tn)) continue;
       mbar_wait(&acc_full[abuf], aphase);
       tc_fence_after();
       // 16 chunks (2 consumer warps x 8 columns of C each), rolled: this code runs beside the
@@ -375,8 +382,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
         const int t = w % num_tiles, split = w / num_tiles;
         int tm, tn;
-        tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
-        if (!tile_active(p, tm, tn)) continue;
+        tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+        if (!tile_active<BN>(p, tm, tn)) continue;
         const int m0 = tm * BM, n0 = tn * BN;
         const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
         for (int kb = kb0; kb < kb1; kb++) {
@@ -433,8 +440,8 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
       const int t = w % num_tiles, split = w / num_tiles;
       int tm, tn;
-      tile_coords(p.zmode ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
-      if (!tile_active(p, tm, tn)) continue;
+      tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+      if (!tile_active<BN>(p, tm, tn)) continue;
       const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
 
       if (!beta_zero && p.ksplit == 1) {
@@ -596,8 +603,39 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     return true;
   }
   // narrow CTA tile (128 x 32) for products with at most 32 columns
-  const bool narrow = n <= 64 && tri == TriFull && !zmode;
-  const int bn = narrow ? (n <= 32 ? 32 : 64) : BN;
+  // CTA tile width: 128 unless a narrower tile keeps more SMs busy (few output tiles: the single
+  // SM that owns a 128 x 128 tile needs 2.1 us per 16 k whatever the rest of the machine does) or
+  // the product has at most 64 columns.  Score = fraction of the SMs' time spent on useful tiles
+  // x relative efficiency of the tile shape (fragment loads per DMMA).
+  int bn = BN;
+  if (tri == TriFull && !zmode) {
+    const int sms_ = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+    const int64_t tm_ = ceil_div(m, (int64_t)BM);
+    double best = -1.0;
+    const int cand[3] = {128, 64, 32};
+    const double eff[3] = {1.0, 0.92, 0.8};
+    for (int c = 0; c < 3; c++) {
+      if (cand[c] < 128 && n > 64 && k > 1024) continue;   // long k: split-K / big tiles do better
+      const int64_t tiles = tm_ * ceil_div(n, (int64_t)cand[c]);
+      const int64_t waves = ceil_div(tiles, (int64_t)sms_);
+      const double used = (double)n / (double)(ceil_div(n, (int64_t)cand[c]) * cand[c]);  // padding
+      const double score = (double)tiles / (double)(waves * sms_) * used * eff[c];
+      if (score > best * 1.05) { best = score; bn = cand[c]; }
+    }
+  }
+  // masked (SYRK-style) products with few tiles: narrow tiles too, enumerating every tile and
+  // skipping those outside the stored triangle (the triangular enumeration needs square tiles)
+  bool full_enum = false;
+  if (tri != TriFull && !zmode) {
+    const int sms_ = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+    const int64_t tm_ = ceil_div(m, (int64_t)BM);
+    const int64_t t128 = tri == TriLower ? tri_tile_count((int)tm_, (int)ceil_div(n, (int64_t)BN))
+                                         : tri_tile_count((int)ceil_div(n, (int64_t)BN), (int)tm_);
+    if (t128 * 2 <= sms_ && k <= 1024) {
+      bn = t128 * 4 <= sms_ ? 32 : 64;
+      full_enum = true;
+    }
+  }
   CUtensorMap tmA, tmB;
   // operand A as op(A) (m x k): stored m x k (lda) when ta == N, else k x m
   if (a_mn) {
@@ -623,10 +661,11 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   p.tiles_n = (int)ceil_div(n, bn);
   if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
   p.zmode = zmode;
+  p.full_enum = full_enum ? 1 : 0;
   p.herm_diag = herm_diag ? 1 : 0;
   static const bool no_red = getenv("LA_B200_NO_RED") != nullptr;
   p.use_red = no_red ? 0 : 1;
-  if (zmode) p.num_tiles = p.tiles_m * p.tiles_n;
+  if (zmode || full_enum) p.num_tiles = p.tiles_m * p.tiles_n;
   else if (tri == TriLower) p.num_tiles = tri_tile_count(p.tiles_m, p.tiles_n);
   else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
   else p.num_tiles = p.tiles_m * p.tiles_n;
