@@ -216,7 +216,8 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   // interchanges of the columns left and right of it, U12 = L11^-1 A12 and the rank-NB
   // trailing update (where nearly all flops are).  Keeping the interchanges per panel bounds
   // the serial part of laswp's net-permutation set-up to NB steps.
-  const int64_t NB = k >= 8192 ? 512 : (k >= 2048 ? 256 : 128);
+  static const int nb_env = getenv("LA_B200_LU_NB") ? atoi(getenv("LA_B200_LU_NB")) : 0;
+  const int64_t NB = nb_env > 0 ? nb_env : (k >= 8192 ? 512 : (k >= 2048 ? 256 : 128));
   // Look-ahead: once the columns of the NEXT panel have received their update, that panel is
   // factored on a side stream (a chain of latency-bound leaf launches that needs only a few
   // SMs) while the main stream finishes the trailing update on the remaining SMs.
