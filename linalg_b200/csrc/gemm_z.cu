@@ -110,7 +110,9 @@ bool gemm_dmma_z(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, zc
                  zcomplex* C, int64_t ldc, int tri, bool herm_diag) {
   if (m <= 0 || n <= 0) return true;
   if (k <= 0 || is_zero(alpha)) return false;
-  if ((double)m * (double)n * (double)k < 48.0 * 48.0 * 48.0) return false;
+  // small products: the two packing passes cost more than they save; the SIMT kernel takes them
+  static const double simt_below = getenv("LA_B200_Z_SIMT_BELOW") ? atof(getenv("LA_B200_Z_SIMT_BELOW")) : 256.0;
+  if ((double)m * (double)n * (double)k < simt_below * simt_below * simt_below) return false;
   if (m > (int64_t)1 << 29 || n > (int64_t)1 << 29 || k > (int64_t)1 << 29) return false;
   Arena::Mark mk = ctx.arena.mark();
   const int64_t lda2 = round_up(2 * m, 16), ldb2 = round_up(2 * k, 16);
