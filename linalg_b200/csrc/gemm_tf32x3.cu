@@ -190,8 +190,11 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int kblocks = (int)((p.k + SK_ - 1) / SK_);
 
+  // warps 0-3 (producer, MMA issuer, TMEM allocator) hand registers to the two epilogue
+  // warpgroups, which keep a 128-float running sum per thread
   if (warp == 0) {
     // ===================== TMA producer =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (lane == 0) {
       tma_prefetch_desc(&tmAhi); tma_prefetch_desc(&tmAlo);
       tma_prefetch_desc(&tmBhi); tma_prefetch_desc(&tmBlo);
@@ -217,6 +220,7 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_tf32(SM_, SN_);
       int stage = 0, as = 0;
@@ -253,8 +257,11 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
         }
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");   // warps 2, 3: the whole warpgroup must
+  } else {
     // ===================== epilogue: TMEM -> registers -> C =====================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
     const int q = warp & 3;                 // TMEM lane quarter of this warp
     const int half = (warp - 4) >> 2;       // which half of the column chunks it drains
     int as = 0;
@@ -265,42 +272,51 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
       s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
       if (s_tile_skipped(p.tri, tm, tn)) continue;
       const int64_t row = (int64_t)tm * SM_ + q * 32 + lane;
+      // The tensor core truncates when it accumulates, so k is cut into chunks of 512 terms; the
+      // chunk sums are added in FP32 (round to nearest) in REGISTERS — this thread owns one row
+      // and four of the eight 32-column groups of the tile — and C is touched once per tile.
+      // (Summing the chunks into C through memory cost 64 GB of extra traffic at N = 16384.)
+      float run[SN_ / 64][32];
       for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
         const bool first = kb0 == 0;
         mbar_wait(&tfull_bar[as], aphase);
         tc_fence_after();
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * SN_);
-#pragma unroll 1
-        for (int cc = half; cc < SN_ / 32; cc += 2) {
+#pragma unroll
+        for (int ci = 0; ci < SN_ / 64; ci++) {
           uint32_t v[32];
-          tmem_ld32(tbase + cc * 32, v);
-          const int64_t col0 = (int64_t)tn * SN_ + cc * 32;
-          if (row < p.m) {
-            float* dst0 = p.C + row + col0 * p.ldc;
-            const bool need_c = !first || !beta_zero;
-            float cold[32];
-            if (need_c) {  // all loads first: 32 independent requests in flight
+          tmem_ld32(tbase + (half + 2 * ci) * 32, v);
 #pragma unroll
-              for (int j = 0; j < 32; j++)
-                cold[j] = (col0 + j < p.n) ? dst0[(int64_t)j * p.ldc] : 0.f;
-            }
-#pragma unroll
-            for (int j = 0; j < 32; j++) {
-              const int64_t col = col0 + j;
-              if (col >= p.n) break;
-              if (p.tri == TriLower && row < col) continue;
-              if (p.tri == TriUpper && row > col) continue;
-              float r = p.alpha * __uint_as_float(v[j]);
-              if (!first) r += cold[j];                     // later chunks accumulate into C
-              else if (!beta_zero) r = fmaf(p.beta, cold[j], r);
-              dst0[(int64_t)j * p.ldc] = r;
-            }
-          }
+          for (int j = 0; j < 32; j++)
+            run[ci][j] = first ? __uint_as_float(v[j]) : run[ci][j] + __uint_as_float(v[j]);
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[as]);
+        if (lane == 0) mbar_arrive(&tempty_bar[as]);   // the accumulator is free again
         if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+      if (row < p.m) {
+#pragma unroll
+        for (int ci = 0; ci < SN_ / 64; ci++) {
+          const int64_t col0 = (int64_t)tn * SN_ + (half + 2 * ci) * 32;
+          float* dst0 = p.C + row + col0 * p.ldc;
+          float cold[32];
+          if (!beta_zero) {  // all loads first: 32 independent requests in flight
+#pragma unroll
+            for (int j = 0; j < 32; j++)
+              cold[j] = (col0 + j < p.n) ? dst0[(int64_t)j * p.ldc] : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 32; j++) {
+            const int64_t col = col0 + j;
+            if (col >= p.n) break;
+            if (p.tri == TriLower && row < col) continue;
+            if (p.tri == TriUpper && row > col) continue;
+            float r = p.alpha * run[ci][j];
+            if (!beta_zero) r = fmaf(p.beta, cold[j], r);
+            dst0[(int64_t)j * p.ldc] = r;
+          }
+        }
       }
     }
   }
