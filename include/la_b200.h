@@ -183,7 +183,10 @@ void zungqr_(const int* m, const int* n, const int* k, void* a, const int* lda, 
  * pointer, dimensions are 64-bit (N = 65536 overflows the reference's Int32 element count,
  * src/matrix/general_matrix.cr:26), and the work is only ENQUEUED on `stream` (a
  * cudaStream_t; NULL = legacy default stream).  `info` is a device int written by the
- * kernels.  Scratch memory comes from a per-thread device arena that grows on first use.
+ * kernels.  Scratch memory comes from a per-thread, per-device arena that grows on first use
+ * and is reused by that thread's next call: a call on another stream than the thread's previous
+ * call is ordered behind it with an event (calls on ONE stream, the normal case, are ordered
+ * anyway); different host threads have separate scratch and run concurrently.
  * Complex scalars are passed as pointers to {re, im}.  Return value: 0, or -i if argument i
  * is invalid (nothing is enqueued).  `X` in the names below is s, d or z.
  */
@@ -227,7 +230,8 @@ LA_B200_DECL_DEV(z, void)
  * the library holds until exit.  m, n <= 32768, else -100 is returned (message on stderr) and
  * nothing is enqueued.  The first call on a device does a one-time set-up and should precede
  * any stream capture.  All calls share the array: order them on one stream; calls that can
- * overlap on the GPU race.  -101: set-up failed. */
+ * overlap on the GPU race.  -101: set-up failed.  -102: a scratch request did not fit the
+ * array (nothing is allocated in that case either). */
 int la_b200_dgetrf_dev_noalloc(int64_t m, int64_t n, double* a, int64_t lda, int* ipiv, int* info,
                                void* stream);
 
@@ -237,6 +241,11 @@ const char* la_b200_version(void);
 int64_t la_b200_workspace_bytes(void);
 /* 1 if the last f64/z/f32 GEMM issued by this thread used the tensor-core path */
 int la_b200_last_gemm_path(void);
+/* Give the device workspaces back to the driver: the calling thread's device-API arenas and
+ * those of every idle context of the host-pointer symbols (the pool otherwise keeps each
+ * arena at its high-water mark, the analogue of the reference's WORK_POOL,
+ * src/linalg/workpool.cr:73).  Synchronises the devices concerned; returns the bytes freed. */
+int64_t la_b200_release_workspace(void);
 
 #ifdef __cplusplus
 }

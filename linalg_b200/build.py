@@ -27,7 +27,6 @@ NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nv
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
           "-Xptxas", "-v" if os.environ.get("LA_PTXAS_V") else "-O3"]
-DEFINES = ["-DLA_HAVE_DMMA_F64", "-DLA_HAVE_DMMA_Z", "-DLA_HAVE_TF32X3"]
 
 
 def _sources():
@@ -40,16 +39,7 @@ def _headers_mtime():
 
 
 def _defines():
-    """Enable a fast-path define only when its implementation file exists."""
-    have = []
-    if (CSRC / "gemm_dmma.cu").exists():
-        have.append("-DLA_HAVE_DMMA_F64")
-    if (CSRC / "gemm_z.cu").exists():
-        have.append("-DLA_HAVE_DMMA_Z")
-    if (CSRC / "gemm_tf32x3.cu").exists():
-        have.append("-DLA_HAVE_TF32X3")
-    have += os.environ.get("LA_EXTRA_DEFINES", "").split()
-    return have
+    return os.environ.get("LA_EXTRA_DEFINES", "").split()
 
 
 def _compile(src: Path, force: bool, verbose: bool, hdr_mtime: float, defines) -> Path:

@@ -11,8 +11,18 @@ namespace {
 struct DevCall {
   Context* ctx;
   Arena::Mark mk;
-  explicit DevCall(void* stream) : ctx(thread_context((cudaStream_t)stream)), mk(ctx->arena.mark()) {}
-  ~DevCall() { ctx->arena.release(mk); }
+  // The per-thread context's scratch is shared by every call of this thread on this device:
+  // a call on a different stream than the previous one is ordered after it with an event.
+  explicit DevCall(void* stream) : ctx(thread_context((cudaStream_t)stream)), mk(ctx->arena.mark()) {
+    if (ctx->has_last && ctx->last_stream != ctx->stream)
+      LA_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->tail_ev, 0));
+  }
+  ~DevCall() {
+    ctx->arena.release(mk);
+    LA_CUDA_CHECK(cudaEventRecord(ctx->tail_ev, ctx->stream));
+    ctx->last_stream = ctx->stream;
+    ctx->has_last = true;
+  }
 };
 
 template <typename T>
@@ -240,5 +250,7 @@ int64_t la_b200_workspace_bytes(void) {
 }
 
 int la_b200_last_gemm_path(void) { return last_gemm_path(); }
+
+int64_t la_b200_release_workspace(void) { return (int64_t)release_workspaces(); }
 
 }  // extern "C"

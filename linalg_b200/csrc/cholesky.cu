@@ -283,11 +283,11 @@ template <typename T>
 void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
   LA_CUDA_CHECK(cudaMemsetAsync(d_info, 0, sizeof(int), ctx.stream));
   if (n <= 0) return;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_set;
+  if (attr_set.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(potf2_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)potf2_smem_bytes<T>()));
-    attr_set = true;
+    attr_set.mark(ctx.device);
   }
   static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
   if (n < 4096 || la_disabled || !ctx.allow_side_stream) {

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cmath>
+#include <atomic>
 
 namespace la {
 
@@ -144,6 +145,20 @@ template <typename T> LA_HD T apply_conj(T a, bool c) { return c ? conj_(a) : a;
       abort();                                                                       \
     }                                                                                \
   } while (0)
+
+// One-time set-up that CUDA keeps PER DEVICE (cudaFuncSetAttribute and the like): a flag per
+// device ordinal, safe to test from any number of host threads.  Two threads that race on the
+// first use both run the (idempotent) set-up; devices beyond the table repeat it every call.
+struct DeviceOnce {
+  static constexpr int kMax = 64;
+  std::atomic<bool> done[kMax] = {};
+  bool pending(int dev) const {
+    return dev < 0 || dev >= kMax || !done[dev].load(std::memory_order_acquire);
+  }
+  void mark(int dev) {
+    if (dev >= 0 && dev < kMax) done[dev].store(true, std::memory_order_release);
+  }
+};
 
 LA_HD int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 LA_HD int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -19,6 +19,7 @@ void* Arena::alloc(size_t bytes) {
       return p;
     }
   }
+  if (fixed) throw ArenaExhausted{bytes};
   size_t sz = bytes > kMinBlock ? bytes : kMinBlock;
   if (!blocks.empty() && blocks.back().size * 2 > sz && bytes <= blocks.back().size * 2)
     sz = blocks.back().size * 2;
@@ -48,7 +49,7 @@ void Arena::release(Mark m) {
   if (m.nblocks > 0) blocks[m.nblocks - 1].used = m.used_last;
   // If several blocks exist and everything is released, coalesce into one large
   // block next time by dropping the small ones.
-  if (m.nblocks == 0 && blocks.size() > 1) {
+  if (m.nblocks == 0 && blocks.size() > 1 && !fixed) {
     size_t want = 0;
     for (auto& b : blocks) want += b.size;
     for (auto& b : blocks) cudaFree(b.base);
@@ -65,6 +66,7 @@ void Arena::release(Mark m) {
 }
 
 void Arena::free_all() {
+  if (fixed) return;               // caller-provided blocks
   for (auto& b : blocks) cudaFree(b.base);
   blocks.clear();
   total = 0;
@@ -117,17 +119,38 @@ void release_context(Context* c) {
   g_free.push_back(c);
 }
 
+static thread_local std::vector<Context*> per_device;
+
 Context* thread_context(cudaStream_t stream) {
-  static thread_local std::vector<Context*> per_device;
   int dev = 0;
   LA_CUDA_CHECK(cudaGetDevice(&dev));
   if ((int)per_device.size() <= dev) per_device.resize(dev + 1, nullptr);
   if (!per_device[dev]) {
     per_device[dev] = new Context();
     init_context(per_device[dev], false);
+    LA_CUDA_CHECK(cudaEventCreateWithFlags(&per_device[dev]->tail_ev, cudaEventDisableTiming));
   }
   per_device[dev]->stream = stream;
   return per_device[dev];
+}
+
+size_t release_workspaces() {
+  size_t freed = 0;
+  auto drop = [&](Context* c) {
+    if (!c) return;
+    int cur = 0;
+    LA_CUDA_CHECK(cudaGetDevice(&cur));
+    if (cur != c->device) LA_CUDA_CHECK(cudaSetDevice(c->device));
+    LA_CUDA_CHECK(cudaDeviceSynchronize());
+    freed += c->arena.total;
+    c->arena.free_all();
+    if (c->side) { freed += c->side->arena.total; c->side->arena.free_all(); }
+    if (cur != c->device) LA_CUDA_CHECK(cudaSetDevice(cur));
+  };
+  for (Context* c : per_device) drop(c);
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (Context* c : g_free) drop(c);
+  return freed;
 }
 
 Context* side_context(Context& c) {

@@ -14,11 +14,16 @@
 
 namespace la {
 
+struct ArenaExhausted { size_t bytes; };
+
 struct Arena {
   struct Block { char* base; size_t size; size_t used; };
   std::vector<Block> blocks;
   struct Mark { size_t nblocks; size_t used_last; };
   void* alloc(size_t bytes);       // 256-byte aligned; grows with cudaMalloc on demand
+  // fixed = true: the arena consists of caller-provided blocks only and never calls cudaMalloc;
+  // a request that does not fit throws ArenaExhausted (caught by the entry point that set it).
+  bool fixed = false;
   Mark mark() const;
   void release(Mark m);            // stack discipline
   void free_all();
@@ -41,6 +46,12 @@ struct Context {
   int sm_limit = 0;                // > 0: persistent kernels use at most this many CTAs
   bool allow_side_stream = true;   // look-ahead may create `side` (a stream, events, an arena)
   Context* side = nullptr;         // second context for work overlapped with the main stream
+  // Device-pointer API: the stream the previous call ran on and an event recorded at its end.
+  // A call that arrives on another stream first waits for that event, because the scratch of
+  // this context (arena, LU exchange area) is reused from call to call.
+  cudaStream_t last_stream = nullptr;
+  bool has_last = false;
+  cudaEvent_t tail_ev = nullptr;
   // Host-pointer shims only: called by a factorisation, in stream order, each time a block of
   // the result has reached its final value (Cholesky: block column / block row [c0, c1)), so
   // that the shim can send it home while the factorisation goes on.
@@ -63,6 +74,10 @@ struct ContextLease {
 Context* thread_context(cudaStream_t stream);
 
 void* pinned_scratch(Context& c, size_t bytes);
+
+// Free the device workspace of the calling thread's device-API contexts and of every pooled
+// (idle) context; returns the number of bytes given back.  Contexts in use are not touched.
+size_t release_workspaces();
 
 // Lazily created companion context (own high-priority stream and arena) for look-ahead.
 Context* side_context(Context& c);

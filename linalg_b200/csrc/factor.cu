@@ -21,6 +21,7 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
               int* d_info);
 int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes);
 void lu_panel_prepare(Context& ctx);
+void lu_panel_begin(Context& ctx, int64_t m);
 
 namespace {
 
@@ -133,11 +134,11 @@ template <typename T>
 void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
                 const int* d_ipiv, bool reverse) {
   if (n <= 0 || k2 <= k1) return;
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(laswp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (LASWP_MAX_MAP + LASWP_CHUNK) * (int)sizeof(int)));
-    attr = true;
+    attr.mark(ctx.device);
   }
   Arena::Mark mk = ctx.arena.mark();
   int* lists = ctx.alloc<int>(4 * LASWP_CHUNK);
@@ -240,8 +241,10 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     (void)side->arena.alloc(1 << 20);
     side->arena.release(smk);
     lu_panel_prepare(*side);
+    lu_panel_begin(*side, m);
     LA_CUDA_CHECK(cudaStreamSynchronize(side->stream));
   }
+  lu_panel_begin(ctx, m);
   bool panel_done = false;  // panel of the current j0 already factored (on the side stream)?
   for (int64_t j0 = 0; j0 < k; j0 += NB) {
     const int64_t jb = NB < k - j0 ? NB : k - j0;

@@ -549,11 +549,11 @@ __global__ void splitk_reduce_kernel(int64_t m, int64_t n, int ksplit, const dou
 
 template <bool A_MN, bool B_MN, int NJ>
 void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p) {
-  static bool attr = false;
+  static DeviceOnce attr;
   auto kern = dgemm_dmma_kernel<A_MN, B_MN, NJ>;
-  if (!attr) {
+  if (attr.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr = true;
+    attr.mark(ctx.device);
   }
   int tiles = p.num_tiles * p.ksplit;
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;

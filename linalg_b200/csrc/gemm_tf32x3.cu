@@ -341,11 +341,11 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   // below this the packing passes and the 128x256 tiles do not pay off
   if ((double)m * (double)n * (double)k < 256.0 * 256.0 * 256.0) return false;
   if (m > (int64_t)1 << 30 || n > (int64_t)1 << 30 || k > (int64_t)1 << 30) return false;
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, S_SMEM_BYTES));
-    attr = true;
+    attr.mark(ctx.device);
   }
   Arena::Mark mk = ctx.arena.mark();
   const int64_t ldk = round_up(k, 32);

@@ -25,10 +25,12 @@
 //  * All calls share the one array and it keeps what the previous call left in it.  Calls are
 //    safe back to back on one stream; two calls that can overlap on the GPU (different streams
 //    or host threads without ordering between them) race on the scratch and give wrong results.
-//  * Nothing has to be cleared between calls: the panel kernel's exchange packets carry a
-//    sequence number that only ever grows (kept per device on the host), so packets left by an
-//    earlier call can never be mistaken for current ones, and the interchange lists are fully
-//    rewritten before they are read.  The array starts zeroed when the module is loaded.
+//  * The caller has nothing to clear between calls: each call first wipes the pivot-exchange
+//    part of the array on its stream (packets left by the previous call would otherwise carry
+//    tags the new call uses again), and the interchange lists are fully rewritten before they
+//    are read.
+//  * The array is all the scratch there is.  Should a code path ever ask for more than fits, the
+//    call returns -102 with a message instead of falling back to cudaMalloc.
 #include "shim_common.h"
 #include <mutex>
 
@@ -87,6 +89,7 @@ NoAllocDevice* setup_current_device() {
   d.ctx.sm_count = sms;
   la::lu_panel_adopt_exchange(d.ctx, base, d.panel_state);
   // the rest of the array becomes the (only) block of this context's bump arena
+  d.ctx.arena.fixed = true;          // never grows: a request that does not fit is an error
   d.ctx.arena.blocks.reserve(1);
   d.ctx.arena.blocks.push_back(
       la::Arena::Block{(char*)base + xch, LA_B200_NOALLOC_SCRATCH_BYTES - xch, 0});
@@ -112,7 +115,16 @@ extern "C" int la_b200_dgetrf_dev_noalloc(int64_t m, int64_t n, double* a, int64
   if (!d) return -101;
   d->ctx.stream = (cudaStream_t)stream;
   la::Arena::Mark mk = d->ctx.arena.mark();
-  la::getrf<double>(d->ctx, m, n, a, lda, ipiv, info);
+  int rc = 0;
+  try {
+    la::getrf<double>(d->ctx, m, n, a, lda, ipiv, info);
+  } catch (const la::ArenaExhausted& e) {
+    fprintf(stderr,
+            "la_b200: dgetrf_dev_noalloc: a scratch request of %zu bytes does not fit the fixed "
+            "%d-byte array; nothing was allocated, the factorisation is incomplete\n",
+            e.bytes, LA_B200_NOALLOC_SCRATCH_BYTES);
+    rc = -102;
+  }
   d->ctx.arena.release(mk);
-  return 0;
+  return rc;
 }

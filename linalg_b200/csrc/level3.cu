@@ -279,12 +279,12 @@ void trsm_rec(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, i
       if (trsm_base_dmma_f64(ctx, side, uplo, op, diag, m, n, alpha, A, lda, B, ldb)) return;
     }
     constexpr int TRSM_NT = TrsmCfg<T>::NT;
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    if (attr.pending(ctx.device)) {
       LA_CUDA_CHECK(cudaFuncSetAttribute(trsm_base_kernel<T>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)trsm_smem_bytes<T>()));
-      attr = true;
+      attr.mark(ctx.device);
     }
     unsigned g = (unsigned)ceil_div(nvec, TRSM_NT);
     trsm_base_kernel<T><<<g, TRSM_NT, trsm_smem_bytes<T>(), ctx.stream>>>(side == Right, uplo == Lower, (int)op,

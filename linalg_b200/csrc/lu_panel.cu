@@ -13,8 +13,10 @@
 //   * all CTAs derive the same winner (max |a|, ties -> smallest row index = i?amax's "first
 //     maximal element"), the two owners swap rows in place, everyone scales and updates its
 //     rows and folds the arg-max of the next column into the same pass.
-// Buffers are double-buffered by column parity; tags grow monotonically across launches, so
-// the exchange area (persistent per context) never needs clearing.
+// Buffers are double-buffered by column parity; tags grow monotonically from launch to launch
+// within one factorisation; every factorisation clears the area and restarts the sequence
+// (lu_panel_begin), so a call enqueues the same work whatever ran before it and the 32-bit
+// sequence cannot wrap.
 // Bytes per column step (algorithmic): (jb-j) * rows * sizeof(T) read+written in SHARED memory;
 // HBM traffic is one read and one write of the panel per launch: 2*m*jb*sizeof(T).
 #include "la_internal.h"
@@ -378,6 +380,15 @@ void lu_panel_adopt_exchange(Context& ctx, void* device_mem, void* state_storage
 // Make sure the context owns its exchange area (allocates on first use).
 void lu_panel_prepare(Context& ctx) { (void)panel_state(ctx); }
 
+// Start of a factorisation of an m-row matrix on ctx.stream: stale packets of earlier calls are
+// wiped (in stream order) and the launch sequence restarts, so tags never repeat within a call.
+void lu_panel_begin(Context& ctx, int64_t m) {
+  if (m <= LU_NT) return;          // single-CTA leaves exchange nothing
+  LuPanelState* st = panel_state(ctx);
+  LA_CUDA_CHECK(cudaMemsetAsync(st->xch, 0, sizeof(LuExchange), ctx.stream));
+  st->seq = 64;
+}
+
 // Rows per thread needed for an m-row panel (a power of two; 0: too tall even for the narrowest
 // leaf).  One row per thread while the panel fits sm_count CTAs of LU_NT rows.
 static int lu_rows_per_thread(Context& ctx, int64_t m, int max_jb) {
@@ -398,12 +409,12 @@ int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
 template <typename T, int R>
 static void lu_panel_launch(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv,
                             int64_t row0, int* d_info) {
-  static bool attr = false;
-  if (!attr) {
+  static DeviceOnce attr;
+  if (attr.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T, R>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)LU_SMEM_TOTAL));
-    attr = true;
+    attr.mark(ctx.device);
   }
   LuPanelState* st = panel_state(ctx);
   constexpr int JBM = MaxJb<T>::N / R;

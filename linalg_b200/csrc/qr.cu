@@ -411,13 +411,13 @@ void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
 }
 
 template <typename T>
-void ensure_attrs() {
-  static bool done = false;
-  if (!done) {
+void ensure_attrs(Context& ctx) {
+  static DeviceOnce done;
+  if (done.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(qr_panel_kernel<T>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)QR_SMEM_BUDGET));
-    done = true;
+    done.mark(ctx.device);
   }
 }
 
@@ -477,7 +477,7 @@ template <typename T>
 void geqrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau) {
   const int64_t k = m < n ? m : n;
   if (k <= 0) return;
-  ensure_attrs<T>();
+  ensure_attrs<T>(ctx);
   Arena::Mark mk = ctx.arena.mark();
   QrWork<T> w = make_work<T>(ctx, m, QR_MAX_JB, n);
   // panels too tall for the shared-memory kernel go through the streaming kernel, which holds

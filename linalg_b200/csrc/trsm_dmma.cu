@@ -209,11 +209,11 @@ bool trsm_base_dmma_f64(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, in
   } else {
     constexpr int W = 8;
     constexpr size_t smem = sizeof(double) * (128 * 129 + 128 * TB);
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    if (attr.pending(ctx.device)) {
       LA_CUDA_CHECK(cudaFuncSetAttribute(trsm_dmma_kernel<128, W>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr = true;
+      attr.mark(ctx.device);
     }
     const unsigned grid = (unsigned)ceil_div(nvec, (int64_t)W * TGROUPS * 8);
     trsm_dmma_kernel<128, W><<<grid, W * 32, smem, ctx.stream>>>(

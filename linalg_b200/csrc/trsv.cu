@@ -242,13 +242,13 @@ bool trsv_small(Context& ctx, Uplo uplo, Op op, Diag diag, int64_t n, int64_t nr
   const int64_t nb = ceil_div(n, (int64_t)TV_RB);
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
   const int64_t G = nb < sms ? nb : sms;
-  static bool attr = false;
+  static DeviceOnce attr;
   const size_t smem = sizeof(T) * ((size_t)TV_RB * (TV_RB + 1) + 2 * TV_RB * TV_MAXRHS +
                                    4 * TV_RB * TV_MAXRHS);
-  if (!attr) {
+  if (attr.pending(ctx.device)) {
     LA_CUDA_CHECK(cudaFuncSetAttribute(trsv_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    attr = true;
+    attr.mark(ctx.device);
   }
   Arena::Mark mk = ctx.arena.mark();
   const size_t npk = (size_t)nb * TV_RB * TV_MAXRHS * W;

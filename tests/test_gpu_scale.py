@@ -177,3 +177,38 @@ def test_trsm_wide_tensor_core_base_case(side, uplo, op, diag, na):
                  dev.UNIT if diag == "U" else dev.NON_UNIT, nvec, na, 2.0, T, na, X, nvec)
         res = X.T @ M - 2.0 * B.T
     assert res.abs().max().item() < 1e-11
+
+
+def test_device_api_calls_on_two_streams_do_not_share_scratch_in_flight():
+    """One host thread, two streams: every device-API call reuses the thread's scratch arena
+    (hi/lo operand packs of the 3xTF32 product, LU exchange area), so a call on another stream
+    must be ordered behind the previous one.  Alternating streams without any host-side
+    synchronisation has to give the results of the serial run, bit for bit."""
+    import torch
+    from linalg_b200 import dev, ffi
+    n = 2048
+    g = torch.Generator(device="cuda").manual_seed(5)
+    mats = [torch.rand((n, n), dtype=torch.float32, device="cuda", generator=g) for _ in range(4)]
+    lus = [torch.rand((n, n), dtype=torch.float64, device="cuda", generator=g) for _ in range(2)]
+
+    def run(streams):
+        outs = [torch.zeros((n, n), dtype=torch.float32, device="cuda") for _ in range(4)]
+        facs = [x.clone() for x in lus]
+        piv = [torch.zeros(n, dtype=torch.int32, device="cuda") for _ in range(2)]
+        info = torch.zeros(1, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        for rep in range(3):
+            for i in range(4):
+                with torch.cuda.stream(streams[i % len(streams)]):
+                    dev.gemm(ffi.NO_TRANS, ffi.TRANS, n, n, n, 1.0, mats[i], n, mats[(i + 1) % 4], n,
+                             0.0, outs[i], n)
+        for i in range(2):
+            with torch.cuda.stream(streams[i % len(streams)]):
+                dev.getrf(n, n, facs[i], n, piv[i], info)
+        torch.cuda.synchronize()
+        return outs + facs + piv
+
+    serial = run([torch.cuda.current_stream()])
+    mixed = run([torch.cuda.Stream(), torch.cuda.Stream()])
+    for a, b in zip(serial, mixed):
+        assert torch.equal(a, b)

@@ -69,3 +69,37 @@ def test_noalloc_getrf_refuses_sizes_beyond_its_limit():
     assert rc == -100
     rc = getrf_noalloc(-1, 4, dummy.data_ptr(), 1, ipiv.data_ptr(), info.data_ptr(), None)
     assert rc == -1
+
+
+def test_noalloc_getrf_leaves_device_memory_untouched():
+    """The point of the entry point is that the driver's free-memory figure does not move: all
+    operands are created first, one call warms the device up (module load, kernel attributes),
+    and from then on cudaMemGetInfo must report the same free bytes after calls of several
+    shapes — including an odd leading dimension, which takes the library's non-TMA product."""
+    import torch
+    _, getrf_noalloc = _bind()
+    rng = np.random.default_rng(7)
+    cases = []
+    for m, n, lda in [(1024, 1024, 1024), (2049, 1500, 2051), (777, 1300, 777), (4096, 4096, 4096)]:
+        a = np.zeros((n, lda))
+        a[:, :m] = rng.random((n, m))
+        cases.append((m, n, lda, a[:, :m].T.copy(), torch.from_numpy(a).cuda(),
+                      torch.zeros(min(m, n), dtype=torch.int32, device="cuda"),
+                      torch.zeros(1, dtype=torch.int32, device="cuda")))
+    stream = torch.cuda.current_stream().cuda_stream
+    warm = cases[0][4].clone()
+    assert getrf_noalloc(1024, 1024, warm.data_ptr(), 1024, cases[0][5].data_ptr(),
+                         cases[0][6].data_ptr(), C.c_void_p(stream)) == 0
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for m, n, lda, _, a, ipiv, info in cases:
+        assert getrf_noalloc(m, n, a.data_ptr(), lda, ipiv.data_ptr(), info.data_ptr(),
+                             C.c_void_p(stream)) == 0
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, f"device free memory moved by {free0 - free1} bytes"
+    from oracle import checks
+    for m, n, lda, a0, a, ipiv, info in cases:
+        assert int(info.item()) == 0
+        lu = a.cpu().numpy()[:, :m].T
+        assert checks.lu_residual(a0, lu, ipiv.cpu().numpy()) <= TOL
