@@ -199,6 +199,30 @@ int la_b200_dgemm_dev(int transa, int transb, int64_t m, int64_t n, int64_t k, d
 int la_b200_zgemm_dev(int transa, int transb, int64_t m, int64_t n, int64_t k, const void* alpha,
                       const void* a, int64_t lda, const void* b, int64_t ldb, const void* beta,
                       void* c, int64_t ldc, void* stream);
+/* C <- alpha*op(A)*op(B) + beta*C restricted to a block staircase: for the multi-GPU
+ * factorisations (no counterpart in the reference, which has no distributed path).
+ * C is the LOCAL part of a block-cyclic matrix: its rows [i*nb, (i+1)*nb) are global block
+ * row_first + i*row_step, its columns [j*nb, (j+1)*nb) global block col_first + j*col_step;
+ * only the blocks whose global row block >= global column block are computed (the trailing
+ * update of a lower Cholesky on a process grid).  Extra error codes: -14 .. -18 for nb,
+ * row_first, row_step, col_first, col_step. */
+int la_b200_sgemm_stair_dev(int transa, int transb, int64_t m, int64_t n, int64_t k, float alpha,
+                            const float* a, int64_t lda, const float* b, int64_t ldb, float beta,
+                            float* c, int64_t ldc, int64_t nb, int64_t row_first, int64_t row_step,
+                            int64_t col_first, int64_t col_step, void* stream);
+int la_b200_dgemm_stair_dev(int transa, int transb, int64_t m, int64_t n, int64_t k, double alpha,
+                            const double* a, int64_t lda, const double* b, int64_t ldb,
+                            double beta, double* c, int64_t ldc, int64_t nb, int64_t row_first,
+                            int64_t row_step, int64_t col_first, int64_t col_step, void* stream);
+int la_b200_zgemm_stair_dev(int transa, int transb, int64_t m, int64_t n, int64_t k,
+                            const void* alpha, const void* a, int64_t lda, const void* b,
+                            int64_t ldb, const void* beta, void* c, int64_t ldc, int64_t nb,
+                            int64_t row_first, int64_t row_step, int64_t col_first,
+                            int64_t col_step, void* stream);
+/* The calling thread's later device-API calls run their persistent kernels on at most `sms`
+ * SMs (0 = all), leaving the rest to kernels of other streams (communication beside a long
+ * product); returns the previous limit. */
+int la_b200_set_sm_limit(int sms);
 #define LA_B200_DECL_DEV(X, T)                                                                    \
   int la_b200_##X##trsm_dev(int side, int uplo, int transa, int diag, int64_t m, int64_t n,       \
                             const void* alpha, const T* a, int64_t lda, T* b, int64_t ldb,        \
@@ -207,6 +231,10 @@ int la_b200_zgemm_dev(int transa, int transb, int64_t m, int64_t n, int64_t k, c
                             int64_t lda, double beta, T* c, int64_t ldc, void* stream);           \
   int la_b200_##X##getrf_dev(int64_t m, int64_t n, T* a, int64_t lda, int* ipiv, int* info,       \
                              void* stream);                                                       \
+  /* rows k (k1 <= k < k2, 0-based) of the m x n matrix swapped with rows ipiv[k]-1, in that  \
+     order: the ?laswp step inside ?getrf/?getrs, exported for the multi-GPU LU */               \
+  int la_b200_##X##laswp_dev(int64_t m, int64_t n, T* a, int64_t lda, int64_t k1, int64_t k2,     \
+                             const int* ipiv, void* stream);                                      \
   int la_b200_##X##getrs_dev(int trans, int64_t n, int64_t nrhs, const T* a, int64_t lda,         \
                              const int* ipiv, T* b, int64_t ldb, void* stream);                   \
   int la_b200_##X##potrf_dev(int uplo, int64_t n, T* a, int64_t lda, int* info, void* stream);    \

@@ -43,6 +43,32 @@ int d_gemm(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A,
 }
 
 template <typename T>
+int d_gemm_stair(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A, int64_t lda,
+                 const T* B, int64_t ldb, T beta, T* C, int64_t ldc, int64_t nb, int64_t row_first,
+                 int64_t row_step, int64_t col_first, int64_t col_step, void* stream) {
+  if (!valid_op(ta)) return -1;
+  if (!valid_op(tb)) return -2;
+  if (m < 0) return -3;
+  if (n < 0) return -4;
+  if (k < 0) return -5;
+  const int64_t ar = ta == OpN ? m : k, br = tb == OpN ? k : n;
+  if (lda < (ar > 1 ? ar : 1)) return -8;
+  if (ldb < (br > 1 ? br : 1)) return -10;
+  if (ldc < (m > 1 ? m : 1)) return -13;
+  if (nb < 1) return -14;
+  if (row_first < 0) return -15;
+  if (row_step < 1) return -16;
+  if (col_first < 0) return -17;
+  if (col_step < 1) return -18;
+  DevCall c(stream);
+  StairMask mk;
+  mk.nb = nb; mk.row_first = row_first; mk.row_step = row_step;
+  mk.col_first = col_first; mk.col_step = col_step;
+  gemm_stair<T>(*c.ctx, (Op)ta, (Op)tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, mk);
+  return 0;
+}
+
+template <typename T>
 int d_trsm(int side, int uplo, int ta, int diag, int64_t m, int64_t n, const void* alpha,
            const T* A, int64_t lda, T* B, int64_t ldb, void* stream) {
   if (!valid_side(side)) return -1;
@@ -82,6 +108,18 @@ int d_getrf(int64_t m, int64_t n, T* A, int64_t lda, int* ipiv, int* info, void*
   if (lda < (m > 1 ? m : 1)) return -4;
   DevCall c(stream);
   getrf<T>(*c.ctx, m, n, A, lda, ipiv, info);
+  return 0;
+}
+template <typename T>
+int d_laswp(int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, const int* ipiv,
+            void* stream) {
+  if (m < 0) return -1;
+  if (n < 0) return -2;
+  if (lda < (m > 1 ? m : 1)) return -4;
+  if (k1 < 0 || k1 > m) return -5;
+  if (k2 < k1 || k2 > m) return -6;
+  DevCall c(stream);
+  laswp_rows<T>(*c.ctx, m, n, A, lda, k1, k2, ipiv, false);
   return 0;
 }
 template <typename T>
@@ -190,6 +228,10 @@ using namespace la;
                              void* stream) {                                                      \
     return d_getrf<T>(m, n, (T*)a, lda, ipiv, info, stream);                                      \
   }                                                                                               \
+  int la_b200_##X##laswp_dev(int64_t m, int64_t n, VT* a, int64_t lda, int64_t k1, int64_t k2,    \
+                             const int* ipiv, void* stream) {                                     \
+    return d_laswp<T>(m, n, (T*)a, lda, k1, k2, ipiv, stream);                                    \
+  }                                                                                               \
   int la_b200_##X##getrs_dev(int trans, int64_t n, int64_t nrhs, const VT* a, int64_t lda,        \
                              const int* ipiv, VT* b, int64_t ldb, void* stream) {                 \
     return d_getrs<T>(trans, n, nrhs, (const T*)a, lda, ipiv, (T*)b, ldb, stream);                \
@@ -236,6 +278,38 @@ int la_b200_zgemm_dev(int ta, int tb, int64_t m, int64_t n, int64_t k, const voi
   return d_gemm<zcomplex>(ta, tb, m, n, k, *(const zcomplex*)alpha, (const zcomplex*)a, lda,
                           (const zcomplex*)b, ldb, *(const zcomplex*)beta, (zcomplex*)c, ldc,
                           stream);
+}
+
+int la_b200_sgemm_stair_dev(int ta, int tb, int64_t m, int64_t n, int64_t k, float alpha,
+                            const float* a, int64_t lda, const float* b, int64_t ldb, float beta,
+                            float* c, int64_t ldc, int64_t nb, int64_t row_first, int64_t row_step,
+                            int64_t col_first, int64_t col_step, void* stream) {
+  return d_gemm_stair<float>(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nb, row_first,
+                             row_step, col_first, col_step, stream);
+}
+int la_b200_dgemm_stair_dev(int ta, int tb, int64_t m, int64_t n, int64_t k, double alpha,
+                            const double* a, int64_t lda, const double* b, int64_t ldb,
+                            double beta, double* c, int64_t ldc, int64_t nb, int64_t row_first,
+                            int64_t row_step, int64_t col_first, int64_t col_step, void* stream) {
+  return d_gemm_stair<double>(ta, tb, m, n, k, alpha, a, lda, b, ldb, beta, c, ldc, nb, row_first,
+                              row_step, col_first, col_step, stream);
+}
+int la_b200_zgemm_stair_dev(int ta, int tb, int64_t m, int64_t n, int64_t k, const void* alpha,
+                            const void* a, int64_t lda, const void* b, int64_t ldb,
+                            const void* beta, void* c, int64_t ldc, int64_t nb, int64_t row_first,
+                            int64_t row_step, int64_t col_first, int64_t col_step, void* stream) {
+  return d_gemm_stair<zcomplex>(ta, tb, m, n, k, *(const zcomplex*)alpha, (const zcomplex*)a, lda,
+                                (const zcomplex*)b, ldb, *(const zcomplex*)beta, (zcomplex*)c, ldc,
+                                nb, row_first, row_step, col_first, col_step, stream);
+}
+
+// Persistent kernels of the calling thread's device-API context use at most `sms` CTAs
+// (0 = all): leaves SMs free for communication kernels that must run beside a long product.
+int la_b200_set_sm_limit(int sms) {
+  Context* c = thread_context(nullptr);
+  const int old = c->sm_limit;
+  c->sm_limit = sms > 0 && sms < c->sm_count ? sms : 0;
+  return old;
 }
 
 LA_DEV_SYMBOLS(s, float, float)

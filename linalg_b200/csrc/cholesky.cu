@@ -333,12 +333,13 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
     potrf_twolevel<T>(*side, uplo, kb2, at(K1, K1), lda, d_info, K1);
     LA_CUDA_CHECK(cudaEventRecord(side->ev[0], side->stream));
     if (r3 > 0) {
+      const int keep = ctx.sm_limit;
       ctx.sm_limit = ctx.sm_count - side_sms;
       if (L)
         herk<T>(ctx, Lower, OpN, r3, kb, -1.0, at(K1 + kb2, K0), lda, 1.0, at(K1 + kb2, K1 + kb2), lda);
       else
         herk<T>(ctx, Upper, OpC, r3, kb, -1.0, at(K0, K1 + kb2), lda, 1.0, at(K1 + kb2, K1 + kb2), lda);
-      ctx.sm_limit = 0;
+      ctx.sm_limit = keep;
     }
     LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, side->ev[0], 0));
   }

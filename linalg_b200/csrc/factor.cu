@@ -12,9 +12,6 @@
 namespace la {
 
 // =========================================================================== LU
-template <typename T>
-void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
-                const int* d_ipiv, bool reverse = false);
 // lu_panel.cu
 template <typename T>
 void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
@@ -300,10 +297,11 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       int64_t c1 = (int64_t)(panel_ms * flop_per_ms / (2.0 * (double)mr * (double)jb));
       c1 = round_up(c1 > 0 ? c1 : 1, (int64_t)128);
       if (c1 + 1024 >= rest) c1 = rest;
+      const int keep = ctx.sm_limit;
       ctx.sm_limit = ctx.sm_count - side_sms;
       gemm<T>(ctx, OpN, OpN, mr, c1, jb, from_real<T>(-1.0), A21, lda, A12 + jb1 * lda, lda,
               one<T>(), A22 + jb1 * lda, lda);
-      ctx.sm_limit = 0;
+      ctx.sm_limit = keep;
       TL(ctx.stream);
       LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, side->ev[0], 0));
       if (c1 < rest)
@@ -365,6 +363,8 @@ void trtrs(Context& ctx, Uplo uplo, Op trans, Diag diag, int64_t n, int64_t nrhs
 
 #define LA_INST_FACTOR(T)                                                                         \
   template void laswp<T>(Context&, int64_t, T*, int64_t, int64_t, int64_t, const int*, bool);     \
+  template void laswp_rows<T>(Context&, int64_t, int64_t, T*, int64_t, int64_t, int64_t,          \
+                              const int*, bool);                                                  \
   template void getrf<T>(Context&, int64_t, int64_t, T*, int64_t, int*, int*);                    \
   template void getrs<T>(Context&, Op, int64_t, int64_t, const T*, int64_t, const int*, T*,       \
                          int64_t);                                                                \

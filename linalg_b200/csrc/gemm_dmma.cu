@@ -102,6 +102,8 @@ struct GemmParams {
   int herm_diag;  // zmode only: store 0 in the imaginary part of the diagonal
   int full_enum;  // masked product, few tiles: enumerate all tiles and skip the masked-out ones
   int use_red;    // beta == 1: accumulate into C with red.global.add instead of load/fma/store
+  // block-staircase mask (StairMask, la_internal.h); st_nb == 0: none
+  int st_nb, st_rf, st_rs, st_cf, st_cs;
 };
 
 __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
@@ -232,6 +234,15 @@ __device__ __forceinline__ void tile_coords(int tri, int t, int tiles_m, int til
 // COMPLEX matrix (complex row = real row >> 1).
 template <int BN_>
 __device__ __forceinline__ bool tile_active(const GemmParams& p, int tm, int tn) {
+  if (p.st_nb) {
+    // last row of the tile against its first column, both as GLOBAL block indices (the first
+    // column's block is the smallest of the tile, the last row's block the largest)
+    int64_t r = (int64_t)tm * BM + BM - 1;
+    if (r >= p.m) r = p.m - 1;
+    const int64_t rb = p.st_rf + (r / p.st_nb) * p.st_rs;
+    const int64_t cb = p.st_cf + ((int64_t)tn * BN_ / p.st_nb) * p.st_cs;
+    return rb >= cb;
+  }
   if (p.tri == TriFull) return true;
   if (p.zmode) {
     if (p.tri == TriLower) return ((tm * BM + BM - 1) >> 1) >= tn * BN_;
@@ -572,7 +583,9 @@ bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, 
 
 bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
                       const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
-                      double* C, int64_t ldc, int tri, int zmode, bool herm_diag) {
+                      double* C, int64_t ldc, int tri, int zmode, bool herm_diag,
+                      const StairMask* stair) {
+  if (stair && (tri != TriFull || zmode || stair->nb % BN != 0)) return false;
   if (ta == OpC) ta = OpT;
   if (tb == OpC) tb = OpT;
   if (m <= 0 || n <= 0) return true;
@@ -594,7 +607,7 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
       const double* Ac = a_mn ? A + l0 * lda : A + l0;
       const double* Bc = b_mn ? B + l0 * ldb : B + l0;
       if (!gemm_dmma_f64_ex(ctx, ta, tb, m, n, kc, alpha, Ac, lda, Bc, ldb, l0 == 0 ? beta : 1.0, C,
-                            ldc, tri, zmode, herm_diag)) {
+                            ldc, tri, zmode, herm_diag, stair)) {
         if (l0 == 0) return false;
         fprintf(stderr, "la_b200: internal error: k-chunked GEMM fell back after the first chunk\n");
         abort();
@@ -608,7 +621,7 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   // the product has at most 64 columns.  Score = fraction of the SMs' time spent on useful tiles
   // x relative efficiency of the tile shape (fragment loads per DMMA).
   int bn = BN;
-  if (tri == TriFull && !zmode) {
+  if (tri == TriFull && !zmode && !stair) {
     const int sms_ = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
     const int64_t tm_ = ceil_div(m, (int64_t)BM);
     double best = -1.0;
@@ -661,11 +674,16 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   p.tiles_n = (int)ceil_div(n, bn);
   if ((int64_t)p.tiles_m * p.tiles_n > (int64_t)1 << 30) return false;
   p.zmode = zmode;
-  p.full_enum = full_enum ? 1 : 0;
+  p.full_enum = (full_enum || stair) ? 1 : 0;
+  p.st_nb = stair ? (int)stair->nb : 0;
+  p.st_rf = stair ? (int)stair->row_first : 0;
+  p.st_rs = stair ? (int)stair->row_step : 0;
+  p.st_cf = stair ? (int)stair->col_first : 0;
+  p.st_cs = stair ? (int)stair->col_step : 0;
   p.herm_diag = herm_diag ? 1 : 0;
   static const bool no_red = getenv("LA_B200_NO_RED") != nullptr;
   p.use_red = no_red ? 0 : 1;
-  if (zmode || full_enum) p.num_tiles = p.tiles_m * p.tiles_n;
+  if (zmode || full_enum || stair) p.num_tiles = p.tiles_m * p.tiles_n;
   else if (tri == TriLower) p.num_tiles = tri_tile_count(p.tiles_m, p.tiles_n);
   else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
   else p.num_tiles = p.tiles_m * p.tiles_n;
@@ -680,7 +698,8 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     const int kblocks = (int)ceil_div(k, BK);
     const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
     // (contexts that must not allocate — allow_side_stream == false — never split)
-    if (ctx.allow_side_stream && tri == TriFull && p.num_tiles * 4 <= sms && kblocks >= 128) {
+    if (ctx.allow_side_stream && tri == TriFull && !stair && p.num_tiles * 4 <= sms &&
+        kblocks >= 128) {
       int S = sms / p.num_tiles;
       if (S > kblocks / 32) S = kblocks / 32;
       if (S >= 2) {

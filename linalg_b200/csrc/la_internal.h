@@ -18,6 +18,19 @@ void gemm(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T alpha, 
           int64_t lda, const T* B, int64_t ldb, T beta, T* C, int64_t ldc, int tri = TriFull,
           bool herm_diag = false);
 
+// Block-staircase mask for products on block-cyclic LOCAL matrices (multi-GPU factorisations):
+// local rows [i*nb, (i+1)*nb) of C are global block row_first + i*row_step, local columns
+// [j*nb, (j+1)*nb) global block col_first + j*col_step; only blocks whose global row block is
+// >= the global column block are computed (whole blocks: no element mask inside them).
+struct StairMask {
+  int64_t nb = 0;
+  int64_t row_first = 0, row_step = 1, col_first = 0, col_step = 1;
+};
+template <typename T>
+void gemm_stair(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A,
+                int64_t lda, const T* B, int64_t ldb, T beta, T* C, int64_t ldc,
+                const StairMask& mask);
+
 // Which GEMM path the calling thread used last (0 = SIMT, 1 = DMMA f64, 2 = DMMA complex,
 // 3 = 3xTF32 tcgen05); written by the dispatcher, read by la_b200_last_gemm_path().
 int& last_gemm_path();
@@ -35,7 +48,8 @@ bool gemm_dmma_f64(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, 
 // same kernel with the complex-interleaved row mask / diagonal rule used by gemm_z.cu
 bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
                       const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
-                      double* C, int64_t ldc, int tri, int zmode, bool herm_diag);
+                      double* C, int64_t ldc, int tri, int zmode, bool herm_diag,
+                      const StairMask* stair = nullptr);
 bool gemm_dmma_z(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, zcomplex alpha,
                  const zcomplex* A, int64_t lda, const zcomplex* B, int64_t ldb, zcomplex beta,
                  zcomplex* C, int64_t ldc, int tri, bool herm_diag);
@@ -88,6 +102,12 @@ void symmetrize(Context& ctx, bool herm, Uplo uplo, int64_t n, const T* A, int64
 template <typename T>
 void laswp(Context& ctx, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, const int* d_ipiv,
            bool reverse);
+
+// the same interchanges as one net permutation per 1024 pivots (parallel over rows and columns);
+// m = number of rows of A (upper bound of the pivot indices)
+template <typename T>
+void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2,
+                const int* d_ipiv, bool reverse = false);
 
 // factorizations / solves
 // Width of the block columns / rows in which potrf reports its result final through

@@ -57,6 +57,45 @@ void gemm<float>(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   gemm_simt<float>(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri, false);
 }
 
+// Product restricted to the blocks on or below a block staircase (la_internal.h: StairMask).
+// FP64 on TMA-legal operands: ONE launch of the tensor-core kernel that skips the tiles above the
+// staircase; otherwise one product per block column, from its first active row block down.
+template <typename T>
+void gemm_stair(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T alpha, const T* A,
+                int64_t lda, const T* B, int64_t ldb, T beta, T* C, int64_t ldc,
+                const StairMask& mask) {
+  if (m <= 0 || n <= 0) return;
+  if constexpr (std::is_same<T, double>::value) {
+    if (gemm_dmma_f64_ex(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, TriFull, 0,
+                         false, &mask)) {
+      last_gemm_path() = 1;
+      return;
+    }
+  }
+  const int64_t nb = mask.nb;
+  for (int64_t j0 = 0; j0 < n; j0 += nb) {
+    const int64_t jb = nb < n - j0 ? nb : n - j0;
+    const int64_t cb = mask.col_first + (j0 / nb) * mask.col_step;
+    // first local row block whose global index reaches cb
+    int64_t li = 0;
+    if (cb > mask.row_first) li = ceil_div(cb - mask.row_first, mask.row_step);
+    const int64_t i0 = li * nb;
+    if (i0 >= m) continue;
+    const T* Ab = ta == OpN ? A + i0 : A + i0 * lda;
+    const T* Bb = tb == OpN ? B + j0 * ldb : B + j0;
+    gemm<T>(ctx, ta, tb, m - i0, jb, k, alpha, Ab, lda, Bb, ldb, beta, C + i0 + j0 * ldc, ldc);
+  }
+}
+template void gemm_stair<float>(Context&, Op, Op, int64_t, int64_t, int64_t, float, const float*,
+                                int64_t, const float*, int64_t, float, float*, int64_t,
+                                const StairMask&);
+template void gemm_stair<double>(Context&, Op, Op, int64_t, int64_t, int64_t, double,
+                                 const double*, int64_t, const double*, int64_t, double, double*,
+                                 int64_t, const StairMask&);
+template void gemm_stair<zcomplex>(Context&, Op, Op, int64_t, int64_t, int64_t, zcomplex,
+                                   const zcomplex*, int64_t, const zcomplex*, int64_t, zcomplex,
+                                   zcomplex*, int64_t, const StairMask&);
+
 template <typename T>
 void herk(Context& ctx, Uplo uplo, Op trans, int64_t n, int64_t k, double alpha, const T* A,
           int64_t lda, double beta, T* C, int64_t ldc) {

@@ -58,6 +58,33 @@ def gemm(ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, Cm, ldc):
              _stream()), "gemm")
 
 
+def gemm_stair(ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, Cm, ldc, nb, row_first, row_step,
+               col_first, col_step):
+    """Product restricted to the blocks on/below a block staircase (la_b200_Xgemm_stair_dev)."""
+    L = _LET[A.dtype]
+    al, k1 = _scalar(L, alpha)
+    be, k2 = _scalar(L, beta)
+    sc = _p if L == "z" else (C.c_float if L == "s" else C.c_double)
+    f = _fn(f"la_b200_{L}gemm_stair_dev", [_int, _int, _i64, _i64, _i64, sc, _p, _i64, _p, _i64, sc,
+                                           _p, _i64, _i64, _i64, _i64, _i64, _i64, _p])
+    _check(f(ta, tb, m, n, k, al, A.data_ptr(), lda, B.data_ptr(), ldb, be, Cm.data_ptr(), ldc, nb,
+             row_first, row_step, col_first, col_step, _stream()), "gemm_stair")
+
+
+def set_sm_limit(sms: int) -> int:
+    """Persistent kernels of this thread's later calls use at most `sms` SMs (0 = all)."""
+    f = lib().la_b200_set_sm_limit
+    f.argtypes = [_int]
+    f.restype = _int
+    return int(f(int(sms)))
+
+
+def laswp(m, n, A, lda, k1, k2, ipiv):
+    L = _LET[A.dtype]
+    f = _fn(f"la_b200_{L}laswp_dev", [_i64, _i64, _p, _i64, _i64, _i64, _p, _p])
+    _check(f(m, n, A.data_ptr(), lda, k1, k2, ipiv.data_ptr(), _stream()), "laswp")
+
+
 def getrf(m, n, A, lda, ipiv, info):
     L = _LET[A.dtype]
     f = _fn(f"la_b200_{L}getrf_dev", [_i64, _i64, _p, _i64, _p, _p, _p])

@@ -4,13 +4,21 @@ The reference has no distributed path; what shards naturally is stated in SURVEY
 
   * GEMM: B and C split by block columns over the ranks, A replicated, no data-path collective
     (`shard_columns`, used by bench.py).
-  * Cholesky: block columns dealt round-robin to the ranks (1-D block-cyclic).  Per block column
-    k the owner factors the diagonal block and solves the panel below it, the panel is
-    broadcast (NCCL over NVLink on GPUs), and every rank applies the rank-nb update to the block
-    columns it owns (`potrf_block_cyclic`).  One broadcast of (N - k*nb) x nb elements per step
-    is the only exchange.
-  * Tall-skinny least squares: rows split over the ranks, local QR of [A_i | b_i], all-gather of
-    the small R factors, QR of the stack, triangular solve (`lstsq_tsqr`).
+  * Cholesky (`potrf_block_cyclic`): 2-D block-cyclic layout on a P x Q process grid (block
+    (i, j) lives on grid position (i mod P, j mod Q)).  Per block column k: the owner of the
+    diagonal block factors it and sends it down its grid column; the P ranks of that column solve
+    their rows of the panel; every rank then receives exactly the two pieces of the panel it
+    needs — the rows of its own row blocks (broadcast along its grid row) and the rows of its own
+    column blocks (broadcast along its grid column) — and applies ONE rank-nb update to its local
+    trailing matrix, restricted to the blocks on or below the diagonal (staircase-masked product).
+    Look-ahead: the ranks that hold block column k+1 update that column first, factor it and
+    start its exchange on a second stream before they touch the rest of the trailing matrix.
+  * LU (`getrf_block_cyclic`): block columns dealt cyclically to the ranks (a 1 x Q grid), so a
+    panel and its pivot search stay on one GPU; the factored panel and its pivots are broadcast,
+    every rank applies the interchanges, the triangular solve and the rank-nb update to its own
+    columns, with the same look-ahead.
+  * Tall-skinny least squares (`lstsq_tsqr`): rows split over the ranks, local QR of [A_i | b_i],
+    all-gather of the small R factors, QR of the stack, triangular solve.
 
 All matrices are column-major and are held as torch tensors in "transposed" orientation: a
 tensor `t` of shape (cols, rows) with stride (ld, 1) is the matrix whose element (r, c) is
@@ -19,6 +27,8 @@ the product path) or any object with the same methods (the CPU tests pass an ora
 and the gloo backend, so that the sharding / exchange logic runs without a GPU).
 """
 from __future__ import annotations
+
+import contextlib
 
 import torch
 import torch.distributed as dist
@@ -29,26 +39,142 @@ def shard_columns(n: int, world: int, rank: int):
     return (n * rank) // world, (n * (rank + 1)) // world
 
 
-def owner_of_block(k: int, world: int) -> int:
-    return k % world
+def default_grid_shape(world: int):
+    """P x Q with P <= Q, P | Q: 1x1, 1x2, 2x2, 2x4 for 1, 2, 4, 8 ranks."""
+    p = 1
+    while (p * 2) * (p * 2) <= world and world % (p * 2) == 0 and (world // (p * 2)) % (p * 2) == 0:
+        p *= 2
+    return p, world // p
 
 
-def local_block_index(k: int, world: int) -> int:
-    return k // world
+class Grid:
+    """P x Q process grid over the ranks of `torch.distributed`'s world (row-major: rank = p*Q+q)
+    with one sub-group per grid row and per grid column.  Every rank must construct it (group
+    creation is collective).  Requires P | Q, so that the rows of a panel that grid column q needs
+    all sit in ONE grid row (q mod P)."""
+
+    def __init__(self, P: int | None = None, Q: int | None = None, comm_ctas: int = 0):
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        if P is None or Q is None:
+            P, Q = default_grid_shape(self.world)
+        if P * Q != self.world or Q % P != 0:
+            raise ValueError(f"grid {P} x {Q} does not fit {self.world} ranks (need P*Q = world, P | Q)")
+        self.P, self.Q = P, Q
+        self.p, self.q = self.rank // Q, self.rank % Q
+        self.row_group = self.col_group = None
+        if self.world > 1:
+            opts = None
+            if comm_ctas > 0 and dist.get_backend() == "nccl":
+                # keep the collectives on a few SMs: they run beside the trailing update
+                opts = dist.ProcessGroupNCCL.Options()
+                opts.config.max_ctas = comm_ctas
+                opts.config.min_ctas = 1
+            for pp in range(P):
+                g = dist.new_group([pp * Q + qq for qq in range(Q)], pg_options=opts) if Q > 1 else None
+                if pp == self.p:
+                    self.row_group = g
+            for qq in range(Q):
+                g = dist.new_group([pp * Q + qq for pp in range(P)], pg_options=opts) if P > 1 else None
+                if qq == self.q:
+                    self.col_group = g
+
+    def rank_of(self, p: int, q: int) -> int:
+        return p * self.Q + q
+
+
+class BlockCyclic:
+    """Index arithmetic of an n x n matrix in nb x nb blocks on a Grid (n must be a multiple of
+    nb).  The local matrix of grid position (p, q) holds the row blocks p, p+P, ... and the column
+    blocks q, q+Q, ... in increasing order: local shape mloc x nloc, column-major."""
+
+    def __init__(self, n: int, nb: int, grid: Grid):
+        if n % nb != 0:
+            raise ValueError("block-cyclic drivers need n to be a multiple of nb")
+        self.n, self.nb, self.grid = n, nb, grid
+        self.nblk = n // nb
+        self.row_blocks = list(range(grid.p, self.nblk, grid.P))
+        self.col_blocks = list(range(grid.q, self.nblk, grid.Q))
+        self.mloc = len(self.row_blocks) * nb
+        self.nloc = len(self.col_blocks) * nb
+
+    def lrow_from(self, g: int) -> int:
+        """Local row offset of the first owned row block with global index >= g."""
+        li = max(0, -(-(g - self.grid.p) // self.grid.P))
+        return min(li * self.nb, self.mloc)
+
+    def lcol_from(self, g: int) -> int:
+        lj = max(0, -(-(g - self.grid.q) // self.grid.Q))
+        return min(lj * self.nb, self.nloc)
+
+    def global_rows(self) -> torch.Tensor:
+        """Global row index of every local row (int64, CPU)."""
+        return torch.cat([torch.arange(i * self.nb, (i + 1) * self.nb) for i in self.row_blocks]) \
+            if self.row_blocks else torch.zeros(0, dtype=torch.int64)
+
+    def global_cols(self) -> torch.Tensor:
+        return torch.cat([torch.arange(j * self.nb, (j + 1) * self.nb) for j in self.col_blocks]) \
+            if self.col_blocks else torch.zeros(0, dtype=torch.int64)
+
+
+class _SideStream:
+    """The exchange runs on a second CUDA stream next to the compute stream; on CPU tensors
+    (gloo tests) every method is a no-op and the collectives simply block."""
+
+    def __init__(self, device: torch.device):
+        self.cuda = device.type == "cuda"
+        self.stream = torch.cuda.Stream(device) if self.cuda else None
+
+    def section(self):
+        """`with side.section():` work issued inside is ordered after everything already on the
+        compute stream and runs on the side stream."""
+        if not self.cuda:
+            return contextlib.nullcontext()
+        self.stream.wait_stream(torch.cuda.current_stream())
+        return torch.cuda.stream(self.stream)
+
+    def mark(self):
+        """Inside a section: an event the compute stream can wait for."""
+        if not self.cuda:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
+        return ev
+
+    def wait(self, ev):
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
 
 
 class DevOps:
-    """Local arithmetic on CUDA tensors through the device-resident C API."""
+    """Local arithmetic on CUDA tensors through the device-resident C API.
 
-    def __init__(self):
+    `reserve_sms` > 0: the long products of the trailing updates leave that many SMs free, so
+    that the collectives of the NEXT panel (kernels on another stream) can run beside them.
+    """
+
+    def __init__(self, reserve_sms: int = 0):
         from . import dev
         self.dev = dev
         self.info = torch.zeros(1, dtype=torch.int32, device="cuda")
         self.first = torch.zeros(1, dtype=torch.int32, device="cuda")   # first failing column
+        self.reserve_sms = reserve_sms
+        self.sm_count = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
 
     @staticmethod
     def _ld(t):
         return t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1)
+
+    @contextlib.contextmanager
+    def _limited(self):
+        if self.reserve_sms > 0:
+            old = self.dev.set_sm_limit(self.sm_count - self.reserve_sms)
+            try:
+                yield
+            finally:
+                self.dev.set_sm_limit(old)
+        else:
+            yield
 
     def potrf_lower(self, a, k0=0):                # a: n x n view at global offset k0
         n = a.shape[0]
@@ -61,10 +187,39 @@ class DevOps:
         self.dev.trsm(self.dev.RIGHT, self.dev.LOWER, self.dev.CONJ_TRANS, self.dev.NON_UNIT, m, n,
                       1.0, tri, self._ld(tri), b, self._ld(b))
 
+    def trsm_left_lower_unit(self, tri, b):        # b <- tri^-1 b ; tri: m x m unit lower, b: m x n
+        m, n = b.shape[1], b.shape[0]
+        self.dev.trsm(self.dev.LEFT, self.dev.LOWER, self.dev.NO_TRANS, self.dev.UNIT, m, n, 1.0,
+                      tri, self._ld(tri), b, self._ld(b))
+
     def gemm_nt_sub(self, c, a, b):                # c <- c - a * b^H ; a: m x k, b: n x k, c: m x n
         m, n, k = c.shape[1], c.shape[0], a.shape[0]
-        self.dev.gemm(self.dev.NO_TRANS, self.dev.CONJ_TRANS, m, n, k, -1.0, a, self._ld(a), b,
-                      self._ld(b), 1.0, c, self._ld(c))
+        with self._limited():
+            self.dev.gemm(self.dev.NO_TRANS, self.dev.CONJ_TRANS, m, n, k, -1.0, a, self._ld(a), b,
+                          self._ld(b), 1.0, c, self._ld(c))
+
+    def gemm_nn_sub(self, c, a, b):                # c <- c - a * b ; a: m x k, b: k x n, c: m x n
+        m, n, k = c.shape[1], c.shape[0], a.shape[0]
+        with self._limited():
+            self.dev.gemm(self.dev.NO_TRANS, self.dev.NO_TRANS, m, n, k, -1.0, a, self._ld(a), b,
+                          self._ld(b), 1.0, c, self._ld(c))
+
+    def gemm_nt_sub_stair(self, c, a, b, nb, row_first, row_step, col_first, col_step):
+        """c <- c - a * b^H on the blocks whose global row block >= global column block."""
+        m, n, k = c.shape[1], c.shape[0], a.shape[0]
+        with self._limited():
+            self.dev.gemm_stair(self.dev.NO_TRANS, self.dev.CONJ_TRANS, m, n, k, -1.0, a, self._ld(a),
+                                b, self._ld(b), 1.0, c, self._ld(c), nb, row_first, row_step,
+                                col_first, col_step)
+
+    def getrf(self, a, ipiv, row0=0):              # in-place LU of the m x n view, pivots 1-based
+        m, n = a.shape[1], a.shape[0]
+        self.dev.getrf(m, n, a, self._ld(a), ipiv, self.info)
+        self.first = torch.where((self.first == 0) & (self.info != 0), self.info + row0, self.first)
+
+    def laswp(self, a, ipiv, k1, k2):              # rows k of a swapped with ipiv[k]-1, k1 <= k < k2
+        m, n = a.shape[1], a.shape[0]
+        self.dev.laswp(m, n, a, self._ld(a), k1, k2, ipiv)
 
     def info_value(self):
         return int(self.first.item())
@@ -81,76 +236,175 @@ class DevOps:
                        b, self._ld(b), self.info)
 
 
-def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, group=None):
-    """In-place lower Cholesky of an n x n SPD matrix distributed by block columns.
+def _reduce_info(info: int, device) -> int:
+    """Smallest non-zero LAPACK info over the ranks."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return info
+    big = 2 ** 31 - 1
+    t = torch.tensor([info if info > 0 else big], dtype=torch.int64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    info = int(t.item())
+    return 0 if info == big else info
 
-    `a_local` has shape (nloc * nb_cols, n): the block columns k with k % world == rank, in
-    increasing k, each nb columns wide (the last one may be narrower), full height n.  On return
-    the lower triangle of every owned block column holds L.  Returns LAPACK's info (0 = ok).
 
-    Look-ahead: as soon as panel k has arrived, the owner of block column k+1 updates that column
-    alone, factors it and posts its broadcast (asynchronous, on NCCL's stream), and only then do
-    all ranks apply panel k to the rest of their columns — the next panel travels while the
-    tensor cores are busy, and no rank ever waits for a barrier, only for the panel it needs.
+def potrf_block_cyclic(a_local: torch.Tensor, n: int, nb: int, ops, grid: Grid | None = None):
+    """In-place lower Cholesky of an n x n SPD matrix in 2-D block-cyclic layout.
+
+    `a_local` has shape (nloc, mloc) — see `BlockCyclic`: the local column-major mloc x nloc
+    matrix of this rank's row blocks x column blocks.  On return the blocks on or below the
+    diagonal hold L (blocks above it, and the upper triangles of the diagonal blocks, are not
+    meaningful).  Returns LAPACK's info (0, or the 1-based index of the first bad pivot).
     """
-    world = dist.get_world_size(group) if dist.is_initialized() else 1
-    rank = dist.get_rank(group) if dist.is_initialized() else 0
-    nblk = (n + nb - 1) // nb
-    # column offset of each owned block column inside a_local
-    offs, pos = {}, 0
-    for k in range(nblk):
-        if owner_of_block(k, world) == rank:
-            offs[k] = pos
-            pos += min(nb, n - k * nb)
-    bufs = [torch.empty(nb * n, dtype=a_local.dtype, device=a_local.device) for _ in range(2)]
+    grid = grid or Grid()
+    lay = BlockCyclic(n, nb, grid)
+    P, Q, p, q = grid.P, grid.Q, grid.p, grid.q
+    nblk, mloc, nloc = lay.nblk, lay.mloc, lay.nloc
+    assert tuple(a_local.shape) == (nloc, mloc), (tuple(a_local.shape), (nloc, mloc))
+    dt, dv = a_local.dtype, a_local.device
+    side = _SideStream(dv)
+    # the two pieces of a panel this rank needs, double buffered by the parity of k
+    row_bufs = [torch.empty(nb * max(mloc, 1), dtype=dt, device=dv) for _ in range(2)]
+    col_bufs = [torch.empty(nb * max(nloc, 1), dtype=dt, device=dv) for _ in range(2)]
+    diag_bufs = [torch.empty((nb, nb), dtype=dt, device=dv) for _ in range(2)]
+    src_p = q % P            # the grid row whose panel rows contain this rank's column blocks
 
-    def factor_and_post(k):
-        """Owner: factor block column k (all updates applied) and stage it; all: post the
-        broadcast.  Returns (panel view (kb, n - k0) with ld = n - k0, pending work or None)."""
+    def post(k):
+        """Factor block column k (every earlier update applied) and start its exchange.
+        Returns (lrow, lcol, event): lrow = panel rows of my row blocks > k as an (nb, mr) view,
+        lcol = panel rows of my column blocks > k as an (nb, nc) view."""
+        pk, qk = k % P, k % Q
+        r0, c0 = lay.lrow_from(k + 1), lay.lcol_from(k + 1)
+        mr, nc = mloc - r0, nloc - c0
+        lrow = row_bufs[k % 2][: nb * mr].view(nb, mr)
+        lcol = col_bufs[k % 2][: nb * nc].view(nb, nc)
+        if k == nblk - 1:
+            if p == pk and q == qk:
+                lc, lr = (k - q) // Q * nb, (k - p) // P * nb
+                ops.potrf_lower(a_local[lc: lc + nb, lr: lr + nb], k * nb)
+            return lrow, lcol, None
+        if q == qk:
+            lc = (k - q) // Q * nb
+            colblk = a_local[lc: lc + nb]                      # my rows of block column k
+            d = diag_bufs[k % 2]
+            if p == pk:
+                lr = (k - p) // P * nb
+                ops.potrf_lower(colblk[:, lr: lr + nb], k * nb)
+                if P > 1 or mr > 0:
+                    d.copy_(colblk[:, lr: lr + nb])
+            if P > 1:
+                dist.broadcast(d, src=grid.rank_of(pk, qk), group=grid.col_group)
+            if mr > 0:
+                ops.trsm_right_lower_ct(d, colblk[:, r0:])
+                lrow.copy_(colblk[:, r0:])
+        with side.section():
+            if mr > 0 and Q > 1:
+                dist.broadcast(lrow, src=grid.rank_of(p, qk), group=grid.row_group, async_op=True).wait()
+            if nc > 0:
+                if p == src_p:
+                    # my column blocks j = q, q+Q, ... (> k) inside my row blocks p, p+P, ... (> k)
+                    i_first = lay.row_blocks[r0 // nb]
+                    j_first = lay.col_blocks[c0 // nb]
+                    pos0, step = (j_first - i_first) // P, Q // P
+                    lcol.view(nb, nc // nb, nb).copy_(lrow.view(nb, mr // nb, nb)[:, pos0::step, :])
+                if P > 1:
+                    dist.broadcast(lcol, src=grid.rank_of(src_p, q), group=grid.col_group,
+                                   async_op=True).wait()
+            ev = side.mark()
+        return lrow, lcol, ev
+
+    def update(k, lrow, lcol, g_lo, g_hi):
+        """Apply panel k to my column blocks with global index in [g_lo, g_hi)."""
+        r0, c0 = lay.lrow_from(k + 1), lay.lcol_from(k + 1)
+        c_lo, c_hi = lay.lcol_from(g_lo), lay.lcol_from(g_hi)
+        if c_hi <= c_lo:
+            return
+        gj = lay.col_blocks[c_lo // nb]                        # first column block of the range
+        r1 = lay.lrow_from(gj)                                 # rows above it stay untouched
+        if r1 >= mloc:
+            return
+        c = a_local[c_lo: c_hi][:, r1:]
+        ops.gemm_nt_sub_stair(c, lrow[:, r1 - r0:], lcol[:, c_lo - c0: c_hi - c0], nb,
+                              lay.row_blocks[r1 // nb], P, gj, Q)
+
+    cur = post(0)
+    for k in range(nblk - 1):
+        lrow, lcol, ev = cur
+        side.wait(ev)
+        if q == (k + 1) % Q:
+            update(k, lrow, lcol, k + 1, k + 2)                # look-ahead: next panel's column first
+        cur = post(k + 1)
+        update(k, lrow, lcol, k + 2, nblk)
+    return _reduce_info(ops.info_value(), dv)
+
+
+def getrf_block_cyclic(a_local: torch.Tensor, ipiv: torch.Tensor, n: int, nb: int, ops,
+                       grid: Grid | None = None):
+    """In-place LU with partial pivoting, P A = L U, of an n x n matrix whose block columns are
+    dealt cyclically to the ranks (a 1 x Q grid: `a_local` has shape (nloc, n)).
+
+    Every panel, and with it the pivot search of each column, stays on one GPU and is factored
+    by the single-GPU recursive panel code, so the pivot sequence is the one LAPACK's dgetrf
+    finds.  `ipiv` (int32, length n, on every rank) receives LAPACK's 1-based global pivot rows.
+    Returns info (0, or the index of the first exactly zero pivot).
+    """
+    grid = grid or Grid(1, dist.get_world_size() if dist.is_initialized() else 1)
+    if grid.P != 1:
+        raise ValueError("getrf_block_cyclic distributes block columns only: use a 1 x Q grid")
+    lay = BlockCyclic(n, nb, grid)
+    Q, q, nblk, nloc = grid.Q, grid.q, lay.nblk, lay.nloc
+    assert tuple(a_local.shape) == (nloc, n)
+    dt, dv = a_local.dtype, a_local.device
+    side = _SideStream(dv)
+    bufs = [torch.empty(nb * n, dtype=dt, device=dv) for _ in range(2)]
+    piv_bufs = [torch.zeros(nb, dtype=torch.int32, device=dv) for _ in range(2)]
+
+    def post(k):
+        """Factor panel k (all earlier updates applied) and start its broadcast."""
         k0 = k * nb
-        kb = min(nb, n - k0)
-        owner = owner_of_block(k, world)
-        panel = bufs[k % 2][: kb * (n - k0)].view(kb, n - k0)
-        if rank == owner:
-            col = a_local[offs[k]: offs[k] + kb]       # n x kb view
-            diag = col[:, k0: k0 + kb]
-            ops.potrf_lower(diag, k0)
-            if n - k0 - kb > 0:
-                ops.trsm_right_lower_ct(diag, col[:, k0 + kb:])
-            panel.copy_(col[:, k0:])
-        work = None
-        if world > 1:
-            work = dist.broadcast(panel, src=owner, group=group, async_op=True)
-        return panel, work
+        panel = bufs[k % 2][: nb * (n - k0)].view(nb, n - k0)   # rows k0.. of block column k
+        piv = piv_bufs[k % 2]
+        if q == k % Q:
+            lc = (k - q) // Q * nb
+            blk = a_local[lc: lc + nb][:, k0:]
+            ops.getrf(blk, piv, k0)
+            panel.copy_(blk)
+        ev = None
+        if Q > 1:
+            with side.section():
+                w1 = dist.broadcast(panel, src=k % Q, group=grid.row_group, async_op=True)
+                w2 = dist.broadcast(piv, src=k % Q, group=grid.row_group, async_op=True)
+                w1.wait()
+                w2.wait()
+                ev = side.mark()
+        return panel, piv, ev
 
-    def update(j, k, panel):
-        """Block column j (owned) -= panel_k(j0:, :) * panel_k(j0:j0+jb, :)^H."""
-        k0, j0 = k * nb, j * nb
-        jb = min(nb, n - j0)
-        c = a_local[offs[j]: offs[j] + jb][:, j0:]                 # (n - j0) x jb
-        ops.gemm_nt_sub(c, panel[:, j0 - k0:], panel[:, j0 - k0: j0 - k0 + jb])
+    def apply(k, panel, piv, g_lo, g_hi, left=False):
+        """Interchanges of panel k on my column blocks in [g_lo, g_hi); for blocks right of the
+        panel also U12 = L11^-1 A12 and the rank-nb update of the rows below."""
+        k0 = k * nb
+        c_lo, c_hi = lay.lcol_from(g_lo), lay.lcol_from(g_hi)
+        if c_hi <= c_lo:
+            return
+        cols = a_local[c_lo: c_hi]
+        ops.laswp(cols[:, k0:], piv, 0, nb)                    # pivots are relative to row k0
+        if left:
+            return
+        ops.trsm_left_lower_unit(panel[:, :nb], cols[:, k0: k0 + nb])
+        if n - k0 - nb > 0:
+            ops.gemm_nn_sub(cols[:, k0 + nb:], panel[:, nb:], cols[:, k0: k0 + nb])
 
-    panel, work = factor_and_post(0)
+    cur = post(0)
     for k in range(nblk):
-        if work is not None:
-            work.wait()
-        nxt = (None, None)
+        panel, piv, ev = cur
+        side.wait(ev)
+        ipiv[k * nb: (k + 1) * nb].copy_(piv + k * nb)
         if k + 1 < nblk:
-            if owner_of_block(k + 1, world) == rank:
-                update(k + 1, k, panel)
-            nxt = factor_and_post(k + 1)
-        for j in range(k + 2, nblk):
-            if owner_of_block(j, world) == rank:
-                update(j, k, panel)
-        panel, work = nxt
-    info = ops.info_value()
-    if world > 1:                                   # smallest non-zero info over the ranks
-        big = 2 ** 31 - 1
-        t = torch.tensor([info if info > 0 else big], dtype=torch.int64, device=a_local.device)
-        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
-        info = int(t.item())
-        info = 0 if info == big else info
-    return info
+            if q == (k + 1) % Q:
+                apply(k, panel, piv, k + 1, k + 2)
+            cur = post(k + 1)
+        apply(k, panel, piv, k + 2, nblk)
+        apply(k, panel, piv, 0, k, left=True)
+    return _reduce_info(ops.info_value(), dv)
 
 
 def lstsq_tsqr(a_local: torch.Tensor, b_local: torch.Tensor, ops, group=None):

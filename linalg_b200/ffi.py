@@ -149,12 +149,13 @@ def declared_symbols():
                   "getri", "potri", "trtri"):
             syms.append(f"{l}{r}_")
         for r in ("trsm", "herk", "getrf", "getrs", "potrf", "potrs", "geqrf", "ormqr", "gels",
-                  "trtrs"):
+                  "trtrs", "laswp", "gemm_stair"):
             syms.append(f"la_b200_{l}{r}_dev")
         syms.append(f"la_b200_{l}gemm_dev")
     syms += ["cblas_zhemm", "cblas_ssyrk", "cblas_dsyrk", "cblas_zherk", "sormqr_", "dormqr_",
              "zunmqr_", "sorgqr_", "dorgqr_", "zungqr_", "ilaver_", "openblas_set_num_threads",
              "openblas_get_num_threads", "openblas_get_num_procs", "openblas_get_config",
              "openblas_get_corename", "openblas_get_parallel", "la_b200_version",
-             "la_b200_workspace_bytes", "la_b200_last_gemm_path"]
+             "la_b200_workspace_bytes", "la_b200_last_gemm_path", "la_b200_release_workspace",
+             "la_b200_set_sm_limit", "la_b200_dgetrf_dev_noalloc"]
     return syms
