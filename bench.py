@@ -6,16 +6,26 @@
 Metric: FP64 GEMM TFLOP/s at N = 16384 (the DGEMM leg of "DGEMM/DGETRF/DPOTRF TFLOP/s at
 N=16384"), in the reference's `Matrix#*` call pattern: C <- 1.0*A*B + 1.0*C on a zeroed C,
 column-major, NoTrans/NoTrans (src/linalg/mult.cr:26,64-69,119-120).  One step = one such
-product.  DGETRF / DPOTRF at the same N are timed in the same run and reported under "extra".
+product.  DGETRF / DPOTRF at the same N are timed in the same run and reported under "extra",
+each with its own roofline object.
 
   value   device-resident: operands already in HBM, CUDA events on the launching stream
           (la_b200_dgemm_dev), max over ranks.
-  e2e     the drop-in symbol cblas_dgemm called with HOST pointers (pinned), i.e. H2D of A, B, C
-          + kernel + D2H of C inside the timed region.
-  N > 1   strong scaling: B and C are split by block columns over the ranks,
-          A is replicated; no collective on the data path; value = 2N^3 / max-rank time.
+  e2e     N = 1: the drop-in symbol cblas_dgemm called with HOST pointers (pinned), i.e. H2D of
+          A, B, C + kernel + D2H of C inside the timed region; "e2e_pageable" is the same call on
+          plain (unpinned) numpy buffers, which is what the reference's GC-heap slices are
+          (src/matrix/general_matrix.cr:26).  N > 1: `dist.HostGemmPlan` — every rank uploads its
+          block columns of B and C and 1/N of A from pinned host memory, A is all-gathered over
+          NVLink, the result block goes back to the host.
+  N > 1   strong scaling of the product: B and C are split by block columns over the ranks
+          (SURVEY.md §8e), no collective on the device-resident data path.  The factorisations
+          of BASELINE config c4 / the scaling target run in the same job: Cholesky N = 65536 on
+          the 2-D block-cyclic process grid and LU N = 65536 on block columns
+          (linalg_b200/dist.py), each with its distributed residual and its speed-up over the
+          single-GPU routine timed on rank 0 in the same run, plus the TSQR least squares
+          (2^20 x 512) — all under "extra.dist_*".
   --impl reference   the reference's own arithmetic path — OpenBLAS dgemm through the same C ABI
-          on the host cores (all threads) — on a bounded sample (N = 8192) of the workload.
+          on the host cores (all threads) — at the SAME N.
 
 Inputs are synthetic U[0,1) (Mat.rand, src/matrix/matrix.cr:490-492).  Operands (3 x 2 GiB)
 exceed the 126 MB L2, so no explicit flush is needed between iterations.
@@ -38,10 +48,28 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 FP64_DMMA_PEAK_TFLOPS = 37.0   # measured: tools/microbench/peak_fp64.cu on this pool's B200
-CPU_SAMPLE_N = 8192
+# measured: tools/microbench/peak_tf32.cu (tcgen05.mma.kind::tf32, M128 N256 K8, TMEM resident),
+# profiles/r2_peak_tf32.jsonl: best single launch / back to back for 3 s
+TF32_PEAK_BURST_TFLOPS = 1115.1
+TF32_PEAK_SUSTAINED_TFLOPS = 1018.7
 DGEMM_KCHUNK = 4096                     # the library runs long-k products as k-chunks (gemm_dmma.cu)
 DGEMM_DRAM_BYTES_PER_LAUNCH = 18.82e9   # one k-chunk launch at N = 16384: 16.69 GB read + 2.14 GB written (ncu)
 WORKLOAD = "dgemm N={n} NoTrans/NoTrans alpha=1 beta=1 on zeroed C (Matrix#*)"
+DIST_N = 65536                          # BASELINE config c4 / north_star scaling target
+DIST_NB = 512
+DIST_RESERVE_SMS = int(os.environ.get("LA_DIST_RESERVE_SMS", "8"))
+DIST_COMM_CTAS = int(os.environ.get("LA_DIST_COMM_CTAS", "8"))
+# kernel time shares of one factorisation at N = 16384 from the ncu launch lists (serialised,
+# cold caches: shares, not absolutes); refreshed whenever the kernels change
+FACTOR_PROFILE = {
+    "dgetrf": {"source": "profiles/r1h_dgetrf16384_launches.csv",
+               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 125.0,
+                              "lu_panel_kernel (480 leaves)": 43.7, "laswp_*": 17.6,
+                              "trsm_dmma_kernel": 11.3}},
+    "dpotrf": {"source": "profiles/r1d_dpotrf16384_launches.csv",
+               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 65.0,
+                              "potf2_kernel (120 leaves)": 12.0, "trsm_dmma_kernel": 5.5}},
+}
 
 
 def _peaks():
@@ -102,6 +130,7 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+# ------------------------------------------------------------------------- CPU arm
 def _cpu_gemm_setup(n):
     from linalg_b200 import ffi
     from oracle import openblas_ref
@@ -129,14 +158,15 @@ def cpu_dgemm_tflops(n, reps=2):
         t0 = time.perf_counter()
         step()
         best = min(best, time.perf_counter() - t0)
-    return 2.0 * n ** 3 / best * 1e-12, cores, cfg
+    return 2.0 * n ** 3 / best * 1e-12, cores, cfg, reps + 1
 
 
 def run_reference(args):
-    """Reference arm: the reference's CPU arithmetic path on the box's host cores (rank 0)."""
+    """Reference arm: the reference's CPU arithmetic path on the box's host cores (rank 0), on
+    the same workload as the GPU arm (dgemm at N = args.n, ~6 s per step on 16 cores)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
-    n = CPU_SAMPLE_N
+    n = args.n
     step, cores, cfg = _cpu_gemm_setup(n)
     for _ in range(args.warmup):
         step()
@@ -145,21 +175,49 @@ def run_reference(args):
         step()
     dt = (time.perf_counter() - t0) / args.steps
     tf = 2.0 * n ** 3 / dt * 1e-12
-    sample = f"dgemm N={n} (2N^3 = {2.0 * n ** 3:.3e} flop per step) of the N={args.n} workload"
+    sample = f"the full workload: dgemm N={n} (2N^3 = {2.0 * n ** 3:.3e} flop) per step"
     print(json.dumps({
         "impl": "reference", "metric": "fp64_gemm_tflops", "value": tf, "unit": "TFLOP/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD.format(n=args.n), "cpu_sample": sample},
+        "config": {"workload": WORKLOAD.format(n=n)},
         "cpu_baseline": {"value": tf, "unit": "TFLOP/s", "cores": cores, "kind": "reference",
                          "sample": sample + "; " + cfg},
         "e2e": {"value": tf, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
+# ------------------------------------------------------------------------- GPU legs
+def _best_ms(fn, reps=3, setup=None):
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    b = 1e30
+    for i in range(reps + 1):
+        if setup:
+            setup()
+        torch.cuda.synchronize()
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if i:
+            b = min(b, e0.elapsed_time(e1))
+    return b
+
+
+def _roofline_obj(name, tflops, ms, peak):
+    prof = FACTOR_PROFILE[name]
+    tot = sum(prof["kernels_ms"].values())
+    return {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
+            "frac": tflops / peak, "ms": ms,
+            "kernel_share": {k: round(v / tot, 3) for k, v in prof["kernels_ms"].items()},
+            "kernel_share_source": prof["source"] + " (ncu launch list, serialised: shares only)"}
+
+
 def time_factorizations(n, steps):
-    """DGETRF and DPOTRF at the same N, device resident, with probe-vector parity checks."""
+    """DGETRF and DPOTRF at the same N, device resident, with probe-vector parity checks, and the
+    s/z factorisations at the same N."""
     import torch
 
     from linalg_b200 import dev
@@ -170,22 +228,8 @@ def time_factorizations(n, steps):
     W = torch.empty_like(A0)
     ipiv = torch.zeros(n, dtype=torch.int32, device="cuda")
     info = torch.zeros(1, dtype=torch.int32, device="cuda")
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-
-    def timed(fn, reps):
-        best = 1e30
-        for _ in range(reps):
-            W.copy_(A0)
-            torch.cuda.synchronize()
-            e0.record()
-            fn()
-            e1.record()
-            torch.cuda.synchronize()
-            best = min(best, e0.elapsed_time(e1))
-        return best
-
-    reps = max(2, min(steps, 3)) + 1
-    ms = timed(lambda: dev.getrf(n, n, W, n, ipiv, info), reps)
+    reps = max(2, min(steps, 3))
+    ms = _best_ms(lambda: dev.getrf(n, n, W, n, ipiv, info), reps, setup=lambda: W.copy_(A0))
     out["dgetrf_tflops"] = (2.0 / 3.0) * n ** 3 / (ms * 1e-3) * 1e-12
     out["dgetrf_ms"] = ms
     out["dgetrf_info"] = int(info.item())
@@ -208,7 +252,7 @@ def time_factorizations(n, steps):
     # SPD matrix: symmetric, diagonally dominant (cheap variant)
     A0.add_(A0.T.clone()).mul_(0.5)
     A0.diagonal().add_(float(n))
-    ms = timed(lambda: dev.potrf(dev.LOWER, n, W, n, info), reps)
+    ms = _best_ms(lambda: dev.potrf(dev.LOWER, n, W, n, info), reps, setup=lambda: W.copy_(A0))
     out["dpotrf_tflops"] = (1.0 / 3.0) * n ** 3 / (ms * 1e-3) * 1e-12
     out["dpotrf_ms"] = ms
     out["dpotrf_info"] = int(info.item())
@@ -216,68 +260,127 @@ def time_factorizations(n, steps):
     Lx = Lm @ (Lm.T @ xm)
     Ax = A0.T @ xm
     out["dpotrf_probe_residual"] = float(((Ax - Lx).norm() / (A0.norm() * xm.norm())).item())
-    del A0, W
+    del A0, W, LU, Lm
     torch.cuda.empty_cache()
-    out.update(time_other_types())
     out["fp64_peak_tflops"] = FP64_DMMA_PEAK_TFLOPS
     out["dgetrf_frac_of_peak"] = out["dgetrf_tflops"] / FP64_DMMA_PEAK_TFLOPS
     out["dpotrf_frac_of_peak"] = out["dpotrf_tflops"] / FP64_DMMA_PEAK_TFLOPS
+    out["dgetrf_roofline"] = _roofline_obj("dgetrf", out["dgetrf_tflops"], out["dgetrf_ms"],
+                                           FP64_DMMA_PEAK_TFLOPS)
+    out["dpotrf_roofline"] = _roofline_obj("dpotrf", out["dpotrf_tflops"], out["dpotrf_ms"],
+                                           FP64_DMMA_PEAK_TFLOPS)
+
+    # Float32 / Complex factorisations at the same N (flop counts: complex x4)
+    for dt, let, fl in ((torch.float32, "s", 1.0), (torch.complex128, "z", 4.0)):
+        A0 = torch.rand((n, n), dtype=dt, device="cuda", generator=g)
+        W = torch.empty_like(A0)
+        ms = _best_ms(lambda: dev.getrf(n, n, W, n, ipiv, info), 1, setup=lambda: W.copy_(A0))
+        out[f"{let}getrf_ms"] = ms
+        out[f"{let}getrf_tflops"] = fl * (2.0 / 3.0) * n ** 3 / (ms * 1e-3) * 1e-12
+        out[f"{let}getrf_info"] = int(info.item())
+        A0.add_(A0.T.conj().clone()).mul_(0.5)
+        A0.diagonal().add_(float(n))
+        ms = _best_ms(lambda: dev.potrf(dev.LOWER, n, W, n, info), 1, setup=lambda: W.copy_(A0))
+        out[f"{let}potrf_ms"] = ms
+        out[f"{let}potrf_tflops"] = fl * (1.0 / 3.0) * n ** 3 / (ms * 1e-3) * 1e-12
+        out[f"{let}potrf_info"] = int(info.item())
+        x = torch.rand(n, dtype=dt, device="cuda", generator=g)
+        Lm = torch.triu(W).T
+        res = (A0.T @ x - Lm @ (Lm.conj().T @ x)).norm() / (A0.norm() * x.norm())
+        out[f"{let}potrf_probe_residual"] = float(res.item())
+        del A0, W, Lm
+        torch.cuda.empty_cache()
     return out
 
 
 def time_other_types():
     """Float32 (3xTF32 tcgen05) and complex128 (DMMA) GEMM and the tall-skinny least squares of
-    BASELINE config c5, device resident, one size each."""
+    BASELINE config c5 (Float64 and Complex), device resident, one size each."""
     import torch
 
     from linalg_b200 import dev, ffi
     out = {}
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-
-    def best(fn, reps=3):
-        b = 1e30
-        for i in range(reps + 1):
-            torch.cuda.synchronize()
-            e0.record()
-            fn()
-            e1.record()
-            torch.cuda.synchronize()
-            if i:
-                b = min(b, e0.elapsed_time(e1))
-        return b
-
     for dt, name, n, fl, want in ((torch.float32, "sgemm", 16384, 2, 3), (torch.complex128, "zgemm", 8192, 8, 2)):
         A = torch.rand((n, n), dtype=dt, device="cuda")
         B = torch.rand((n, n), dtype=dt, device="cuda")
         Cm = torch.zeros((n, n), dtype=dt, device="cuda")
-        ms = best(lambda: dev.gemm(ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, 1.0, A, n, B, n, 0.0, Cm, n))
+        ms = _best_ms(lambda: dev.gemm(ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, 1.0, A, n, B, n, 0.0, Cm, n))
         assert dev.last_gemm_path() == want, f"{name}: tensor-core path not taken"
-        # probe-vector check: C x == A (B x)
-        x = torch.rand(n, dtype=dt, device="cuda")
-        lhs = Cm.T @ x
-        rhs = A.T @ (B.T @ x)
         out[f"{name}_n"] = n
         out[f"{name}_tflops"] = fl * n ** 3 / (ms * 1e-3) * 1e-12
-        out[f"{name}_probe_relerr"] = float(((lhs - rhs).norm() / rhs.norm()).item())
-        del A, B, Cm
+        # three full columns of C against a product formed in double precision
+        cols = [0, n // 2 + 1, n - 1]
+        hi = torch.complex128 if dt.is_complex else torch.float64
+        ref = torch.stack([A.T.to(hi) @ B[c].to(hi) for c in cols]) if dt != torch.float32 else None
+        if ref is None:
+            Ad = A.T.to(torch.float64)
+            ref = torch.stack([Ad @ B[c].to(torch.float64) for c in cols])
+            del Ad
+        got = Cm[cols].to(hi)
+        out[f"{name}_relerr_vs_f64"] = float(((got - ref).norm() / ref.norm()).item())
+        out[f"{name}_max_abs_err_vs_f64"] = float((got - ref).abs().max().item())
+        del A, B, Cm, ref, got
         torch.cuda.empty_cache()
+    out["tf32_peak_tflops_burst"] = TF32_PEAK_BURST_TFLOPS
+    out["tf32_peak_tflops_sustained"] = TF32_PEAK_SUSTAINED_TFLOPS
+    # the tensor pipe executes three TF32 products per useful one
+    out["sgemm_frac_of_measured_tf32_peak"] = 3.0 * out["sgemm_tflops"] / TF32_PEAK_BURST_TFLOPS
+    out["sgemm_frac_of_sustained_tf32_peak"] = 3.0 * out["sgemm_tflops"] / TF32_PEAK_SUSTAINED_TFLOPS
     m, n = 1 << 20, 512
-    A = torch.rand((n, m), dtype=torch.float64, device="cuda")
-    b = torch.rand((1, m), dtype=torch.float64, device="cuda")
-    W, X = torch.empty_like(A), torch.empty_like(b)
-    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for dt, let, fl in ((torch.float64, "d", 1.0), (torch.complex128, "z", 4.0)):
+        A = torch.rand((n, m), dtype=dt, device="cuda")
+        b = torch.rand((1, m), dtype=dt, device="cuda")
+        W, X = torch.empty_like(A), torch.empty_like(b)
+        info = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ms = _best_ms(lambda: dev.gels(ffi.NO_TRANS, m, n, 1, W, m, X, m, info), 2,
+                      setup=lambda: (W.copy_(A), X.copy_(b)))
+        r = A.T @ X[0, :n] - b[0]
+        out[f"{let}gels_1Mx512_ms"] = ms
+        out[f"{let}gels_1Mx512_tflops"] = fl * (2.0 * m * n * n - (2.0 / 3.0) * n ** 3) / (ms * 1e-3) * 1e-12
+        out[f"{let}gels_1Mx512_normal_eq_residual"] = float(
+            ((A.conj() @ r).norm() / (A.norm() * r.norm())).item())
+        del A, b, W, X
+        torch.cuda.empty_cache()
+    return out
 
-    def ls():
-        W.copy_(A)
-        X.copy_(b)
-        dev.gels(ffi.NO_TRANS, m, n, 1, W, m, X, m, info)
 
-    tcopy = best(lambda: (W.copy_(A), X.copy_(b)), reps=2)
-    ms = best(ls, reps=2) - tcopy
-    r = A.T @ X[0, :n] - b[0]
-    out["dgels_1Mx512_ms"] = ms
-    out["dgels_1Mx512_tflops"] = (2.0 * m * n * n - (2.0 / 3.0) * n ** 3) / (ms * 1e-3) * 1e-12
-    out["dgels_1Mx512_normal_eq_residual"] = float(((A @ r).norm() / (A.norm() * r.norm())).item())
+def dist_legs(world, rank):
+    """Factorisations at N = 65536 and the TSQR least squares across the ranks of this job."""
+    import torch.distributed as dist
+
+    from linalg_b200 import dist as ladist
+    from linalg_b200 import dist_measure as dm
+    out = {}
+    single = {}
+    if rank == 0:
+        for kind in ("potrf", "getrf"):
+            single[kind] = dm.run_single_gpu(kind, DIST_N)
+    if world == 1:
+        for kind in ("potrf", "getrf"):
+            s = single[kind]
+            out.update({f"dist_{kind}_n": DIST_N, f"dist_{kind}_ms": s["ms"], f"dist_{kind}_tflops": s["tflops"],
+                        f"dist_{kind}_speedup_vs_1gpu": 1.0, f"dist_{kind}_residual": s["residual"],
+                        f"dist_{kind}_info": s["info"], f"dist_{kind}_grid": "1x1 (single-GPU routine)"})
+        return out
+    dist.barrier()
+    grid = ladist.Grid(comm_ctas=DIST_COMM_CTAS)
+    d = dm.run_potrf(DIST_N, DIST_NB, grid, reserve_sms=DIST_RESERVE_SMS, reps=2,
+                     warm_n=DIST_NB * grid.Q * 2)
+    lu_grid = grid if grid.P == 1 else ladist.Grid(1, world, comm_ctas=DIST_COMM_CTAS)
+    e = dm.run_getrf(DIST_N, DIST_NB, lu_grid, reserve_sms=DIST_RESERVE_SMS, reps=2,
+                     warm_n=DIST_NB * world * 2)
+    t = dm.run_tsqr(1 << 20, 512)
+    for kind, r in (("potrf", d), ("getrf", e)):
+        out.update({f"dist_{kind}_n": DIST_N, f"dist_{kind}_nb": DIST_NB, f"dist_{kind}_grid": r["grid"],
+                    f"dist_{kind}_ms": r["ms"], f"dist_{kind}_tflops": r["tflops"],
+                    f"dist_{kind}_residual": r["residual"], f"dist_{kind}_info": r["info"]})
+        if rank == 0:
+            out[f"dist_{kind}_1gpu_ms"] = single[kind]["ms"]
+            out[f"dist_{kind}_1gpu_residual"] = single[kind]["residual"]
+            out[f"dist_{kind}_speedup_vs_1gpu"] = single[kind]["ms"] / r["ms"]
+    out.update({"dist_tsqr_m": t["m"], "dist_tsqr_n": t["n"], "dist_tsqr_ms": t["ms"],
+                "dist_tsqr_tflops": t["tflops"], "dist_tsqr_max_rel_err": t["max_rel_err"],
+                "dist_reserve_sms": DIST_RESERVE_SMS, "dist_comm_ctas": DIST_COMM_CTAS})
     return out
 
 
@@ -287,6 +390,7 @@ def run_ours(args):
 
     import linalg_b200
     from linalg_b200 import dev, ffi
+    from linalg_b200 import dist as ladist
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -295,7 +399,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n = args.n
-    c0, c1 = (n * rank) // world, (n * (rank + 1)) // world   # this rank's block columns
+    c0, c1 = ladist.shard_columns(n, world, rank)   # this rank's block columns
     nc = c1 - c0
     g = torch.Generator(device="cuda")
     g.manual_seed(20261106)
@@ -349,54 +453,89 @@ def run_ours(args):
     assert relerr < 1e-12, f"dgemm residual {relerr}"
     extra = {"dgemm_relerr": relerr}
 
-    # ---- e2e through the drop-in symbol with pinned host buffers
-    e2e_steps = max(1, min(args.steps, 2))
+    # ---- e2e with host buffers
+    e2e_steps = max(1, min(args.steps, 3))
     hA = torch.empty((n, n), dtype=torch.float64).pin_memory()
     hB = torch.empty((nc, n), dtype=torch.float64).pin_memory()
-    hC = torch.zeros((nc, n), dtype=torch.float64).pin_memory()
     hA.copy_(A)
     hB.copy_(B)
     torch.cuda.synchronize()
     del Cm, A, B
     torch.cuda.empty_cache()
-    f = lib.cblas_dgemm
-    f.argtypes = [ctypes.c_int] * 6 + [ctypes.c_double, ctypes.c_void_p, ctypes.c_int,
-                                       ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
-                                       ctypes.c_void_p, ctypes.c_int]
-    f.restype = None
+    # Matrix#* multiplies into a freshly zeroed result (mult.cr:118-119): one zeroed C per step,
+    # prepared before the clock starts (inputs are ready when a step begins)
+    hCs = [torch.zeros((nc, n), dtype=torch.float64).pin_memory() for _ in range(e2e_steps)]
+    if world == 1:
+        f = lib.cblas_dgemm
+        f.argtypes = [ctypes.c_int] * 6 + [ctypes.c_double, ctypes.c_void_p, ctypes.c_int,
+                                           ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
+                                           ctypes.c_void_p, ctypes.c_int]
+        f.restype = None
 
-    def e2e_step(hc):
-        f(ffi.COL_MAJOR, ffi.NO_TRANS, ffi.NO_TRANS, n, nc, n, 1.0, hA.data_ptr(), n, hB.data_ptr(),
-          n, 1.0, hc.data_ptr(), n)
+        def host_gemm(pa, pb, pc):
+            f(ffi.COL_MAJOR, ffi.NO_TRANS, ffi.NO_TRANS, n, nc, n, 1.0, pa, n, pb, n, 1.0, pc, n)
 
-    # Matrix#* multiplies into a freshly zeroed result (mult.cr:118-119): one zeroed pinned C per
-    # step, prepared before the clock starts (inputs are ready when a step begins)
-    hCs = [hC] + [torch.zeros((nc, n), dtype=torch.float64).pin_memory() for _ in range(e2e_steps - 1)]
-    e2e_step(hC)   # warm-up (sizes the shim's device workspace)
-    hC.zero_()
+        def e2e_step(hc):
+            host_gemm(hA.data_ptr(), hB.data_ptr(), hc.data_ptr())
+        e2e_how = "cblas_dgemm (drop-in symbol), pinned host buffers"
+        h2d = 8 * (n * n + 2 * n * nc)
+    else:
+        plan = ladist.HostGemmPlan(n, nc)
+        a0, a1 = plan.a_slice()
+        hA_slice = hA[a0:a1]
+
+        def e2e_step(hc):
+            plan.run(hA_slice, hB, hc)
+        e2e_how = ("dist.HostGemmPlan: 1/N of A + block columns of B, C per rank from pinned host "
+                   "memory, A all-gathered over NVLink")
+        h2d = 8 * ((a1 - a0) * n + 2 * n * nc)
+    warm = torch.zeros((nc, n), dtype=torch.float64).pin_memory()
+    e2e_step(warm)   # warm-up (sizes the device workspace)
+    del warm
     barrier()
     t0 = time.perf_counter()
     for i in range(e2e_steps):
         e2e_step(hCs[i])
     barrier()
     e2e_s = allmax((time.perf_counter() - t0) / e2e_steps)
-    hC = hCs[-1]
-    got = hC[cols].T.numpy()
+    got = hCs[-1][cols].T.numpy()
     relerr2 = float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
-    assert relerr2 < 1e-12, f"cblas_dgemm residual {relerr2}"
+    assert relerr2 < 1e-12, f"host-buffer dgemm residual {relerr2}"
     e2e = {"value": 2.0 * n ** 3 / e2e_s * 1e-12, "unit": "TFLOP/s",
-           "h2d_bytes_per_step": 8 * (n * n + 2 * n * nc), "d2h_bytes_per_step": 8 * n * nc,
-           "ms_per_step": e2e_s * 1e3, "steps": e2e_steps}
-    del hA, hB, hC, hCs
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8 * n * nc,
+           "ms_per_step": e2e_s * 1e3, "steps": e2e_steps, "how": e2e_how}
+    del hCs
+    if world == 1:
+        # the same call on pageable memory (plain numpy arrays), as a Crystal caller's GC-heap
+        # slices are: the shim stages through its pinned ring
+        pA, pB = np.empty((n, n)), np.empty((nc, n))
+        pA[:] = hA.numpy()
+        pB[:] = hB.numpy()
+        pCs = [np.zeros((nc, n)) for _ in range(e2e_steps + 1)]
+        host_gemm(pA.ctypes.data, pB.ctypes.data, pCs[-1].ctypes.data)
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            host_gemm(pA.ctypes.data, pB.ctypes.data, pCs[i].ctypes.data)
+        pg_s = (time.perf_counter() - t0) / e2e_steps
+        relerr3 = float(np.linalg.norm(pCs[0][cols].T - ref) / np.linalg.norm(ref))
+        assert relerr3 < 1e-12, f"pageable cblas_dgemm residual {relerr3}"
+        extra["e2e_pageable"] = {"value": 2.0 * n ** 3 / pg_s * 1e-12, "unit": "TFLOP/s",
+                                 "ms_per_step": pg_s * 1e3, "steps": e2e_steps,
+                                 "how": "cblas_dgemm on unpinned numpy buffers (the reference's "
+                                        "GC-heap case)"}
+        del pA, pB, pCs
+    del hA, hB
 
+    extra.update(dist_legs(world, rank))
     cpu = None
     if rank == 0:
         extra.update(time_factorizations(n, args.steps))
+        extra.update(time_other_types())
         if world == 1:
-            tf, cores, cfg = cpu_dgemm_tflops(CPU_SAMPLE_N)
+            tf, cores, cfg, runs = cpu_dgemm_tflops(n, reps=1)
             cpu = {"value": tf, "unit": "TFLOP/s", "cores": cores, "kind": "reference",
-                   "sample": f"OpenBLAS dgemm N={CPU_SAMPLE_N} (the library the reference links), "
-                             f"best of 3, ~{2.0 * CPU_SAMPLE_N ** 3 / tf * 1e-12:.1f} s each; {cfg}"}
+                   "sample": f"OpenBLAS dgemm N={n} (the library the reference links, the full "
+                             f"workload), best of {runs}, ~{2.0 * n ** 3 / tf * 1e-12:.1f} s each; {cfg}"}
         out = {
             "metric": "fp64_gemm_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,

@@ -43,6 +43,7 @@ struct Context {
   void* pinned = nullptr;          // small pinned bounce buffer (info, ipiv)
   size_t pinned_size = 0;
   void* lu_state = nullptr;        // LU panel exchange area + launch sequence (lu_panel.cu)
+  void* stager = nullptr;          // pinned staging ring for pageable host operands (host_stage.cu)
   int sm_limit = 0;                // > 0: persistent kernels use at most this many CTAs
   bool allow_side_stream = true;   // look-ahead may create `side` (a stream, events, an arena)
   Context* side = nullptr;         // second context for work overlapped with the main stream

@@ -6,6 +6,17 @@
 
 namespace la {
 
+// host_stage.cu: 2-D copies between the caller's host matrix and the device (`width` bytes per
+// column, `ncols` columns).  Large transfers from / to PAGEABLE memory go through the context's
+// ring of pinned slots (parallel memcpy + DMA); everything else is a plain cudaMemcpy2DAsync.
+// Staged device -> host copies complete asynchronously: drain_host_transfers() (called by sync())
+// returns once they have all landed in the caller's memory.
+void h2d_2d(Context& ctx, void* dst, size_t dpitch, const void* src, size_t spitch, size_t width,
+            size_t ncols, cudaStream_t s);
+void d2h_2d(Context& ctx, void* dst, size_t dpitch, const void* src, size_t spitch, size_t width,
+            size_t ncols, cudaStream_t s);
+void drain_host_transfers(Context& ctx);
+
 // A matrix staged on the device for one host-pointer call.
 template <typename T>
 struct DevMat {
@@ -27,17 +38,15 @@ inline DevMat<T> dev_alloc(Context& ctx, int64_t rows, int64_t cols) {
 template <typename T>
 inline void upload(Context& ctx, DevMat<T>& d, const T* h, int64_t ldh, cudaStream_t s = nullptr) {
   if (d.rows <= 0 || d.cols <= 0) return;
-  LA_CUDA_CHECK(cudaMemcpy2DAsync(d.p, (size_t)d.ld * sizeof(T), h, (size_t)ldh * sizeof(T),
-                                  (size_t)d.rows * sizeof(T), (size_t)d.cols,
-                                  cudaMemcpyHostToDevice, s ? s : ctx.stream));
+  h2d_2d(ctx, d.p, (size_t)d.ld * sizeof(T), h, (size_t)ldh * sizeof(T),
+         (size_t)d.rows * sizeof(T), (size_t)d.cols, s ? s : ctx.stream);
 }
 
 template <typename T>
 inline void download(Context& ctx, const DevMat<T>& d, T* h, int64_t ldh, cudaStream_t s = nullptr) {
   if (d.rows <= 0 || d.cols <= 0) return;
-  LA_CUDA_CHECK(cudaMemcpy2DAsync(h, (size_t)ldh * sizeof(T), d.p, (size_t)d.ld * sizeof(T),
-                                  (size_t)d.rows * sizeof(T), (size_t)d.cols,
-                                  cudaMemcpyDeviceToHost, s ? s : ctx.stream));
+  d2h_2d(ctx, h, (size_t)ldh * sizeof(T), d.p, (size_t)d.ld * sizeof(T),
+         (size_t)d.rows * sizeof(T), (size_t)d.cols, s ? s : ctx.stream);
 }
 
 template <typename T>
@@ -64,17 +73,18 @@ inline void copy_triangle_hd(Context& ctx, bool to_device, bool lower, int64_t n
     T* d = dev + r0 + c0 * ldd;
     T* h = host + r0 + c0 * ldh;
     if (to_device)
-      LA_CUDA_CHECK(cudaMemcpy2DAsync(d, (size_t)ldd * sizeof(T), h, (size_t)ldh * sizeof(T),
-                                      (size_t)rows * sizeof(T), (size_t)w, cudaMemcpyHostToDevice,
-                                      s ? s : ctx.stream));
+      h2d_2d(ctx, d, (size_t)ldd * sizeof(T), h, (size_t)ldh * sizeof(T), (size_t)rows * sizeof(T),
+             (size_t)w, s ? s : ctx.stream);
     else
-      LA_CUDA_CHECK(cudaMemcpy2DAsync(h, (size_t)ldh * sizeof(T), d, (size_t)ldd * sizeof(T),
-                                      (size_t)rows * sizeof(T), (size_t)w, cudaMemcpyDeviceToHost,
-                                      s ? s : ctx.stream));
+      d2h_2d(ctx, h, (size_t)ldh * sizeof(T), d, (size_t)ldd * sizeof(T), (size_t)rows * sizeof(T),
+             (size_t)w, s ? s : ctx.stream);
   }
 }
 
-inline void sync(Context& ctx) { LA_CUDA_CHECK(cudaStreamSynchronize(ctx.stream)); }
+inline void sync(Context& ctx) {
+  drain_host_transfers(ctx);
+  LA_CUDA_CHECK(cudaStreamSynchronize(ctx.stream));
+}
 
 // Read the device info word after the stream has drained.
 inline int read_info(Context& ctx, const int* d_info) {

@@ -37,18 +37,16 @@ static void getrf_streamed_home(Context& ctx, int64_t m, int64_t n, DevMat<T>& d
       LA_CUDA_CHECK(cudaEventRecord(e, ctx.stream));
       LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.d2h_stream, e, 0));
       evs.push_back(e);
-      LA_CUDA_CHECK(cudaMemcpy2DAsync(A + r0, (size_t)lda * sizeof(T), dA.p + r0,
-                                      (size_t)dA.ld * sizeof(T), (size_t)(r1 - r0) * sizeof(T),
-                                      (size_t)n, cudaMemcpyDeviceToHost, ctx.d2h_stream));
+      d2h_2d(ctx, A + r0, (size_t)lda * sizeof(T), dA.p + r0, (size_t)dA.ld * sizeof(T),
+             (size_t)(r1 - r0) * sizeof(T), (size_t)n, ctx.d2h_stream);
       done = r1;
     };
   }
   getrf<T>(ctx, m, n, dA.p, dA.ld, d_ipiv, ctx.d_info);
   ctx.on_block_final = nullptr;
   if (m - done > 0)
-    LA_CUDA_CHECK(cudaMemcpy2DAsync(A + done, (size_t)lda * sizeof(T), dA.p + done,
-                                    (size_t)dA.ld * sizeof(T), (size_t)(m - done) * sizeof(T),
-                                    (size_t)n, cudaMemcpyDeviceToHost, ctx.stream));
+    d2h_2d(ctx, A + done, (size_t)lda * sizeof(T), dA.p + done, (size_t)dA.ld * sizeof(T),
+           (size_t)(m - done) * sizeof(T), (size_t)n, ctx.stream);
   LA_CUDA_CHECK(cudaStreamSynchronize(ctx.d2h_stream));
   for (auto e : evs) cudaEventDestroy(e);
 }
@@ -143,8 +141,8 @@ static void potrf_streamed_home(Context& ctx, int uplo, int64_t n, DevMat<T>& dA
     // lower: columns [c0, c1), rows c0..n ; upper: rows [c0, c1), columns c0..n
     const size_t width = (size_t)(lower ? n - c0 : c1 - c0) * sizeof(T);
     const size_t height = (size_t)(lower ? c1 - c0 : n - c0);
-    LA_CUDA_CHECK(cudaMemcpy2DAsync(h, (size_t)lda * sizeof(T), d, (size_t)dA.ld * sizeof(T), width,
-                                    height, cudaMemcpyDeviceToHost, ctx.d2h_stream));
+    d2h_2d(ctx, h, (size_t)lda * sizeof(T), d, (size_t)dA.ld * sizeof(T), width, height,
+           ctx.d2h_stream);
     done = c1;
   };
   potrf<T>(ctx, (Uplo)uplo, n, dA.p, dA.ld, ctx.d_info);

@@ -22,10 +22,16 @@ def _stream():
     return _p(torch.cuda.current_stream().cuda_stream)
 
 
+_FN_CACHE = {}
+
+
 def _fn(name, argtypes):
-    f = getattr(lib(), name)
-    f.argtypes = argtypes
-    f.restype = _int
+    f = _FN_CACHE.get(name)
+    if f is None:
+        f = getattr(lib(), name)
+        f.argtypes = argtypes
+        f.restype = _int
+        _FN_CACHE[name] = f
     return f
 
 

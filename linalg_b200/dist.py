@@ -435,3 +435,50 @@ def lstsq_tsqr(a_local: torch.Tensor, b_local: torch.Tensor, ops, group=None):
     c = r_all[n:, :n].contiguous()                                  # nrhs x n  (Q^H b)(0:n)
     ops.trtrs_upper(r, c)
     return c
+
+
+class HostGemmPlan:
+    """C <- A B + C for a product split by block columns over the ranks, operands in (pinned)
+    HOST memory on every rank: rank r holds its block columns of B and C and only the r-th slice
+    of A's columns.  Each rank uploads its slice of A over its own PCIe link and the slices are
+    all-gathered over NVLink, instead of every rank pulling the whole of A through the host
+    (world x the PCIe traffic of the replicated layout).  Device buffers are allocated once per
+    plan and reused by every `run`."""
+
+    def __init__(self, n: int, nc: int, dtype=torch.float64, group=None):
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.group, self.n, self.nc = group, n, nc
+        if n % self.world != 0:
+            raise ValueError("n must be a multiple of the number of ranks")
+        self.a_full = torch.empty((n, n), dtype=dtype, device="cuda")
+        self.b = torch.empty((nc, n), dtype=dtype, device="cuda")
+        self.c = torch.empty((nc, n), dtype=dtype, device="cuda")
+        self.copy = torch.cuda.Stream()
+        from . import dev
+        self.dev = dev
+
+    def a_slice(self):
+        """Column range [c0, c1) of A this rank must supply."""
+        w = self.n // self.world
+        return self.rank * w, (self.rank + 1) * w
+
+    def run(self, hA_slice: torch.Tensor, hB: torch.Tensor, hC: torch.Tensor):
+        """hA_slice: (n/world, n) host tensor = this rank's columns of A; hB, hC: (nc, n) host
+        tensors.  On return (host-synchronous) hC holds the result."""
+        n, nc, dev = self.n, self.nc, self.dev
+        c0, c1 = self.a_slice()
+        cur = torch.cuda.current_stream()
+        self.a_full[c0:c1].copy_(hA_slice, non_blocking=True)
+        if self.world > 1:
+            work = dist.all_gather_into_tensor(self.a_full, self.a_full[c0:c1], group=self.group,
+                                               async_op=True)
+        with torch.cuda.stream(self.copy):          # B and C travel while A is gathered
+            self.b.copy_(hB, non_blocking=True)
+            self.c.copy_(hC, non_blocking=True)
+        if self.world > 1:
+            work.wait()
+        cur.wait_stream(self.copy)
+        dev.gemm(dev.NO_TRANS, dev.NO_TRANS, n, nc, n, 1.0, self.a_full, n, self.b, n, 1.0, self.c, n)
+        hC.copy_(self.c, non_blocking=True)
+        cur.synchronize()

@@ -1,6 +1,6 @@
 """Multi-GPU check of linalg_b200/dist.py, launched as
    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-       --master-port 29511 tools/dist_gpu_check.py [--n 16384] [--nb 512] [--what potrf,getrf,tsqr]
+       --master-port 29511 tools/dist_gpu_check.py [--size 16384] [--nb 512] [--what potrf,getrf,tsqr]
        [--reserve 0,8] [--ctas 0,8] [--grids 2x4,1x8] [--single]
 Runs every (grid, reserve, ctas) combination in ONE process group and prints one JSON line per
 run from rank 0: device time (max over ranks), TFLOP/s of the whole job and the distributed probe
@@ -21,7 +21,7 @@ from linalg_b200 import dist_measure as dm      # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=16384)
+    ap.add_argument("--size", type=int, default=16384)
     ap.add_argument("--nb", default="512")
     ap.add_argument("--what", default="potrf,getrf,tsqr")
     ap.add_argument("--reserve", default="0")
@@ -48,7 +48,7 @@ def main():
     if args.single and rank == 0:
         for kind in ("potrf", "getrf"):
             if kind in what:
-                say(f"single_{kind}", dm.run_single_gpu(kind, args.n))
+                say(f"single_{kind}", dm.run_single_gpu(kind, args.size))
     if world > 1:
         dist.barrier()
     for ctas in [int(x) for x in args.ctas.split(",")]:
@@ -57,14 +57,14 @@ def main():
                 grid = ladist.Grid(P, Q, comm_ctas=ctas)
                 for nb in nbs:
                     for rs in [int(x) for x in args.reserve.split(",")]:
-                        d = dm.run_potrf(args.n, nb, grid, reserve_sms=rs, reps=args.reps,
+                        d = dm.run_potrf(args.size, nb, grid, reserve_sms=rs, reps=args.reps,
                                          warm_n=nb * Q * 2)
                         say("potrf", {"comm_ctas": ctas, **d})
         if "getrf" in what:
             grid = ladist.Grid(1, world, comm_ctas=ctas)
             for nb in nbs:
                 for rs in [int(x) for x in args.reserve.split(",")]:
-                    d = dm.run_getrf(args.n, nb, grid, reserve_sms=rs, reps=args.reps,
+                    d = dm.run_getrf(args.size, nb, grid, reserve_sms=rs, reps=args.reps,
                                      warm_n=nb * world * 2)
                     say("getrf", {"comm_ctas": ctas, **d})
     if "tsqr" in what:
