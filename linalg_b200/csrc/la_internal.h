@@ -57,6 +57,11 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
                  const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
                  int64_t ldc, int tri);
 
+// S (p x q) = X^H Y for tall X (m x p), Y (m x q), p, q <= 64 (tall_gram.cu); false: not taken.
+template <typename T>
+bool tall_gram(Context& ctx, int64_t p, int64_t q, int64_t m, const T* X, int64_t ldx, const T* Y,
+               int64_t ldy, T* S, int64_t lds);
+
 // C = alpha*op(A)*op(A)^H + beta*C on one triangle (trans = OpN: A is n x k; else k x n).
 template <typename T>
 void herk(Context& ctx, Uplo uplo, Op trans, int64_t n, int64_t k, double alpha, const T* A,

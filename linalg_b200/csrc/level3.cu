@@ -20,11 +20,26 @@ int& last_gemm_path() {
   return path;
 }
 
+// op(A)^H-times-B products with a tiny result and a very long reduction (block reflectors of a
+// tall-skinny QR) have their own streaming kernel
+template <typename T>
+static bool try_tall_gram(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, T alpha,
+                          const T* A, int64_t lda, const T* B, int64_t ldb, T beta, T* C,
+                          int64_t ldc, int tri) {
+  const bool conj_a = ta == OpC || (ta == OpT && !Traits<T>::is_complex);
+  if (!conj_a || tb != OpN || tri != TriFull || m > 64 || n > 64 || k < 8192) return false;
+  if (!is_one(alpha) || !is_zero(beta)) return false;
+  if (!tall_gram<T>(ctx, m, n, k, A, lda, B, ldb, C, ldc)) return false;
+  last_gemm_path() = 4;
+  return true;
+}
+
 template <>
 void gemm<double>(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, double alpha,
                   const double* A, int64_t lda, const double* B, int64_t ldb, double beta,
                   double* C, int64_t ldc, int tri, bool herm_diag) {
   if (m <= 0 || n <= 0) return;
+  if (try_tall_gram<double>(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri)) return;
   if (gemm_dmma_f64(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri)) {
     last_gemm_path() = 1;
     return;
@@ -37,6 +52,7 @@ void gemm<zcomplex>(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k,
                     const zcomplex* A, int64_t lda, const zcomplex* B, int64_t ldb,
                     zcomplex beta, zcomplex* C, int64_t ldc, int tri, bool herm_diag) {
   if (m <= 0 || n <= 0) return;
+  if (try_tall_gram<zcomplex>(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri)) return;
   if (gemm_dmma_z(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri, herm_diag)) {
     last_gemm_path() = 2;
     return;
@@ -49,6 +65,7 @@ void gemm<float>(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
                  const float* A, int64_t lda, const float* B, int64_t ldb, float beta, float* C,
                  int64_t ldc, int tri, bool herm_diag) {
   if (m <= 0 || n <= 0) return;
+  if (try_tall_gram<float>(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri)) return;
   if (gemm_tf32x3(ctx, ta, tb, m, n, k, alpha, A, lda, B, ldb, beta, C, ldc, tri)) {
     last_gemm_path() = 3;
     return;

@@ -22,7 +22,7 @@ namespace {
 
 constexpr int QR_NT = 256;
 constexpr int QR_MAX_JB = 32;
-constexpr int QR_MAX_CTAS = 160;
+constexpr int QR_MAX_CTAS = 640;
 constexpr size_t QR_SMEM_BUDGET = 200 * 1024;
 
 template <typename T>
@@ -214,20 +214,18 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tall panels (the row slice of a CTA does not fit shared memory, e.g. 2^20 x 32): streaming
+// Tall panels (the row slice of a CTA does not fit shared memory, e.g. 2^20 x 8): streaming
 // variant.  Same mathematics and the same one-grid-barrier-per-column exchange, but the
 // application of reflector j and the partial sums that define reflector j+1 are FUSED into a
-// single pass over the CTA's rows: each row is read once and written once per column, every
-// thread keeps one row of the panel in registers with all its loads in flight, so a column step
-// costs 2*(jb-j)*rows*sizeof(T) bytes of HBM traffic and runs at memory bandwidth.
-template <typename T> struct StreamJb { static constexpr int N = 32; };
-template <> struct StreamJb<zcomplex> { static constexpr int N = 16; };
-
-template <typename T>
+// single pass over the CTA's rows: each row is read once and written once per column.  A thread
+// keeps U rows of the (at most JB-column) panel in registers with all their loads in flight, and
+// several CTAs share an SM, so that a pass runs at memory bandwidth.  The HBM/L2 traffic of a
+// panel is 2 * (jb + 1) * jb / 2 * rows * sizeof(T) bytes, quadratic in its width: geqrf therefore
+// factors tall matrices in 8-column panels inside a recursive block structure.
+template <typename T, int JB, int U>
 __global__ void __launch_bounds__(QR_NT)
 qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
                        QrExchange<T>* xch, int64_t rpc) {
-  constexpr int JB = StreamJb<T>::N;
   __shared__ T s_f[QR_MAX_JB];
   __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
   __shared__ T s_scale, s_beta;
@@ -248,48 +246,57 @@ qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __
 #pragma unroll
     for (int c = 0; c < JB; c++) acc[c] = zero<T>();
     const T scale = ja >= 0 ? s_scale : zero<T>();
-    for (int64_t r = tid; r < nr; r += QR_NT) {
-      const int64_t gr = rs + r;
-      if (gr < ja) continue;                      // finished rows of R
-      if (ja < 0 && gr < 0) continue;
-      T a[JB];
-      const int c_lo = ja >= 0 ? ja : 0;
+    const int c_lo = ja >= 0 ? ja : 0;
+    for (int64_t r0 = tid; r0 < nr; r0 += (int64_t)U * QR_NT) {
+      T a[U][JB];
+      bool live[U];
 #pragma unroll
-      for (int c = 0; c < JB; c++)
-        a[c] = (c >= c_lo && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
-      if (ja >= 0) {
-        if (gr == ja) {                           // the reflector's own row: v = 1
-#pragma unroll
-          for (int c = 0; c < JB; c++) {
-            if (c == ja) a[c] = s_beta;
-            else if (c > ja && c < jb) a[c] = sub(a[c], s_f[c]);
-          }
-        } else {                                  // gr > ja: v = x * scale
-          T v = zero<T>();
-#pragma unroll
-          for (int c = 0; c < JB; c++)
-            if (c == ja) { v = mul(a[c], scale); a[c] = v; }
-#pragma unroll
-          for (int c = 0; c < JB; c++)
-            if (c > ja && c < jb) a[c] = fnma_(v, s_f[c], a[c]);
-        }
+      for (int u = 0; u < U; u++) {
+        const int64_t r = r0 + (int64_t)u * QR_NT;
+        live[u] = r < nr && rs + r >= ja;         // rows above ja are finished rows of R
 #pragma unroll
         for (int c = 0; c < JB; c++)
-          if (c >= ja && c < jb) base[(int64_t)c * lda + r] = a[c];
+          a[u][c] = (live[u] && c >= c_lo && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
       }
-      if (js < kmax) {
-        if (gr == js) {                           // next reflector's own row: publish it
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        if (!live[u]) continue;
+        const int64_t r = r0 + (int64_t)u * QR_NT;
+        const int64_t gr = rs + r;
+        if (ja >= 0) {
+          if (gr == ja) {                           // the reflector's own row: v = 1
+#pragma unroll
+            for (int c = 0; c < JB; c++) {
+              if (c == ja) a[u][c] = s_beta;
+              else if (c > ja && c < jb) a[u][c] = sub(a[u][c], s_f[c]);
+            }
+          } else {                                  // gr > ja: v = x * scale
+            T v = zero<T>();
+#pragma unroll
+            for (int c = 0; c < JB; c++)
+              if (c == ja) { v = mul(a[u][c], scale); a[u][c] = v; }
+#pragma unroll
+            for (int c = 0; c < JB; c++)
+              if (c > ja && c < jb) a[u][c] = fnma_(v, s_f[c], a[u][c]);
+          }
 #pragma unroll
           for (int c = 0; c < JB; c++)
-            if (c >= js && c < jb) st_cg<T>(&xch->rowj[js & 1][c], a[c]);
-        } else if (gr > js) {
-          T x = zero<T>();
+            if (c >= ja && c < jb) base[(int64_t)c * lda + r] = a[u][c];
+        }
+        if (js < kmax) {
+          if (gr == js) {                           // next reflector's own row: publish it
 #pragma unroll
-          for (int c = 0; c < JB; c++)
-            if (c == js) x = conj_(a[c]);
+            for (int c = 0; c < JB; c++)
+              if (c >= js && c < jb) st_cg<T>(&xch->rowj[js & 1][c], a[u][c]);
+          } else if (gr > js) {
+            T x = zero<T>();
 #pragma unroll
-          for (int c = 0; c < JB; c++)
-            if (c >= js && c < jb) acc[c] = fma_(x, a[c], acc[c]);
+            for (int c = 0; c < JB; c++)
+              if (c == js) x = conj_(a[u][c]);
+#pragma unroll
+            for (int c = 0; c < JB; c++)
+              if (c >= js && c < jb) acc[c] = fma_(x, a[u][c], acc[c]);
+          }
         }
       }
     }
@@ -381,6 +388,39 @@ struct QrWork {
   int64_t ldw;
 };
 
+// launch the streaming kernel on as many co-resident CTAs as the occupancy allows (at least
+// 1024 rows each): the more loads in flight, the closer a pass gets to the HBM bandwidth
+template <typename T, int JB, int U>
+void launch_stream(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch) {
+  static int per_sm[DeviceOnce::kMax] = {};
+  const int dev = ctx.device >= 0 && ctx.device < DeviceOnce::kMax ? ctx.device : 0;
+  if (per_sm[dev] == 0) {
+    int nb = 1;
+    LA_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+        &nb, qr_panel_stream_kernel<T, JB, U>, QR_NT, 0));
+    per_sm[dev] = nb < 1 ? 1 : (nb > 4 ? 4 : nb);
+  }
+  const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+  int64_t G = (int64_t)sms * per_sm[dev];
+  if (G > QR_MAX_CTAS) G = QR_MAX_CTAS;
+  const int64_t by_rows = ceil_div(mp, (int64_t)1024);
+  if (G > by_rows) G = by_rows;
+  if (G < 1) G = 1;
+  int64_t rpc = round_up(ceil_div(mp, G), 2);
+  G = ceil_div(mp, rpc);
+  void* sargs[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc};
+  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_stream_kernel<T, JB, U>,
+                                            dim3((unsigned)G), dim3(QR_NT), sargs, 0, ctx.stream));
+}
+
+// true when an mp x QR_MAX_JB panel does not fit the shared memory of all SMs together: such
+// panels are streamed from global memory
+template <typename T>
+bool qr_panel_is_tall(Context& ctx, int64_t mp) {
+  return (size_t)round_up(ceil_div(mp, (int64_t)ctx.sm_count), 2) * QR_MAX_JB * sizeof(T) >
+         QR_SMEM_BUDGET;
+}
+
 template <typename T>
 void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch) {
   int64_t G = ceil_div(mp, 512);
@@ -400,9 +440,16 @@ void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
   }
   LA_CUDA_CHECK(cudaMemsetAsync(&xch->barrier, 0, sizeof(unsigned), ctx.stream));
   if (!use_smem) {
-    void* sargs[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc};
-    LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_stream_kernel<T>, dim3((unsigned)G),
-                                              dim3(QR_NT), sargs, 0, ctx.stream));
+    if (jb <= 8) launch_stream<T, 8, 4>(ctx, mp, jb, A, lda, tau, xch);
+    else if (jb <= 16) launch_stream<T, 16, 2>(ctx, mp, jb, A, lda, tau, xch);
+    else {
+      if constexpr (Traits<T>::is_complex) {
+        fprintf(stderr, "la_b200: internal error: complex streaming QR panel wider than 16\n");
+        abort();
+      } else {
+        launch_stream<T, 32, 1>(ctx, mp, jb, A, lda, tau, xch);
+      }
+    }
     return;
   }
   void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem};
@@ -473,30 +520,136 @@ QrWork<T> make_work(Context& ctx, int64_t vrows, int64_t w_rows, int64_t w_cols)
 
 }  // namespace
 
+namespace {
+
+// Workspace of one block of at most QR_NB reflectors (geqrf_ex): a clean copy of the reflectors
+// (unit diagonal, zeros above), the block's T factor, and the small matrices of the updates.
+constexpr int QR_NB = 128;
+
 template <typename T>
-void geqrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau) {
+struct QrBlock {
+  QrExchange<T>* xch;
+  T* Vc; int64_t ldv;      // (rows of the block) x QR_NB
+  T* Tb;                   // QR_NB x QR_NB, upper triangular (ld QR_NB)
+  T* X; T* X2;             // QR_NB x QR_NB scratch
+  T* G;                    // QR_MAX_JB x QR_MAX_JB Gram matrix of a leaf
+  T* W; T* W2; int64_t ldw;  // (columns to update) x QR_NB
+  int64_t b0;              // first column (= first row) of the block
+  int leaf;                // leaf panel width
+};
+
+// C <- H^H C with H = I - V T V^H (V: mrows x jb, unit lower trapezoidal, clean; T: jb x jb).
+// The products with the long reduction are formed transposed (W^H = C^H V is ncols x jb), so
+// that the jb reflectors sit on the N side of the GEMM, where narrow tiles / split-K apply.
+template <typename T>
+void apply_block_left_conj(Context& ctx, int64_t mrows, int64_t ncols, int64_t jb, const T* V,
+                           int64_t ldv, const T* Tm, int64_t ldt, T* C, int64_t ldc, QrBlock<T>& w) {
+  if (mrows <= 0 || ncols <= 0 || jb <= 0) return;
+  const T onev = one<T>(), zerov = zero<T>(), mone = from_real<T>(-1.0);
+  gemm<T>(ctx, OpC, OpN, ncols, jb, mrows, onev, C, ldc, V, ldv, zerov, w.W, w.ldw);
+  gemm<T>(ctx, OpN, OpN, ncols, jb, jb, onev, w.W, w.ldw, Tm, ldt, zerov, w.W2, w.ldw);
+  gemm<T>(ctx, OpN, OpC, mrows, ncols, jb, mone, V, ldv, w.W2, w.ldw, onev, C, ldc);
+}
+
+// Factor columns [j0, j0 + jn) of A (rows j0..m), all earlier reflectors applied, and leave the
+// clean reflectors in w.Vc and their T factor in w.Tb.  Recursive halving: the left half is
+// factored, applied to the right half, the right half is factored, and the two T factors are
+// merged,  T = [T1, -T1 (V1^H V2) T2; 0, T2].
+template <typename T>
+void qr_rec(Context& ctx, int64_t m, T* A, int64_t lda, T* tau, int64_t j0, int64_t jn,
+            QrBlock<T>& w) {
+  const int64_t o = j0 - w.b0;                 // offset inside the block
+  T* Vn = w.Vc + o + o * w.ldv;                // reflectors of this node, rows from j0
+  T* Tn = w.Tb + o + o * QR_NB;
+  const int64_t mp = m - j0;
+  if (jn <= w.leaf) {
+    T* P = A + j0 + j0 * lda;
+    qr_panel<T>(ctx, mp, (int)jn, P, lda, tau + j0, w.xch);
+    const int64_t kk = mp < jn ? mp : jn;      // reflectors actually produced
+    copy_triangle<T>(ctx, Lower, true, mp, jn, P, lda, Vn, w.ldv);
+    gemm<T>(ctx, OpC, OpN, kk, kk, mp, one<T>(), Vn, w.ldv, Vn, w.ldv, zero<T>(), w.G, QR_MAX_JB);
+    larft_kernel<T><<<1, 64, 0, ctx.stream>>>((int)kk, w.G, QR_MAX_JB, tau + j0, Tn, QR_NB);
+    LA_CUDA_CHECK(cudaGetLastError());
+    return;
+  }
+  int64_t h = round_up(jn / 2, (int64_t)w.leaf);
+  if (h >= jn) h = jn - w.leaf;
+  qr_rec<T>(ctx, m, A, lda, tau, j0, h, w);
+  apply_block_left_conj<T>(ctx, mp, jn - h, h, Vn, w.ldv, Tn, QR_NB, A + j0 + (j0 + h) * lda, lda, w);
+  if (mp - h <= 0) return;                     // (only when m < n: nothing left below)
+  qr_rec<T>(ctx, m, A, lda, tau, j0 + h, jn - h, w);
+  // merge: rows j0+h.. of V1 against V2 (V2 is zero above them)
+  const T* V1s = Vn + h;
+  const T* V2 = Vn + h + h * w.ldv;
+  const T* T2 = Tn + h + h * QR_NB;
+  T* T12 = Tn + h * QR_NB;
+  const int64_t r2 = jn - h;
+  gemm<T>(ctx, OpC, OpN, h, r2, mp - h, one<T>(), V1s, w.ldv, V2, w.ldv, zero<T>(), w.X, QR_NB);
+  gemm<T>(ctx, OpN, OpN, h, r2, h, from_real<T>(-1.0), Tn, QR_NB, w.X, QR_NB, zero<T>(), w.X2, QR_NB);
+  gemm<T>(ctx, OpN, OpN, h, r2, r2, one<T>(), w.X2, QR_NB, T2, QR_NB, zero<T>(), T12, QR_NB);
+}
+
+template <typename T>
+__global__ void zero_square_kernel(int n, T* A, int64_t lda) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int j = blockIdx.y; j < n; j += gridDim.y) A[i + (int64_t)j * lda] = zero<T>();
+}
+
+}  // namespace
+
+// Householder QR of A with the reflectors also applied to nrhs extra columns B (B <- Q^H B;
+// nrhs = 0: plain ?geqrf).  Blocks of QR_NB columns, each factored recursively from leaf panels
+// (8 columns when the panel has to be streamed from HBM, 32 when it fits shared memory); the
+// columns right of a block, and B, receive one rank-QR_NB update per block.
+template <typename T>
+void geqrf_ex(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau, int64_t nrhs, T* B,
+              int64_t ldb) {
   const int64_t k = m < n ? m : n;
   if (k <= 0) return;
   ensure_attrs<T>(ctx);
   Arena::Mark mk = ctx.arena.mark();
-  QrWork<T> w = make_work<T>(ctx, m, QR_MAX_JB, n);
-  // panels too tall for the shared-memory kernel go through the streaming kernel, which holds
-  // a row of the panel in registers: narrower panels for complex
-  const bool tall = (size_t)round_up(ceil_div(m, ctx.sm_count), 2) * QR_MAX_JB * sizeof(T) >
-                    QR_SMEM_BUDGET;
-  const int64_t nb = tall ? StreamJb<T>::N : QR_MAX_JB;
-  for (int64_t j0 = 0; j0 < k; j0 += nb) {
-    const int jb = (int)((k - j0) < nb ? (k - j0) : nb);
-    const int64_t mp = m - j0;
-    T* P = A + j0 + j0 * lda;
-    qr_panel<T>(ctx, mp, jb, P, lda, d_tau + j0, w.xch);
-    const int64_t nc = n - j0 - jb;
-    if (nc > 0) {
-      form_block_reflector<T>(ctx, mp, jb, P, lda, d_tau + j0, w);
-      apply_block_reflector<T>(ctx, Left, OpC, mp, nc, jb, w, A + j0 + (j0 + jb) * lda, lda);
+  QrBlock<T> w;
+  w.xch = (QrExchange<T>*)ctx.arena.alloc(sizeof(QrExchange<T>));
+  w.ldv = round_up(m, 16);
+  w.Vc = ctx.alloc<T>(w.ldv * QR_NB);
+  w.Tb = ctx.alloc<T>(QR_NB * QR_NB);
+  w.X = ctx.alloc<T>(QR_NB * QR_NB);
+  w.X2 = ctx.alloc<T>(QR_NB * QR_NB);
+  w.G = ctx.alloc<T>(QR_MAX_JB * QR_MAX_JB);
+  const int64_t wc = (n > nrhs ? n : nrhs);
+  w.ldw = round_up(wc > 0 ? wc : 1, 16);
+  w.W = ctx.alloc<T>(w.ldw * QR_NB);
+  w.W2 = ctx.alloc<T>(w.ldw * QR_NB);
+  w.leaf = qr_panel_is_tall<T>(ctx, m) ? 8 : QR_MAX_JB;
+  for (int64_t b0 = 0; b0 < k; b0 += QR_NB) {
+    const int64_t bw = (k - b0) < QR_NB ? (k - b0) : QR_NB;
+    const int64_t mp = m - b0;
+    w.b0 = b0;
+    // the part of Vc above the diagonal of later leaves and the lower part of Tb must be zero
+    {
+      const int sq = (int)(mp < QR_NB ? mp : QR_NB);
+      dim3 g((unsigned)ceil_div(sq, 128), (unsigned)sq);
+      zero_square_kernel<T><<<g, 128, 0, ctx.stream>>>(sq, w.Vc, w.ldv);
+      dim3 g2(1, QR_NB);
+      zero_square_kernel<T><<<g2, 128, 0, ctx.stream>>>(QR_NB, w.Tb, QR_NB);
+      LA_CUDA_CHECK(cudaGetLastError());
     }
+    qr_rec<T>(ctx, m, A, lda, d_tau, b0, bw, w);
+    const int64_t kk = mp < bw ? mp : bw;
+    const int64_t nc = n - b0 - bw;
+    if (nc > 0)
+      apply_block_left_conj<T>(ctx, mp, nc, kk, w.Vc, w.ldv, w.Tb, QR_NB, A + b0 + (b0 + bw) * lda,
+                               lda, w);
+    if (nrhs > 0)
+      apply_block_left_conj<T>(ctx, mp, nrhs, kk, w.Vc, w.ldv, w.Tb, QR_NB, B + b0, ldb, w);
   }
   ctx.arena.release(mk);
+}
+
+template <typename T>
+void geqrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau) {
+  geqrf_ex<T>(ctx, m, n, A, lda, d_tau, 0, nullptr, 0);
 }
 
 template <typename T>
@@ -570,12 +723,12 @@ void gels(Context& ctx, Op trans, int64_t m, int64_t n, int64_t nrhs, T* A, int6
   Arena::Mark mk = ctx.arena.mark();
   T* tau = ctx.alloc<T>(mn);
   if (m >= n) {
-    geqrf<T>(ctx, m, n, A, lda, tau);
     if (!tpose) {
-      // least squares: B <- Q^H B, solve R X = B(0:n)
-      ormqr<T>(ctx, Left, OpC, m, nrhs, n, A, lda, tau, B, ldb);
+      // least squares: B <- Q^H B (applied block by block while A is factored), solve R X = B(0:n)
+      geqrf_ex<T>(ctx, m, n, A, lda, tau, nrhs, B, ldb);
       trtrs<T>(ctx, Upper, OpN, NonUnit, n, nrhs, A, lda, B, ldb, d_info);
     } else {
+      geqrf<T>(ctx, m, n, A, lda, tau);
       // minimum norm of A^H X = B: X = Q [R^-H B; 0]
       trtrs<T>(ctx, Upper, OpC, NonUnit, n, nrhs, A, lda, B, ldb, d_info);
       zero_rows<T>(ctx, n, m, nrhs, B, ldb);

@@ -455,6 +455,7 @@ class HostGemmPlan:
         self.b = torch.empty((nc, n), dtype=dtype, device="cuda")
         self.c = torch.empty((nc, n), dtype=dtype, device="cuda")
         self.copy = torch.cuda.Stream()
+        self.down = torch.cuda.Stream()
         from . import dev
         self.dev = dev
 
@@ -463,22 +464,43 @@ class HostGemmPlan:
         w = self.n // self.world
         return self.rank * w, (self.rank + 1) * w
 
-    def run(self, hA_slice: torch.Tensor, hB: torch.Tensor, hC: torch.Tensor):
+    def run(self, hA_slice: torch.Tensor, hB: torch.Tensor, hC: torch.Tensor, nchunks: int = 8):
         """hA_slice: (n/world, n) host tensor = this rank's columns of A; hB, hC: (nc, n) host
-        tensors.  On return (host-synchronous) hC holds the result."""
+        tensors.  On return (host-synchronous) hC holds the result.
+
+        A's slice goes up first and is gathered over NVLink while B and C follow in column
+        chunks on the copy stream; chunk j is multiplied as soon as it has landed and travels
+        home on a third stream while chunk j+1 is multiplied."""
         n, nc, dev = self.n, self.nc, self.dev
         c0, c1 = self.a_slice()
         cur = torch.cuda.current_stream()
+        self.copy.wait_stream(cur)
+        self.down.wait_stream(cur)
         self.a_full[c0:c1].copy_(hA_slice, non_blocking=True)
+        work = None
         if self.world > 1:
             work = dist.all_gather_into_tensor(self.a_full, self.a_full[c0:c1], group=self.group,
                                                async_op=True)
-        with torch.cuda.stream(self.copy):          # B and C travel while A is gathered
-            self.b.copy_(hB, non_blocking=True)
-            self.c.copy_(hC, non_blocking=True)
-        if self.world > 1:
+        step = max(128, -(-nc // nchunks) // 128 * 128)
+        chunks = [(j, min(nc, j + step)) for j in range(0, nc, step)]
+        ups = []
+        with torch.cuda.stream(self.copy):
+            for j0, j1 in chunks:
+                self.b[j0:j1].copy_(hB[j0:j1], non_blocking=True)
+                self.c[j0:j1].copy_(hC[j0:j1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.copy)
+                ups.append(ev)
+        if work is not None:
             work.wait()
-        cur.wait_stream(self.copy)
-        dev.gemm(dev.NO_TRANS, dev.NO_TRANS, n, nc, n, 1.0, self.a_full, n, self.b, n, 1.0, self.c, n)
-        hC.copy_(self.c, non_blocking=True)
+        for (j0, j1), ev in zip(chunks, ups):
+            cur.wait_event(ev)
+            dev.gemm(dev.NO_TRANS, dev.NO_TRANS, n, j1 - j0, n, 1.0, self.a_full, n, self.b[j0:j1], n,
+                     1.0, self.c[j0:j1], n)
+            done = torch.cuda.Event()
+            done.record(cur)
+            with torch.cuda.stream(self.down):
+                self.down.wait_event(done)
+                hC[j0:j1].copy_(self.c[j0:j1], non_blocking=True)
+        cur.wait_stream(self.down)
         cur.synchronize()

@@ -212,3 +212,29 @@ def test_device_api_calls_on_two_streams_do_not_share_scratch_in_flight():
     mixed = run([torch.cuda.Stream(), torch.cuda.Stream()])
     for a, b in zip(serial, mixed):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32, torch.complex128])
+@pytest.mark.parametrize("p,q,m", [(8, 8, 100000), (16, 5, 65537), (32, 32, 200001), (64, 64, 70000),
+                                   (33, 64, 50000), (7, 24, 300000)])
+def test_tall_gram_products_match_a_double_precision_reference(dtype, p, q, m):
+    """X^H Y with a tiny result and a long reduction (the block-reflector products of the
+    tall-skinny QR) takes the streaming kernel: compare with torch in double precision, and make
+    sure two runs give the same bits (the partial sums are added in a fixed order)."""
+    from linalg_b200 import dev, ffi
+    g = torch.Generator(device="cuda").manual_seed(17)
+    ldx, ldy = m + 6, m + 2          # 16-byte aligned columns for every element type
+    X = torch.rand((p, ldx), dtype=dtype, device="cuda", generator=g) - 0.5
+    Y = torch.rand((q, ldy), dtype=dtype, device="cuda", generator=g) - 0.5
+    S = torch.full((q, p), 7.0, dtype=dtype, device="cuda")
+    S2 = torch.full((q, p), -3.0, dtype=dtype, device="cuda")
+    dev.gemm(ffi.CONJ_TRANS, ffi.NO_TRANS, p, q, m, 1.0, X, ldx, Y, ldy, 0.0, S, p)
+    path = dev.last_gemm_path()
+    dev.gemm(ffi.CONJ_TRANS, ffi.NO_TRANS, p, q, m, 1.0, X, ldx, Y, ldy, 0.0, S2, p)
+    assert torch.equal(S, S2)
+    hi = torch.complex128 if dtype.is_complex else torch.float64
+    ref = (X[:, :m].to(hi).conj() @ Y[:, :m].to(hi).T).T        # (q, p) = column-major p x q
+    tol = 2e-4 if dtype == torch.float32 else 1e-12
+    assert float((S.to(hi) - ref).abs().max()) <= tol * float(ref.abs().max())
+    if not (dtype.is_complex and max(p, q) > 32):
+        assert path == 4, "the tall-gram kernel was not taken"
