@@ -62,6 +62,11 @@ template <typename T>
 bool tall_gram(Context& ctx, int64_t p, int64_t q, int64_t m, const T* X, int64_t ldx, const T* Y,
                int64_t ldy, T* S, int64_t lds);
 
+// C (m x nc) -= V (m x h) Z^H for tall m and h, nc <= 64 (tall_gram.cu); false: not taken.
+template <typename T>
+bool tall_update(Context& ctx, int64_t m, int64_t h, int64_t nc, const T* V, int64_t ldv, const T* Z,
+                 int64_t ldz, T* C, int64_t ldc);
+
 // C = alpha*op(A)*op(A)^H + beta*C on one triangle (trans = OpN: A is n x k; else k x n).
 template <typename T>
 void herk(Context& ctx, Uplo uplo, Op trans, int64_t n, int64_t k, double alpha, const T* A,

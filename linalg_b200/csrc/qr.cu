@@ -398,7 +398,8 @@ void launch_stream(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, 
     int nb = 1;
     LA_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
         &nb, qr_panel_stream_kernel<T, JB, U>, QR_NT, 0));
-    per_sm[dev] = nb < 1 ? 1 : (nb > 4 ? 4 : nb);
+    static const int cap = getenv("LA_B200_QR_CTAS_PER_SM") ? atoi(getenv("LA_B200_QR_CTAS_PER_SM")) : 4;
+    per_sm[dev] = nb < 1 ? 1 : (nb > cap ? cap : nb);
   }
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
   int64_t G = (int64_t)sms * per_sm[dev];
@@ -546,9 +547,18 @@ void apply_block_left_conj(Context& ctx, int64_t mrows, int64_t ncols, int64_t j
                            int64_t ldv, const T* Tm, int64_t ldt, T* C, int64_t ldc, QrBlock<T>& w) {
   if (mrows <= 0 || ncols <= 0 || jb <= 0) return;
   const T onev = one<T>(), zerov = zero<T>(), mone = from_real<T>(-1.0);
-  gemm<T>(ctx, OpC, OpN, ncols, jb, mrows, onev, C, ldc, V, ldv, zerov, w.W, w.ldw);
+  if (ncols <= 64 && jb > 64 && mrows >= 8192) {
+    // few columns against a wide block (right-hand sides): 64 reflectors at a time, so that the
+    // streaming X^H Y kernel takes the product instead of 128-row tensor-core tiles
+    for (int64_t c0 = 0; c0 < jb; c0 += 64)
+      gemm<T>(ctx, OpC, OpN, ncols, (jb - c0) < 64 ? (jb - c0) : 64, mrows, onev, C, ldc,
+              V + c0 * ldv, ldv, zerov, w.W + c0 * w.ldw, w.ldw);
+  } else {
+    gemm<T>(ctx, OpC, OpN, ncols, jb, mrows, onev, C, ldc, V, ldv, zerov, w.W, w.ldw);
+  }
   gemm<T>(ctx, OpN, OpN, ncols, jb, jb, onev, w.W, w.ldw, Tm, ldt, zerov, w.W2, w.ldw);
-  gemm<T>(ctx, OpN, OpC, mrows, ncols, jb, mone, V, ldv, w.W2, w.ldw, onev, C, ldc);
+  if (!tall_update<T>(ctx, mrows, jb, ncols, V, ldv, w.W2, w.ldw, C, ldc))
+    gemm<T>(ctx, OpN, OpC, mrows, ncols, jb, mone, V, ldv, w.W2, w.ldw, onev, C, ldc);
 }
 
 // Factor columns [j0, j0 + jn) of A (rows j0..m), all earlier reflectors applied, and leave the

@@ -223,7 +223,7 @@ def test_tall_gram_products_match_a_double_precision_reference(dtype, p, q, m):
     sure two runs give the same bits (the partial sums are added in a fixed order)."""
     from linalg_b200 import dev, ffi
     g = torch.Generator(device="cuda").manual_seed(17)
-    ldx, ldy = m + 6, m + 2          # 16-byte aligned columns for every element type
+    ldx, ldy = (m + 7) // 8 * 8 + 8, (m + 7) // 8 * 8   # 16-byte aligned columns for every type
     X = torch.rand((p, ldx), dtype=dtype, device="cuda", generator=g) - 0.5
     Y = torch.rand((q, ldy), dtype=dtype, device="cuda", generator=g) - 0.5
     S = torch.full((q, p), 7.0, dtype=dtype, device="cuda")
