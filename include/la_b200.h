@@ -177,6 +177,77 @@ void dorgqr_(const int* m, const int* n, const int* k, double* a, const int* lda
              const double* tau, double* work, const int* lwork, int* info);
 void zungqr_(const int* m, const int* n, const int* k, void* a, const int* lda, const void* tau,
              void* work, const int* lwork, int* info);
+/* "next" row 2, rest: the RQ / LQ / QL siblings (src/linalg/rq_lq_ql.cr:3-39)
+ * ?gerqf: :1201, :633, :1743   ?gelqf: :1173, :605, :1715   ?geqlf: :1187, :619, :1729
+ * ?orgrq / zungrq: :1472, :904, :2203   ?orglq / zunglq: :1468, :900, :2199
+ * ?orgql / zungql: :1469, :901, :2200 */
+void sgerqf_(const int* m, const int* n, float* a, const int* lda, float* tau, float* work,
+             const int* lwork, int* info);
+void sgelqf_(const int* m, const int* n, float* a, const int* lda, float* tau, float* work,
+             const int* lwork, int* info);
+void sgeqlf_(const int* m, const int* n, float* a, const int* lda, float* tau, float* work,
+             const int* lwork, int* info);
+void sorgrq_(const int* m, const int* n, const int* k, float* a, const int* lda,
+             const float* tau, float* work, const int* lwork, int* info);
+void sorglq_(const int* m, const int* n, const int* k, float* a, const int* lda,
+             const float* tau, float* work, const int* lwork, int* info);
+void sorgql_(const int* m, const int* n, const int* k, float* a, const int* lda,
+             const float* tau, float* work, const int* lwork, int* info);
+void dgerqf_(const int* m, const int* n, double* a, const int* lda, double* tau, double* work,
+             const int* lwork, int* info);
+void dgelqf_(const int* m, const int* n, double* a, const int* lda, double* tau, double* work,
+             const int* lwork, int* info);
+void dgeqlf_(const int* m, const int* n, double* a, const int* lda, double* tau, double* work,
+             const int* lwork, int* info);
+void dorgrq_(const int* m, const int* n, const int* k, double* a, const int* lda,
+             const double* tau, double* work, const int* lwork, int* info);
+void dorglq_(const int* m, const int* n, const int* k, double* a, const int* lda,
+             const double* tau, double* work, const int* lwork, int* info);
+void dorgql_(const int* m, const int* n, const int* k, double* a, const int* lda,
+             const double* tau, double* work, const int* lwork, int* info);
+void zgerqf_(const int* m, const int* n, void* a, const int* lda, void* tau, void* work,
+             const int* lwork, int* info);
+void zgelqf_(const int* m, const int* n, void* a, const int* lda, void* tau, void* work,
+             const int* lwork, int* info);
+void zgeqlf_(const int* m, const int* n, void* a, const int* lda, void* tau, void* work,
+             const int* lwork, int* info);
+void zungrq_(const int* m, const int* n, const int* k, void* a, const int* lda,
+             const void* tau, void* work, const int* lwork, int* info);
+void zunglq_(const int* m, const int* n, const int* k, void* a, const int* lda,
+             const void* tau, void* work, const int* lwork, int* info);
+void zungql_(const int* m, const int* n, const int* k, void* a, const int* lda,
+             const void* tau, void* work, const int* lwork, int* info);
+/* QR with column pivoting (src/linalg/qr.cr:38-41; rank(method: QRP), src/linalg/linalg.cr:772-774)
+ * ?geqp3: :1188, :620, :1730 (the complex form carries rwork) */
+void sgeqp3_(const int* m, const int* n, float* a, const int* lda, int* jpvt, float* tau,
+             float* work, const int* lwork, int* info);
+void dgeqp3_(const int* m, const int* n, double* a, const int* lda, int* jpvt, double* tau,
+             double* work, const int* lwork, int* info);
+void zgeqp3_(const int* m, const int* n, void* a, const int* lda, int* jpvt, void* tau, void* work,
+             const int* lwork, double* rwork, int* info);
+/* "next" row 4: norms (src/linalg/linalg.cr:721-748) and the copy / fill helpers
+ * ?lange: :1335, :767, :1959   ?lansy: :1342, :774, :1969   zlanhe: :1962
+ * ?lantr: :1345, :777, :1972   ?lacpy: :1288, :720, :1929   ?laset: :1421, :853, :2019
+ * (REAL functions return float, FloatReturn = Float, libLAPACK_linux.cr:17; `work` is unused) */
+float slange_(const char* norm, const int* m, const int* n, const float* a, const int* lda, float* work);
+double dlange_(const char* norm, const int* m, const int* n, const double* a, const int* lda, double* work);
+double zlange_(const char* norm, const int* m, const int* n, const void* a, const int* lda, double* work);
+float slansy_(const char* norm, const char* uplo, const int* n, const float* a, const int* lda, float* work);
+double dlansy_(const char* norm, const char* uplo, const int* n, const double* a, const int* lda, double* work);
+double zlansy_(const char* norm, const char* uplo, const int* n, const void* a, const int* lda, double* work);
+double zlanhe_(const char* norm, const char* uplo, const int* n, const void* a, const int* lda, double* work);
+float slantr_(const char* norm, const char* uplo, const char* diag, const int* m, const int* n,
+              const float* a, const int* lda, float* work);
+double dlantr_(const char* norm, const char* uplo, const char* diag, const int* m, const int* n,
+               const double* a, const int* lda, double* work);
+double zlantr_(const char* norm, const char* uplo, const char* diag, const int* m, const int* n,
+               const void* a, const int* lda, double* work);
+void slacpy_(const char* uplo, const int* m, const int* n, const float* a, const int* lda, float* b, const int* ldb);
+void dlacpy_(const char* uplo, const int* m, const int* n, const double* a, const int* lda, double* b, const int* ldb);
+void zlacpy_(const char* uplo, const int* m, const int* n, const void* a, const int* lda, void* b, const int* ldb);
+void slaset_(const char* uplo, const int* m, const int* n, const float* alpha, const float* beta, float* a, const int* lda);
+void dlaset_(const char* uplo, const int* m, const int* n, const double* alpha, const double* beta, double* a, const int* lda);
+void zlaset_(const char* uplo, const int* m, const int* n, const void* alpha, const void* beta, void* a, const int* lda);
 
 /* ===================== Part 3: device-resident API ======================================
  * Same mathematics as the symbols above, but every matrix/ipiv/tau/info pointer is a DEVICE
@@ -235,6 +306,15 @@ int la_b200_set_sm_limit(int sms);
      order: the ?laswp step inside ?getrf/?getrs, exported for the multi-GPU LU */               \
   int la_b200_##X##laswp_dev(int64_t m, int64_t n, T* a, int64_t lda, int64_t k1, int64_t k2,     \
                              const int* ipiv, void* stream);                                      \
+  /* ?lange / ?lacpy / ?laset on resident matrices: norm = 'M', 'O', 'I' or 'F'; the norm is    \
+     written to the DEVICE double `result`; uplo = 'U', 'L' or anything else for the whole  \
+     matrix; alpha / beta by pointer */                                                         \
+  int la_b200_##X##lange_dev(int norm, int64_t m, int64_t n, const T* a, int64_t lda,             \
+                             double* result, void* stream);                                       \
+  int la_b200_##X##lacpy_dev(int uplo, int64_t m, int64_t n, const T* a, int64_t lda, T* b,       \
+                             int64_t ldb, void* stream);                                          \
+  int la_b200_##X##laset_dev(int uplo, int64_t m, int64_t n, const void* alpha, const void* beta, \
+                             T* a, int64_t lda, void* stream);                                    \
   int la_b200_##X##getrs_dev(int trans, int64_t n, int64_t nrhs, const T* a, int64_t lda,         \
                              const int* ipiv, T* b, int64_t ldb, void* stream);                   \
   int la_b200_##X##potrf_dev(int uplo, int64_t n, T* a, int64_t lda, int* info, void* stream);    \
@@ -262,6 +342,22 @@ LA_B200_DECL_DEV(z, void)
  * array (nothing is allocated in that case either). */
 int la_b200_dgetrf_dev_noalloc(int64_t m, int64_t n, double* a, int64_t lda, int* ipiv, int* info,
                                void* stream);
+
+/* Device-matrix handles (no counterpart in the reference): a host that runs
+ * a CHAIN of products and solves — `**` (src/linalg/power.cr:19-30), expm-style code
+ * (src/linalg/expm.cr:37-111) — creates its operands once, uploads once, calls the *_dev entry
+ * points on la_b200_mat_ptr / la_b200_mat_ld, and downloads the result once, instead of paying
+ * an upload and a download per call of the drop-in symbols.  type = 's', 'd' or 'z'; the
+ * leading dimension is the row count rounded up to 16.  upload / download are synchronous;
+ * NULL on allocation failure; -1 / -3: bad handle or pointer / leading dimension. */
+void* la_b200_mat_create(int type, int64_t rows, int64_t cols);
+void la_b200_mat_free(void* handle);
+void* la_b200_mat_ptr(void* handle);
+int64_t la_b200_mat_ld(void* handle);
+int64_t la_b200_mat_rows(void* handle);
+int64_t la_b200_mat_cols(void* handle);
+int la_b200_mat_upload(void* handle, const void* host, int64_t ldh);
+int la_b200_mat_download(void* handle, void* host, int64_t ldh);
 
 /* library identification / diagnostics */
 const char* la_b200_version(void);

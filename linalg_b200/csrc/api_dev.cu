@@ -69,6 +69,18 @@ int d_gemm_stair(int ta, int tb, int64_t m, int64_t n, int64_t k, T alpha, const
 }
 
 template <typename T>
+int d_lange(int norm, int64_t m, int64_t n, const T* A, int64_t lda, double* result, void* stream) {
+  const int kind = norm_kind_from_char((char)norm);
+  if (kind < 0) return -1;
+  if (m < 0) return -2;
+  if (n < 0) return -3;
+  if (lda < (m > 1 ? m : 1)) return -5;
+  DevCall c(stream);
+  matrix_norm<T>(*c.ctx, kind, ShapeGeneral, Upper, false, m, n, A, lda, result);
+  return 0;
+}
+
+template <typename T>
 int d_trsm(int side, int uplo, int ta, int diag, int64_t m, int64_t n, const void* alpha,
            const T* A, int64_t lda, T* B, int64_t ldb, void* stream) {
   if (!valid_side(side)) return -1;
@@ -231,6 +243,10 @@ using namespace la;
   int la_b200_##X##laswp_dev(int64_t m, int64_t n, VT* a, int64_t lda, int64_t k1, int64_t k2,    \
                              const int* ipiv, void* stream) {                                     \
     return d_laswp<T>(m, n, (T*)a, lda, k1, k2, ipiv, stream);                                    \
+  }                                                                                               \
+  int la_b200_##X##lange_dev(int norm, int64_t m, int64_t n, const VT* a, int64_t lda,            \
+                             double* result, void* stream) {                                      \
+    return d_lange<T>(norm, m, n, (const T*)a, lda, result, stream);                              \
   }                                                                                               \
   int la_b200_##X##getrs_dev(int trans, int64_t n, int64_t nrhs, const VT* a, int64_t lda,        \
                              const int* ipiv, VT* b, int64_t ldb, void* stream) {                 \

@@ -143,6 +143,26 @@ void ormqr(Context& ctx, Side side, Op trans, int64_t m, int64_t n, int64_t k, c
            int64_t lda, const T* d_tau, T* C, int64_t ldc);
 template <typename T>  // generate the leading n columns of Q (orgqr / ungqr)
 void orgqr(Context& ctx, int64_t m, int64_t n, int64_t k, T* A, int64_t lda, const T* d_tau);
+// matrix norms (aux_ops.cu): the result lands in a device double
+enum NormKind : int { NormMax = 0, NormOne = 1, NormInf = 2, NormFro = 3 };
+enum NormShape : int { ShapeGeneral = 0, ShapeSym = 1, ShapeHerm = 2, ShapeTri = 3 };
+int norm_kind_from_char(char c);    // 'M', 'O' / '1', 'I', 'F' / 'E' -> NormKind, else -1
+template <typename T>
+void matrix_norm(Context& ctx, int kind, int shape, Uplo uplo, bool unit, int64_t m, int64_t n,
+                 const T* A, int64_t lda, double* d_out);
+
+// RQ ('R'), LQ ('L'), QL ('Q') factorisations in LAPACK's storage, and their Q generators
+template <typename T>
+void geqrf_variant(Context& ctx, char which, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau);
+template <typename T>
+void orgqr_variant(Context& ctx, char which, int64_t m, int64_t n, int64_t k, T* A, int64_t lda,
+                   const T* d_tau);
+// QR with column pivoting; d_jpvt holds the starting permutation (fixed columns first)
+template <typename T>
+void geqp3(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_jpvt, T* d_tau,
+           int64_t nfixed);
+template <typename T>
+void swap_columns(Context& ctx, int64_t m, T* a, T* b);
 template <typename T>
 void gels(Context& ctx, Op trans, int64_t m, int64_t n, int64_t nrhs, T* A, int64_t lda, T* B,
           int64_t ldb, int* d_info);

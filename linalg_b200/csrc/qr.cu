@@ -765,12 +765,322 @@ void gels(Context& ctx, Op trans, int64_t m, int64_t n, int64_t nrhs, T* A, int6
   ctx.arena.release(mk);
 }
 
+// =============================================================================================
+// RQ / LQ / QL factorisations and their Q generators (src/linalg/rq_lq_ql.cr:3-39 ->
+// ?gerqf_/?gelqf_/?geqlf_, ?orgrq_/?orglq_/?orgql_ and the zung* forms).  Each is the QR
+// factorisation of a mirrored and / or conjugate-transposed copy of A, which gives exactly
+// LAPACK's storage: ?gelq2 / ?gerq2 / ?geql2 generate the same ?larfg reflectors as ?geqr2 does
+// on that copy (rows instead of columns, last-to-first instead of first-to-last).
+//   LQ:  A^H            = Q R   ->  A = R^H Q^H            tau as returned
+//   QL:  J A J          = Q R   ->  A = (J Q J)(J R J)     tau reversed
+//   RQ:  (J A J)^H      = Q R   ->  A = (J R^H J)(J Q^H J) tau reversed
+namespace {
+
+// B (rows x cols of the RESULT) from A: optional mirror of both index ranges, optional conjugate
+// transposition.  mode bit 0: conjugate-transpose, bit 1: mirror.  A is ma x na.
+template <typename T>
+__global__ void mirror_copy_kernel(int mode, int64_t ma, int64_t na, const T* __restrict__ A,
+                                   int64_t lda, T* __restrict__ B, int64_t ldb) {
+  const bool tr = mode & 1, mir = mode & 2;
+  const int64_t mb = tr ? na : ma, nb = tr ? ma : na;
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= mb) return;
+  for (int64_t c = blockIdx.y; c < nb; c += gridDim.y) {
+    int64_t sr = tr ? c : r, sc = tr ? r : c;
+    if (mir) { sr = ma - 1 - sr; sc = na - 1 - sc; }
+    const T v = A[sr + sc * lda];
+    B[r + c * ldb] = tr ? conj_(v) : v;
+  }
+}
+template <typename T>
+void mirror_copy(Context& ctx, int mode, int64_t ma, int64_t na, const T* A, int64_t lda, T* B,
+                 int64_t ldb) {
+  if (ma <= 0 || na <= 0) return;
+  const int64_t mb = (mode & 1) ? na : ma, nb = (mode & 1) ? ma : na;
+  dim3 g((unsigned)ceil_div(mb, 256), (unsigned)(nb < 2048 ? nb : 2048));
+  mirror_copy_kernel<T><<<g, 256, 0, ctx.stream>>>(mode, ma, na, A, lda, B, ldb);
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+template <typename T>
+__global__ void reverse_copy_kernel(int64_t n, const T* __restrict__ x, T* __restrict__ y) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] = x[n - 1 - i];
+}
+template <typename T>
+void reverse_copy(Context& ctx, int64_t n, const T* x, T* y) {
+  if (n <= 0) return;
+  reverse_copy_kernel<T><<<(unsigned)ceil_div(n, 256), 256, 0, ctx.stream>>>(n, x, y);
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace
+
+// which: 'L' = gelqf, 'R' = gerqf, 'Q' = geqlf
+template <typename T>
+void geqrf_variant(Context& ctx, char which, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau) {
+  const int64_t k = m < n ? m : n;
+  if (k <= 0) return;
+  const int mode = which == 'L' ? 1 : (which == 'Q' ? 2 : 3);
+  const int64_t mw = (mode & 1) ? n : m, nw = (mode & 1) ? m : n;
+  Arena::Mark mk = ctx.arena.mark();
+  const int64_t ldw = round_up(mw, 16);
+  T* W = ctx.alloc<T>(ldw * nw);
+  T* tw = ctx.alloc<T>(k);
+  mirror_copy<T>(ctx, mode, m, n, A, lda, W, ldw);
+  geqrf<T>(ctx, mw, nw, W, ldw, mode == 1 ? d_tau : tw);
+  if (mode != 1) reverse_copy<T>(ctx, k, tw, d_tau);
+  mirror_copy<T>(ctx, mode, mw, nw, W, ldw, A, lda);        // the mapping is its own inverse
+  ctx.arena.release(mk);
+}
+
+// which: 'L' = orglq (m x n, orthonormal rows), 'R' = orgrq, 'Q' = orgql (m x n, orthonormal columns)
+template <typename T>
+void orgqr_variant(Context& ctx, char which, int64_t m, int64_t n, int64_t k, T* A, int64_t lda,
+                   const T* d_tau) {
+  if (m <= 0 || n <= 0) return;
+  const int mode = which == 'L' ? 1 : (which == 'Q' ? 2 : 3);
+  const int64_t mw = (mode & 1) ? n : m, nw = (mode & 1) ? m : n;
+  Arena::Mark mk = ctx.arena.mark();
+  const int64_t ldw = round_up(mw, 16);
+  T* W = ctx.alloc<T>(ldw * nw);
+  T* tw = ctx.alloc<T>(k > 0 ? k : 1);
+  mirror_copy<T>(ctx, mode, m, n, A, lda, W, ldw);
+  const T* tq = d_tau;
+  if (mode != 1 && k > 0) { reverse_copy<T>(ctx, k, d_tau, tw); tq = tw; }
+  // after mirroring, the k reflectors sit in the FIRST k columns of W, first reflector first
+  orgqr<T>(ctx, mw, nw, k, W, ldw, tq);
+  mirror_copy<T>(ctx, mode, mw, nw, W, ldw, A, lda);
+  ctx.arena.release(mk);
+}
+
+// =============================================================================================
+// QR with column pivoting, ?geqp3_ (src/linalg/qr.cr:38-41; rank(method: QRP),
+// src/linalg/linalg.cr:772-774).  Column by column as ?laqp2 does: the free column with the
+// largest partial norm (first maximum) is swapped into place, its ?larfg reflector is generated
+// and applied to the columns to the right, whose partial norms are then downdated with LAPACK's
+// formula and recomputed when the downdate has lost its accuracy (tol3z = sqrt(eps)).  Two
+// launches per column: this routine is about parity of pivots and factors, not speed.
+namespace {
+
+constexpr int QP_NT = 512;
+
+template <typename T>
+__global__ void __launch_bounds__(QP_NT)
+qp3_norms_kernel(int64_t m, int64_t n, const T* __restrict__ A, int64_t lda, double* vn1, double* vn2) {
+  __shared__ double red[QP_NT / 32];
+  for (int64_t c = blockIdx.x; c < n; c += gridDim.x) {
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < m; i += QP_NT) {
+      const T v = A[i + c * lda];
+      s += (double)real_(v) * (double)real_(v) + (double)imag_(v) * (double)imag_(v);
+    }
+    s = warp_sum<double>(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int w = 0; w < QP_NT / 32; w++) t += red[w];
+      vn1[c] = vn2[c] = sqrt(t);
+    }
+    __syncthreads();
+  }
+}
+
+// one CTA: choose the pivot of step j, swap it into column j, generate the reflector
+template <typename T>
+__global__ void __launch_bounds__(QP_NT)
+qp3_pivot_kernel(int64_t m, int64_t n, int64_t j, int64_t nfixed, T* __restrict__ A, int64_t lda,
+                 int* __restrict__ jpvt, T* __restrict__ tau, double* vn1, double* vn2) {
+  __shared__ double sv[QP_NT / 32];
+  __shared__ int si[QP_NT / 32];
+  __shared__ int s_pvt;
+  __shared__ T s_scale;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (j >= nfixed) {
+    double bv = -1.0;
+    int bi = 0x7fffffff;
+    for (int64_t c = j + tid; c < n; c += QP_NT) {
+      const double v = vn1[c];
+      if (v > bv) { bv = v; bi = (int)c; }            // ascending c: the first maximum stays
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) { sv[warp] = bv; si[warp] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+      for (int w = 1; w < QP_NT / 32; w++)
+        if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+      s_pvt = bi == 0x7fffffff ? (int)j : bi;
+    }
+    __syncthreads();
+  } else {
+    if (tid == 0) s_pvt = (int)j;
+    __syncthreads();
+  }
+  const int64_t pvt = s_pvt;
+  if (pvt != j) {
+    for (int64_t i = tid; i < m; i += QP_NT) {
+      const T t = A[i + pvt * lda];
+      A[i + pvt * lda] = A[i + j * lda];
+      A[i + j * lda] = t;
+    }
+    if (tid == 0) {
+      const int t = jpvt[pvt]; jpvt[pvt] = jpvt[j]; jpvt[j] = t;
+      vn1[pvt] = vn1[j];
+      vn2[pvt] = vn2[j];
+    }
+  }
+  __syncthreads();
+  // ?larfg on A(j:m, j)
+  T* col = A + j * lda;
+  double s = 0.0;
+  for (int64_t i = j + 1 + tid; i < m; i += QP_NT) {
+    const T v = col[i];
+    s += (double)real_(v) * (double)real_(v) + (double)imag_(v) * (double)imag_(v);
+  }
+  s = warp_sum<double>(s);
+  __syncthreads();
+  if (lane == 0) sv[warp] = s;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    for (int w = 0; w < QP_NT / 32; w++) t += sv[w];
+    T beta, tj, scale;
+    householder<T>(col[j], t, beta, tj, scale);
+    col[j] = beta;
+    tau[j] = tj;
+    s_scale = scale;
+  }
+  __syncthreads();
+  const T scale = s_scale;
+  for (int64_t i = j + 1 + tid; i < m; i += QP_NT) col[i] = mul(col[i], scale);
+}
+
+// one CTA per column c > j: apply H(j)^H, then downdate (or recompute) the partial norm
+template <typename T>
+__global__ void __launch_bounds__(256)
+qp3_apply_kernel(int64_t m, int64_t n, int64_t j, T* __restrict__ A, int64_t lda,
+                 const T* __restrict__ tau, double* vn1, double* vn2, double tol3z) {
+  __shared__ T red[8];
+  __shared__ double dred[8];
+  __shared__ T s_w;
+  __shared__ int s_recompute;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const T* v = A + j * lda;
+  const T tj = tau[j];
+  for (int64_t c = j + 1 + blockIdx.x; c < n; c += gridDim.x) {
+    T* col = A + c * lda;
+    T acc = zero<T>();
+    for (int64_t i = j + tid; i < m; i += 256) {
+      const T vi = i == j ? one<T>() : v[i];
+      acc = fma_(conj_(vi), col[i], acc);
+    }
+    acc = warp_sum<T>(acc);
+    if (lane == 0) red[warp] = acc;
+    __syncthreads();
+    if (tid == 0) {
+      T t = zero<T>();
+      for (int w = 0; w < 8; w++) t = add(t, red[w]);
+      s_w = mul(conj_(tj), t);                      // conj(tau) * v^H a_c
+    }
+    __syncthreads();
+    const T f = s_w;
+    for (int64_t i = j + tid; i < m; i += 256) {
+      const T vi = i == j ? one<T>() : v[i];
+      col[i] = fnma_(vi, f, col[i]);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int rec = 0;
+      if (vn1[c] != 0.0) {
+        const T ajc = col[j];
+        const double a = sqrt((double)real_(ajc) * (double)real_(ajc) + (double)imag_(ajc) * (double)imag_(ajc));
+        double temp = 1.0 - (a / vn1[c]) * (a / vn1[c]);
+        temp = temp > 0.0 ? temp : 0.0;
+        const double r = vn1[c] / vn2[c];
+        const double temp2 = temp * r * r;
+        if (temp2 <= tol3z) rec = 1;
+        else vn1[c] *= sqrt(temp);
+      }
+      s_recompute = rec;
+    }
+    __syncthreads();
+    if (s_recompute) {
+      double s = 0.0;
+      for (int64_t i = j + 1 + tid; i < m; i += 256) {
+        const T x = col[i];
+        s += (double)real_(x) * (double)real_(x) + (double)imag_(x) * (double)imag_(x);
+      }
+      s = warp_sum<double>(s);
+      if (lane == 0) dred[warp] = s;
+      __syncthreads();
+      if (tid == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; w++) t += dred[w];
+        vn1[c] = vn2[c] = j + 1 < m ? sqrt(t) : 0.0;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void swap_columns_kernel(int64_t m, T* a, T* b) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < m) { const T t = a[i]; a[i] = b[i]; b[i] = t; }
+}
+
+}  // namespace
+
+// d_jpvt: device array of n ints, on entry LAPACK's "fixed column" markers already resolved by
+// the caller into a permutation (jpvt[c] = 1-based original index of the column now at c) with
+// the `nfixed` fixed columns in front; on exit the final permutation.
+template <typename T>
+void geqp3(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_jpvt, T* d_tau,
+           int64_t nfixed) {
+  const int64_t k = m < n ? m : n;
+  if (k <= 0) return;
+  Arena::Mark mk = ctx.arena.mark();
+  double* vn1 = ctx.alloc<double>(n);
+  double* vn2 = ctx.alloc<double>(n);
+  const double eps = sizeof(typename Traits<T>::real) == 4 ? 5.9604644775390625e-08 : 1.1102230246251565e-16;
+  const double tol3z = sqrt(eps);
+  const int64_t gn = n < (int64_t)ctx.sm_count * 4 ? n : (int64_t)ctx.sm_count * 4;
+  qp3_norms_kernel<T><<<(unsigned)gn, QP_NT, 0, ctx.stream>>>(m, n, A, lda, vn1, vn2);
+  for (int64_t j = 0; j < k; j++) {
+    qp3_pivot_kernel<T><<<1, QP_NT, 0, ctx.stream>>>(m, n, j, nfixed, A, lda, d_jpvt, d_tau, vn1, vn2);
+    const int64_t nc = n - j - 1;
+    if (nc > 0) {
+      const int64_t g = nc < (int64_t)ctx.sm_count * 8 ? nc : (int64_t)ctx.sm_count * 8;
+      qp3_apply_kernel<T><<<(unsigned)g, 256, 0, ctx.stream>>>(m, n, j, A, lda, d_tau, vn1, vn2, tol3z);
+    }
+  }
+  LA_CUDA_CHECK(cudaGetLastError());
+  ctx.arena.release(mk);
+}
+
+template <typename T>
+void swap_columns(Context& ctx, int64_t m, T* a, T* b) {
+  if (m <= 0 || a == b) return;
+  swap_columns_kernel<T><<<(unsigned)ceil_div(m, 256), 256, 0, ctx.stream>>>(m, a, b);
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+
 #define LA_INST_QR(T)                                                                            \
   template void geqrf<T>(Context&, int64_t, int64_t, T*, int64_t, T*);                           \
   template void ormqr<T>(Context&, Side, Op, int64_t, int64_t, int64_t, const T*, int64_t,       \
                          const T*, T*, int64_t);                                                 \
   template void orgqr<T>(Context&, int64_t, int64_t, int64_t, T*, int64_t, const T*);            \
-  template void gels<T>(Context&, Op, int64_t, int64_t, int64_t, T*, int64_t, T*, int64_t, int*);
+  template void gels<T>(Context&, Op, int64_t, int64_t, int64_t, T*, int64_t, T*, int64_t, int*); \
+  template void geqrf_variant<T>(Context&, char, int64_t, int64_t, T*, int64_t, T*);             \
+  template void orgqr_variant<T>(Context&, char, int64_t, int64_t, int64_t, T*, int64_t,         \
+                                 const T*);                                                      \
+  template void geqp3<T>(Context&, int64_t, int64_t, T*, int64_t, int*, T*, int64_t);            \
+  template void swap_columns<T>(Context&, int64_t, T*, T*);
 LA_INST_QR(float)
 LA_INST_QR(double)
 LA_INST_QR(zcomplex)

@@ -117,8 +117,24 @@ class BlasLapackABI:
             "orgqr": [_IP, _IP, _IP, _P, _IP, _P, _P, _IP, _IP],
             "ungqr": [_IP, _IP, _IP, _P, _IP, _P, _P, _IP, _IP],
             "gels": [c_char_p, _IP, _IP, _IP, _P, _IP, _P, _IP, _P, _IP, _IP],
+            "geqp3": [_IP, _IP, _P, _IP, _P, _P, _P, _IP] + ([_P] if letter == "z" else []) + [_IP],
+            "lacpy": [c_char_p, _IP, _IP, _P, _IP, _P, _IP],
+            "laset": [c_char_p, _IP, _IP, _P, _P, _P, _IP],
         }
+        for fam in ("gerqf", "gelqf", "geqlf"):
+            sigs[fam] = sigs["geqrf"]
+        for fam in ("orgrq", "orglq", "orgql", "ungrq", "unglq", "ungql"):
+            sigs[fam] = sigs["orgqr"]
         return self._fn(f"{letter}{routine}_", sigs[routine])
+
+    def norm(self, routine: str, letter: str):
+        """?lange / ?lansy / zlanhe / ?lantr: functions returning the norm (float for the REAL
+        routines, FloatReturn = Float, libLAPACK_linux.cr:17)."""
+        sigs = {"lange": [c_char_p, _IP, _IP, _P, _IP, _P],
+                "lansy": [c_char_p, c_char_p, _IP, _P, _IP, _P],
+                "lanhe": [c_char_p, c_char_p, _IP, _P, _IP, _P],
+                "lantr": [c_char_p, c_char_p, c_char_p, _IP, _IP, _P, _IP, _P]}
+        return self._fn(f"{letter}{routine}_", sigs[routine], c_float if letter == "s" else c_double)
 
     def ilaver(self):
         f = self._fn("ilaver_", [_IP, _IP, _IP])
@@ -146,10 +162,11 @@ def declared_symbols():
     for l in "sdz":
         syms += [f"cblas_{l}gemm", f"cblas_{l}symm", f"cblas_{l}trmm", f"cblas_{l}trsm"]
         for r in ("getrf", "getrs", "gesv", "potrf", "potrs", "posv", "geqrf", "gels", "trtrs",
-                  "getri", "potri", "trtri"):
+                  "getri", "potri", "trtri", "gerqf", "gelqf", "geqlf", "geqp3", "lange", "lansy",
+                  "lantr", "lacpy", "laset"):
             syms.append(f"{l}{r}_")
         for r in ("trsm", "herk", "getrf", "getrs", "potrf", "potrs", "geqrf", "ormqr", "gels",
-                  "trtrs", "laswp", "gemm_stair"):
+                  "trtrs", "laswp", "gemm_stair", "lange", "lacpy", "laset"):
             syms.append(f"la_b200_{l}{r}_dev")
         syms.append(f"la_b200_{l}gemm_dev")
     syms += ["cblas_zhemm", "cblas_ssyrk", "cblas_dsyrk", "cblas_zherk", "sormqr_", "dormqr_",
@@ -157,5 +174,8 @@ def declared_symbols():
              "openblas_get_num_threads", "openblas_get_num_procs", "openblas_get_config",
              "openblas_get_corename", "openblas_get_parallel", "la_b200_version",
              "la_b200_workspace_bytes", "la_b200_last_gemm_path", "la_b200_release_workspace",
-             "la_b200_set_sm_limit", "la_b200_dgetrf_dev_noalloc"]
+             "la_b200_set_sm_limit", "la_b200_dgetrf_dev_noalloc", "zlanhe_", "sorgrq_", "dorgrq_",
+             "zungrq_", "sorglq_", "dorglq_", "zunglq_", "sorgql_", "dorgql_", "zungql_",
+             "la_b200_mat_create", "la_b200_mat_free", "la_b200_mat_ptr", "la_b200_mat_ld",
+             "la_b200_mat_rows", "la_b200_mat_cols", "la_b200_mat_upload", "la_b200_mat_download"]
     return syms

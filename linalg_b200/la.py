@@ -110,7 +110,21 @@ class LUTranspose(enum.Enum):
     ConjTranspose = 2
 
 
-_WORK_DETECT = {"gels", "geqrf", "getri", "orgqr", "ormqr"}  # lapack_helper.cr:143-183
+# lapack_helper.cr:143-183
+_WORK_DETECT = {"gels", "geqrf", "getri", "orgqr", "ormqr", "gerqf", "gelqf", "geqlf", "orgrq",
+                "orglq", "orgql", "geqp3"}
+
+
+class MatrixNorm(enum.Enum):      # src/linalg/linalg.cr:703-708
+    Frobenius = "F"
+    One = "O"
+    Inf = "I"
+    MaxAbs = "M"
+
+
+class RankMethod(enum.Enum):
+    SVD = 0
+    QRP = 1
 
 
 def _ci(v):
@@ -135,11 +149,16 @@ def _lapack(name, letter, *args):
             keep.append(ci)
             cargs.append(byref(ci))
     info = c_int(0)
+    extra = []
+    if name == "geqp3" and letter == "z":       # rwork, WORK_PARAM1 = 2n (lapack_helper.cr:151)
+        rwork = np.zeros(2 * max(1, int(args[1])), dtype=np.float64)
+        keep.append(rwork)
+        extra = [ffi.ptr(rwork)]
     if name in _WORK_DETECT:
         dt = {"s": np.float32, "d": np.float64, "z": np.complex128}[letter]
         q = np.zeros(1, dtype=dt)
         lw = c_int(-1)
-        fn(*cargs, ffi.ptr(q), byref(lw), byref(info))
+        fn(*cargs, ffi.ptr(q), byref(lw), *extra, byref(info))
         if info.value != 0:
             raise LinAlgError(f"LAPACK.{letter}{name} returned {info.value}")
         lwork = max(1, int(q[0].real))
@@ -147,7 +166,7 @@ def _lapack(name, letter, *args):
         guard = dt(0xDEADBEEF)
         work[lwork] = guard  # overrun guard, workpool.cr:37-49
         lw = c_int(lwork)
-        fn(*cargs, ffi.ptr(work), byref(lw), byref(info))
+        fn(*cargs, ffi.ptr(work), byref(lw), *extra, byref(info))
         if work[lwork] != guard:
             raise RuntimeError("worksize guard failed")
     else:
@@ -391,6 +410,8 @@ class GeneralMatrix:
             raise ValueError("matrix must be square")
         if p < 0:
             return (self ** (-p)).inv()
+        if p > 1 and hasattr(backend().cdll, "la_b200_mat_create"):
+            return self._pow_resident(int(p))
         result = GeneralMatrix.identity(self.nrows, self.dtype)
         result.clear_flags()
         base = self
@@ -403,6 +424,68 @@ class GeneralMatrix:
             if p:
                 base = base * base
         return result
+
+    def _pow_resident(self, p):
+        """power.cr:19-30 with the operands kept on the device (include/la_b200.h, handles): one
+        upload of the base, every product of the repeated squaring through la_b200_?gemm_dev on
+        resident matrices (same kernels, same order of products as the pointer path: the result
+        is bit-identical), one download of the result."""
+        from ctypes import c_double, c_float, c_int64, c_void_p
+        L, n = self.letter, self.nrows
+        cd = backend().cdll
+        cd.la_b200_mat_create.restype = c_void_p
+        cd.la_b200_mat_create.argtypes = [c_int, c_int64, c_int64]
+        cd.la_b200_mat_ptr.restype, cd.la_b200_mat_ptr.argtypes = c_void_p, [c_void_p]
+        cd.la_b200_mat_ld.restype, cd.la_b200_mat_ld.argtypes = c_int64, [c_void_p]
+        cd.la_b200_mat_free.restype, cd.la_b200_mat_free.argtypes = None, [c_void_p]
+        cd.la_b200_mat_upload.argtypes = [c_void_p, c_void_p, c_int64]
+        cd.la_b200_mat_download.argtypes = [c_void_p, c_void_p, c_int64]
+        gemm = getattr(cd, f"la_b200_{L}gemm_dev")
+        sc = c_void_p if L == "z" else (c_float if L == "s" else c_double)
+        gemm.argtypes = [c_int, c_int, c_int64, c_int64, c_int64, sc, c_void_p, c_int64, c_void_p,
+                         c_int64, sc, c_void_p, c_int64, c_void_p]
+        lacpy = getattr(cd, f"la_b200_{L}lacpy_dev")
+        lacpy.argtypes = [c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p]
+        laset = getattr(cd, f"la_b200_{L}laset_dev")
+        laset.argtypes = [c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        one, _k1 = ffi.scalar_arg(L, 1.0)
+        zbuf = np.zeros(1, dtype=self.dtype)
+        hs = [c_void_p(cd.la_b200_mat_create(ord(L), n, n)) for _ in range(4)]
+        try:
+            if any(h.value is None for h in hs):
+                raise MemoryError("la_b200_mat_create failed")
+            ld = cd.la_b200_mat_ld(hs[0])
+            ptr = cd.la_b200_mat_ptr
+
+            def mult(dst, a, b):           # Matrix#*: beta = 1 on a zeroed result (mult.cr:118-120)
+                laset(ord("A"), n, n, ffi.ptr(zbuf), ffi.ptr(zbuf), ptr(dst), ld, None)
+                rc = gemm(ffi.NO_TRANS, ffi.NO_TRANS, n, n, n, one, ptr(a), ld, ptr(b), ld, one,
+                          ptr(dst), ld, None)
+                if rc != 0:
+                    raise LinAlgError(f"la_b200_{L}gemm_dev returned {rc}")
+
+            base, result, t1, t2 = hs
+            cd.la_b200_mat_upload(base, ffi.ptr(self.raw), n)
+            have = False
+            while p > 0:
+                if p & 1:
+                    if not have:           # result = base.clone
+                        lacpy(ord("A"), n, n, ptr(base), ld, ptr(result), ld, None)
+                        have = True
+                    else:
+                        mult(t1, result, base)
+                        result, t1 = t1, result
+                p >>= 1
+                if p:
+                    mult(t2, base, base)
+                    base, t2 = t2, base
+            out = GeneralMatrix.zeros(n, n, self.dtype)
+            cd.la_b200_mat_download(result, ffi.ptr(out.raw), n)
+        finally:
+            for h in hs:
+                if h.value is not None:
+                    cd.la_b200_mat_free(h)
+        return out
 
     # -- LU (lu.cr) --------------------------------------------------------------------------
     def lu(self, *, overwrite_a=False):
@@ -530,18 +613,71 @@ class GeneralMatrix:
         return x
 
     # -- QR (qr.cr) --------------------------------------------------------------------------------------
-    def qr_raw(self, *, overwrite_a=False):
+    def qr_raw(self, *, overwrite_a=False, pivoting=False):   # qr.cr:34-54
         a = self if overwrite_a else self.clone()
         m, n = a.nrows, a.ncolumns
         tau = np.zeros(n, dtype=self.dtype)
+        if pivoting:
+            jpvt = np.zeros(n, dtype=np.int32)
+            _lapack("geqp3", self.letter, m, n, a.raw, m, jpvt, tau)
+            a.clear_flags()
+            return a, tau, jpvt
         _lapack("geqrf", self.letter, m, n, a.raw, m, tau)
         a.clear_flags()
         return a, tau
 
-    def qr_r(self, *, overwrite_a=False):
+    def qr_r(self, *, overwrite_a=False, pivoting=False):
+        if pivoting:
+            a, _, pvt = self.qr_raw(overwrite_a=overwrite_a, pivoting=True)
+            a.triu_()
+            return a, pvt
         a, _ = self.qr_raw(overwrite_a=overwrite_a)
         a.triu_()
         return a
+
+    # -- RQ, LQ, QL (rq_lq_ql.cr:3-39) ------------------------------------------------------------
+    def _decomposition(self, letters, overwrite_a):
+        a = self if overwrite_a else self.clone()
+        m, n = a.nrows, a.ncolumns
+        tau = np.zeros(n, dtype=self.dtype)
+        _lapack("ge" + letters + "f", self.letter, m, n, a.raw, m, tau)
+        a.clear_flags()
+        r = a.clone()
+        r.tril_() if "l" in letters else r.triu_()
+        k = min(m, n)
+        _lapack("org" + letters, self.letter, m, n, k, a.raw, m, tau)
+        a.assume_(MatrixFlags.Orthogonal)
+        return (a, r) if letters[0] == "q" else (r, a)
+
+    def rq(self, *, overwrite_a=False): return self._decomposition("rq", overwrite_a)
+
+    def lq(self, *, overwrite_a=False): return self._decomposition("lq", overwrite_a)
+
+    def ql(self, *, overwrite_a=False): return self._decomposition("ql", overwrite_a)
+
+    # -- norms and rank (linalg.cr:721-780) -----------------------------------------------------------
+    def norm(self, kind=MatrixNorm.Frobenius):
+        let, L = kind.value.encode(), self.letter
+        n = self.nrows
+        work = np.zeros(max(1, n), dtype=np.float32 if L == "s" else np.float64)
+        ab = backend()
+        if self.flags.triangular:
+            uplo = b"U" if self.flags.upper_triangular else b"L"
+            return float(ab.norm("lantr", L)(let, uplo, b"N", _ci(self.nrows), _ci(self.ncolumns),
+                                             ffi.ptr(self.raw), _ci(self.nrows), ffi.ptr(work)))
+        if L == "z" and self.flags.hermitian:
+            return float(ab.norm("lanhe", L)(let, b"U", _ci(n), ffi.ptr(self.raw), _ci(n), ffi.ptr(work)))
+        if self.flags.symmetric:
+            return float(ab.norm("lansy", L)(let, b"U", _ci(n), ffi.ptr(self.raw), _ci(n), ffi.ptr(work)))
+        return float(ab.norm("lange", L)(let, _ci(self.nrows), _ci(self.ncolumns), ffi.ptr(self.raw),
+                                         _ci(self.nrows), ffi.ptr(work)))
+
+    def rank(self, eps=None, *, method=RankMethod.QRP, overwrite_a=False):
+        eps = self.tolerance() if eps is None else eps
+        if method is not RankMethod.QRP:
+            raise NotImplementedError("svdvals (gesdd) is outside the hot path (SURVEY.md §2)")
+        a, _ = self.qr_r(overwrite_a=overwrite_a, pivoting=True)
+        return int(np.count_nonzero(np.abs(np.diagonal(a.raw)) > eps))
 
     def qr(self, *, overwrite_a=False):
         a, tau = self.qr_raw(overwrite_a=overwrite_a)
