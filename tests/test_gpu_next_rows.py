@@ -117,7 +117,7 @@ def test_pivoted_qr_keeps_fixed_columns_in_front_and_finds_the_rank(product_abi,
     a0, p0, t0 = run(oracle_abi)
     assert sorted(p1[:3]) == [5, 10, 31]
     assert np.array_equal(p1[:r], p0[:r])                          # beyond the rank: rounding noise
-    assert np.abs(np.triu(a1)[:r] - np.triu(a0)[:r]).max() < 1e-10
+    assert np.abs(np.triu(a1)[:r, :r] - np.triu(a0)[:r, :r]).max() < 1e-10
 
 
 @pytest.mark.parametrize("dt", DTYPES, ids=IDS)
