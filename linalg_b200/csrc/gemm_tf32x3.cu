@@ -119,6 +119,28 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                    smem_u32(bar))
                : "memory");
 }
+// the same arrive, delivered to the barrier at this offset in every CTA of `mask` (cluster)
+__device__ __forceinline__ void umma_commit_multicast(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
+// TMA tile load whose bytes (and complete_tx) go to the same shared-memory offsets of every CTA
+// in `mask`.  The tensor map covers THIS GPU's memory only (workspace of the calling context).
+__device__ __forceinline__ void tma_load_2d_multicast(void* smem_dst, const CUtensorMap* map,
+                                                      uint64_t* bar, int c0, int c1, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -140,10 +162,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+template <int SN>
 __device__ __forceinline__ bool s_tile_skipped(int tri, int tm, int tn) {
-  if (tri == TriLower) return tm * SM_ + SM_ - 1 < tn * SN_;
-  if (tri == TriUpper) return tm * SM_ > tn * SN_ + SN_ - 1;
+  if (tri == TriLower) return tm * SM_ + SM_ - 1 < tn * SN;
+  if (tri == TriUpper) return tm * SM_ > tn * SN + SN - 1;
   return false;
+}
+// stages of the TMA ring that fit the shared memory for a tile width
+__host__ __device__ constexpr int s_stages(int sn) { return sn >= 256 ? 2 : (sn >= 128 ? 3 : 4); }
+__host__ __device__ constexpr int s_smem_bytes(int sn) {
+  return s_stages(sn) * (2 * S_A_BYTES + 2 * sn * SK_ * 4) + 1024 + 256;
 }
 
 __device__ __forceinline__ void s_tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
@@ -157,21 +185,33 @@ __device__ __forceinline__ void s_tile_coords(int t, int tiles_m, int tiles_n, i
   tn = r / gsz;
 }
 
+// CL = true: clusters of two CTAs that own vertically adjacent tiles (same tile column).  Both
+// need the same B tile: each loads half of it and multicasts it to the pair, which cuts the
+// L2 -> shared-memory traffic per tile from 96 to 64 KB per stage (the four operand streams of
+// the split product are what bounds the single-CTA kernel at large N).  A stage is recycled when
+// BOTH tensor cores have consumed it (the release is multicast to the pair as well).
+// SN = tile width (256, 128 or 64 columns; narrower tiles for products with few tiles: more CTAs
+// busy, and their smaller stages allow a deeper TMA ring).
+template <bool CL, int SN>
 __global__ void __launch_bounds__(S_THREADS, 1)
 sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
                     const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo,
                     const SParams p) {
+  constexpr int SB = SN * SK_ * 4;                          // bytes of one B tile (hi or lo)
+  constexpr int STAGE = 2 * S_A_BYTES + 2 * SB;
+  constexpr int NST = s_stages(SN);
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = (uint64_t*)(smem + S_STAGES * S_STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + S_STAGES;
-  uint64_t* tfull_bar = empty_bar + S_STAGES;   // accumulator ready for the epilogue
+  uint64_t* full_bar = (uint64_t*)(smem + NST * STAGE);
+  uint64_t* empty_bar = full_bar + NST;
+  uint64_t* tfull_bar = empty_bar + NST;   // accumulator ready for the epilogue
   uint64_t* tempty_bar = tfull_bar + 2;         // accumulator drained by the epilogue
   uint32_t* tmem_ptr = (uint32_t*)(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int crank = CL ? (int)(blockIdx.x & 1) : 0;        // rank in the pair
   if (threadIdx.x == 0) {
-    for (int s = 0; s < S_STAGES; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < NST; s++) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], CL ? 2 : 1); }
     for (int a = 0; a < 2; a++) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 8); }
     mbar_fence_init();
   }
@@ -184,10 +224,15 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
+  if (CL) cluster_sync_all();          // the peer's barriers exist before anything targets them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  // work items: tiles, or (CL) pairs of vertically adjacent tiles, one pair per cluster
+  const int rows_w = CL ? (p.tiles_m + 1) / 2 : p.tiles_m;
+  const int num_tiles = rows_w * p.tiles_n;
+  const int w_first = CL ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int w_step = CL ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const int kblocks = (int)((p.k + SK_ - 1) / SK_);
 
   // warps 0-3 (producer, MMA issuer, TMEM allocator) hand registers to the two epilogue
@@ -200,21 +245,28 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
       tma_prefetch_desc(&tmBhi); tma_prefetch_desc(&tmBlo);
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = w_first; t < num_tiles; t += w_step) {
         int tm, tn;
-        s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-        if (s_tile_skipped(p.tri, tm, tn)) continue;
-        const int m0 = tm * SM_, n0 = tn * SN_;
+        s_tile_coords(t, rows_w, p.tiles_n, tm, tn);
+        if (CL) tm = 2 * tm + crank;
+        if (s_tile_skipped<SN>(p.tri, tm, tn)) continue;
+        const int m0 = tm * SM_, n0 = tn * SN;
         for (int kb = 0; kb < kblocks; kb++) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], S_STAGE_BYTES);
-          unsigned char* s = smem + stage * S_STAGE_BYTES;
+          mbar_expect_tx(&full_bar[stage], STAGE);
+          unsigned char* s = smem + stage * STAGE;
           const int k0 = kb * SK_;
           tma_load_2d(s, &tmAhi, &full_bar[stage], k0, m0);
           tma_load_2d(s + S_A_BYTES, &tmAlo, &full_bar[stage], k0, m0);
-          tma_load_2d(s + 2 * S_A_BYTES, &tmBhi, &full_bar[stage], k0, n0);
-          tma_load_2d(s + 2 * S_A_BYTES + S_B_BYTES, &tmBlo, &full_bar[stage], k0, n0);
-          if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+          if (CL) {   // my half of the B tile, delivered to both CTAs of the pair
+            const int half = crank * (SB / 2), nh = n0 + crank * (SN / 2);
+            tma_load_2d_multicast(s + 2 * S_A_BYTES + half, &tmBhi, &full_bar[stage], k0, nh, 3);
+            tma_load_2d_multicast(s + 2 * S_A_BYTES + SB + half, &tmBlo, &full_bar[stage], k0, nh, 3);
+          } else {
+            tma_load_2d(s + 2 * S_A_BYTES, &tmBhi, &full_bar[stage], k0, n0);
+            tma_load_2d(s + 2 * S_A_BYTES + SB, &tmBlo, &full_bar[stage], k0, n0);
+          }
+          if (++stage == NST) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -222,35 +274,39 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
     // ===================== MMA issuer (one thread) =====================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_tf32(SM_, SN_);
+      constexpr uint32_t idesc = make_idesc_tf32(SM_, SN);
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = w_first; t < num_tiles; t += w_step) {
         int tm, tn;
-        s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-        if (s_tile_skipped(p.tri, tm, tn)) continue;
+        s_tile_coords(t, rows_w, p.tiles_n, tm, tn);
+        if (CL) tm = 2 * tm + crank;
+        if (s_tile_skipped<SN>(p.tri, tm, tn)) continue;
         for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
           const int kb1 = min(kblocks, kb0 + S_KCHUNK_BLOCKS);
           mbar_wait(&tempty_bar[as], aphase ^ 1);
           tc_fence_after();
-          const uint32_t tacc = tmem_base + (uint32_t)(as * SN_);
+          const uint32_t tacc = tmem_base + (uint32_t)(as * SN);
           for (int kb = kb0; kb < kb1; kb++) {
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
-            const uint32_t s = smem_u32(smem + stage * S_STAGE_BYTES);
+            const uint32_t s = smem_u32(smem + stage * STAGE);
 #pragma unroll
             for (int ks = 0; ks < SK_ / 8; ks++) {
               const uint32_t ko = ks * 32;  // 8 floats
               const uint64_t ahi = make_kmajor_sw128_desc(s + ko);
               const uint64_t alo = make_kmajor_sw128_desc(s + S_A_BYTES + ko);
               const uint64_t bhi = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + ko);
-              const uint64_t blo = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + S_B_BYTES + ko);
+              const uint64_t blo = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + SB + ko);
               umma_tf32(tacc, ahi, blo, idesc, (kb > kb0 || ks) ? 1u : 0u);
               umma_tf32(tacc, alo, bhi, idesc, 1u);
               umma_tf32(tacc, ahi, bhi, idesc, 1u);
             }
-            umma_commit(&empty_bar[stage]);   // frees the smem stage when these MMAs retire
-            if (++stage == S_STAGES) { stage = 0; phase ^= 1; }
+            // frees the smem stage when these MMAs retire (in both CTAs of a pair: the peer's
+            // producer writes half of MY next B tile)
+            if (CL) umma_commit_multicast(&empty_bar[stage], 3);
+            else umma_commit(&empty_bar[stage]);
+            if (++stage == NST) { stage = 0; phase ^= 1; }
           }
           umma_commit(&tfull_bar[as]);        // chunk accumulator complete
           if (++as == 2) { as = 0; aphase ^= 1; }
@@ -267,23 +323,24 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
     int as = 0;
     uint32_t aphase = 0;
     const bool beta_zero = p.beta == 0.f;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = w_first; t < num_tiles; t += w_step) {
       int tm, tn;
-      s_tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-      if (s_tile_skipped(p.tri, tm, tn)) continue;
+      s_tile_coords(t, rows_w, p.tiles_n, tm, tn);
+      if (CL) tm = 2 * tm + crank;
+      if (s_tile_skipped<SN>(p.tri, tm, tn)) continue;
       const int64_t row = (int64_t)tm * SM_ + q * 32 + lane;
       // The tensor core truncates when it accumulates, so k is cut into chunks of 512 terms; the
       // chunk sums are added in FP32 (round to nearest) in REGISTERS — this thread owns one row
       // and four of the eight 32-column groups of the tile — and C is touched once per tile.
       // (Summing the chunks into C through memory cost 64 GB of extra traffic at N = 16384.)
-      float run[SN_ / 64][32];
+      float run[SN / 64][32];
       for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
         const bool first = kb0 == 0;
         mbar_wait(&tfull_bar[as], aphase);
         tc_fence_after();
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * SN_);
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * SN);
 #pragma unroll
-        for (int ci = 0; ci < SN_ / 64; ci++) {
+        for (int ci = 0; ci < SN / 64; ci++) {
           uint32_t v[32];
           tmem_ld32(tbase + (half + 2 * ci) * 32, v);
 #pragma unroll
@@ -297,8 +354,8 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
       }
       if (row < p.m) {
 #pragma unroll
-        for (int ci = 0; ci < SN_ / 64; ci++) {
-          const int64_t col0 = (int64_t)tn * SN_ + (half + 2 * ci) * 32;
+        for (int ci = 0; ci < SN / 64; ci++) {
+          const int64_t col0 = (int64_t)tn * SN + (half + 2 * ci) * 32;
           float* dst0 = p.C + row + col0 * p.ldc;
           float cold[32];
           if (!beta_zero) {  // all loads first: 32 independent requests in flight
@@ -322,6 +379,7 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
+  if (CL) cluster_sync_all();          // no CTA leaves while its peer may still signal it
   if (warp == 2) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
                  "n"(S_TMEM_COLS)
@@ -343,8 +401,14 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   if (m > (int64_t)1 << 30 || n > (int64_t)1 << 30 || k > (int64_t)1 << 30) return false;
   static DeviceOnce attr;
   if (attr.pending(ctx.device)) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, S_SMEM_BYTES));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 256>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<true, 256>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 128>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(128)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 64>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(64)));
     attr.mark(ctx.device);
   }
   Arena::Mark mk = ctx.arena.mark();
@@ -364,11 +428,33 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
     split_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>(tb == OpN, n, k, 1.0f, B, ldb, Bhi, Blo, ldk);
     LA_CUDA_CHECK(cudaGetLastError());
   }
+  // pairs of CTAs sharing B tiles: full products with at least two tile rows and enough tiles to
+  // fill the machine with pairs
+  static const bool no_cluster = getenv("LA_B200_SGEMM_NO_CLUSTER") != nullptr;
+  const bool cluster = !no_cluster && tri == TriFull && ceil_div(m, SM_) >= 2 &&
+                       ceil_div(m, SM_) * ceil_div(n, 256) >= 2 * (int64_t)ctx.sm_count;
+  // tile width: 256 unless a narrower tile keeps more SMs busy (score = fraction of the SMs'
+  // time spent on tiles x relative efficiency of the shape, as for the FP64 kernel)
+  int sn = 256;
+  if (!cluster) {
+    const int sms_ = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+    const int cand[3] = {256, 128, 64};
+    const double eff[3] = {1.0, 0.9, 0.7};
+    double best = -1.0;
+    for (int c = 0; c < 3; c++) {
+      const int64_t tl = ceil_div(m, SM_) * ceil_div(n, (int64_t)cand[c]);
+      const int64_t waves = ceil_div(tl, (int64_t)sms_);
+      const double used = (double)n / (double)(ceil_div(n, (int64_t)cand[c]) * cand[c]);
+      const double score = (double)tl / (double)(waves * sms_) * used * eff[c];
+      if (score > best * 1.05) { best = score; sn = cand[c]; }
+    }
+  }
+  const uint32_t bbox = cluster ? 128 : (uint32_t)sn;
   CUtensorMap tAh, tAl, tBh, tBl;
   bool ok = make_tensor_map_2d(&tAh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Ahi, k, m, ldk * 4, SK_, SM_, CU_TENSOR_MAP_SWIZZLE_128B) &&
             make_tensor_map_2d(&tAl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Alo, k, m, ldk * 4, SK_, SM_, CU_TENSOR_MAP_SWIZZLE_128B) &&
-            make_tensor_map_2d(&tBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Bhi, k, n, ldk * 4, SK_, SN_, CU_TENSOR_MAP_SWIZZLE_128B) &&
-            make_tensor_map_2d(&tBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Blo, k, n, ldk * 4, SK_, SN_, CU_TENSOR_MAP_SWIZZLE_128B);
+            make_tensor_map_2d(&tBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Bhi, k, n, ldk * 4, SK_, bbox, CU_TENSOR_MAP_SWIZZLE_128B) &&
+            make_tensor_map_2d(&tBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Blo, k, n, ldk * 4, SK_, bbox, CU_TENSOR_MAP_SWIZZLE_128B);
   if (!ok) {
     ctx.arena.release(mk);
     return false;
@@ -378,11 +464,34 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   p.alpha = alpha; p.beta = beta;
   p.C = C; p.ldc = ldc; p.tri = tri;
   p.tiles_m = (int)ceil_div(m, SM_);
-  p.tiles_n = (int)ceil_div(n, SN_);
+  p.tiles_n = (int)ceil_div(n, (int64_t)sn);
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
-  const int grid = tiles < sms ? tiles : sms;
-  sgemm_tf32x3_kernel<<<grid, S_THREADS, S_SMEM_BYTES, ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+  if (cluster) {
+    const int pairs = (int)(ceil_div(p.tiles_m, 2) * p.tiles_n);
+    int grid = 2 * (pairs < sms / 2 ? pairs : sms / 2);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(S_THREADS);
+    cfg.dynamicSmemBytes = s_smem_bytes(256);
+    cfg.stream = ctx.stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    LA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sgemm_tf32x3_kernel<true, 256>, tAh, tAl, tBh, tBl, p));
+  } else {
+    const int grid = tiles < sms ? tiles : sms;
+    if (sn == 256)
+      sgemm_tf32x3_kernel<false, 256><<<grid, S_THREADS, s_smem_bytes(256), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+    else if (sn == 128)
+      sgemm_tf32x3_kernel<false, 128><<<grid, S_THREADS, s_smem_bytes(128), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+    else
+      sgemm_tf32x3_kernel<false, 64><<<grid, S_THREADS, s_smem_bytes(64), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+  }
   LA_CUDA_CHECK(cudaGetLastError());
   ctx.arena.release(mk);
   return true;
