@@ -35,7 +35,6 @@ constexpr int S_TMEM_COLS = 512;                       // two 256-column accumul
 // bias of ~1e-8 per accumulated term.  k is therefore processed in chunks of S_KCHUNK: each chunk
 // is accumulated in TMEM from zero and added to C in FP32 (round to nearest) by the epilogue,
 // which the double-buffered accumulator overlaps with the next chunk's MMAs.
-constexpr int S_KCHUNK_BLOCKS = 16;                    // 16 x 32 = 512 terms per chunk
 
 struct SParams {
   int64_t m, n, k;
@@ -44,6 +43,7 @@ struct SParams {
   int64_t ldc;
   int tri;
   int tiles_m, tiles_n;
+  int kchunk_terms;   // terms accumulated in tensor memory before the FP32 add in registers
 };
 
 __device__ __forceinline__ uint32_t to_tf32(float x) {
@@ -89,15 +89,17 @@ __global__ void split_kernel(int kcontig, int64_t rows, int64_t k, float scale,
 }
 
 // ---- tcgen05 helpers -------------------------------------------------------------------------
-__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
-  // start address (>>4), LBO = 1 (unused for swizzled K-major), SBO = 1024 B between 8-row
-  // groups, version = 1 (sm_100), layout = SWIZZLE_128B (2)
+template <int SWZ_BYTES>
+__device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t smem_addr) {
+  // start address (>>4), LBO = 1 (unused for swizzled K-major), SBO = 8 rows of SWZ_BYTES
+  // between 8-row groups, version = 1 (sm_100), layout = SWIZZLE_128B (2) or SWIZZLE_64B (4)
+  static_assert(SWZ_BYTES == 128 || SWZ_BYTES == 64, "swizzle span");
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
   d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)((8 * SWZ_BYTES) >> 4) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)(SWZ_BYTES == 128 ? 2 : 4) << 61;
   return d;
 }
 constexpr uint32_t make_idesc_tf32(int M, int N) {
@@ -169,9 +171,12 @@ __device__ __forceinline__ bool s_tile_skipped(int tri, int tm, int tn) {
   return false;
 }
 // stages of the TMA ring that fit the shared memory for a tile width
-__host__ __device__ constexpr int s_stages(int sn) { return sn >= 256 ? 2 : (sn >= 128 ? 3 : 4); }
-__host__ __device__ constexpr int s_smem_bytes(int sn) {
-  return s_stages(sn) * (2 * S_A_BYTES + 2 * sn * SK_ * 4) + 1024 + 256;
+__host__ __device__ constexpr int s_stage_bytes(int sn, int skt) { return 2 * (SM_ + sn) * skt * 4; }
+__host__ __device__ constexpr int s_stages(int sn, int skt) {
+  return (200 * 1024) / s_stage_bytes(sn, skt) > 6 ? 6 : (200 * 1024) / s_stage_bytes(sn, skt);
+}
+__host__ __device__ constexpr int s_smem_bytes(int sn, int skt) {
+  return s_stages(sn, skt) * s_stage_bytes(sn, skt) + 1024 + 256;
 }
 
 __device__ __forceinline__ void s_tile_coords(int t, int tiles_m, int tiles_n, int& tm, int& tn) {
@@ -192,14 +197,19 @@ __device__ __forceinline__ void s_tile_coords(int t, int tiles_m, int tiles_n, i
 // BOTH tensor cores have consumed it (the release is multicast to the pair as well).
 // SN = tile width (256, 128 or 64 columns; narrower tiles for products with few tiles: more CTAs
 // busy, and their smaller stages allow a deeper TMA ring).
-template <bool CL, int SN>
+// SKT = k extent of a stage in floats: 32 (128-byte rows, 128B swizzle) or 16 (64-byte rows, 64B
+// swizzle).  The ring holds as many stages as fit the shared memory: what the tensor core can be
+// fed is (bytes in flight) / (TMA latency), and with two 96 KB stages only one is ever in flight.
+template <bool CL, int SN, int SKT>
 __global__ void __launch_bounds__(S_THREADS, 1)
 sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_constant__ CUtensorMap tmAlo,
                     const __grid_constant__ CUtensorMap tmBhi, const __grid_constant__ CUtensorMap tmBlo,
                     const SParams p) {
-  constexpr int SB = SN * SK_ * 4;                          // bytes of one B tile (hi or lo)
-  constexpr int STAGE = 2 * S_A_BYTES + 2 * SB;
-  constexpr int NST = s_stages(SN);
+  constexpr int SA = SM_ * SKT * 4;                         // bytes of one A tile (hi or lo)
+  constexpr int SB = SN * SKT * 4;                          // bytes of one B tile (hi or lo)
+  constexpr int STAGE = 2 * SA + 2 * SB;
+  constexpr int NST = s_stages(SN, SKT);
+  constexpr int SWZ = SKT * 4;                              // swizzle span = row length in bytes
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = (uint64_t*)(smem + NST * STAGE);
@@ -233,7 +243,8 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
   const int num_tiles = rows_w * p.tiles_n;
   const int w_first = CL ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int w_step = CL ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  const int kblocks = (int)((p.k + SK_ - 1) / SK_);
+  const int kblocks = (int)((p.k + SKT - 1) / SKT);
+  const int kchunk = p.kchunk_terms / SKT;                 // k-blocks per accumulation chunk
 
   // warps 0-3 (producer, MMA issuer, TMEM allocator) hand registers to the two epilogue
   // warpgroups, which keep a 128-float running sum per thread
@@ -255,16 +266,16 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE);
           unsigned char* s = smem + stage * STAGE;
-          const int k0 = kb * SK_;
+          const int k0 = kb * SKT;
           tma_load_2d(s, &tmAhi, &full_bar[stage], k0, m0);
-          tma_load_2d(s + S_A_BYTES, &tmAlo, &full_bar[stage], k0, m0);
+          tma_load_2d(s + SA, &tmAlo, &full_bar[stage], k0, m0);
           if (CL) {   // my half of the B tile, delivered to both CTAs of the pair
             const int half = crank * (SB / 2), nh = n0 + crank * (SN / 2);
-            tma_load_2d_multicast(s + 2 * S_A_BYTES + half, &tmBhi, &full_bar[stage], k0, nh, 3);
-            tma_load_2d_multicast(s + 2 * S_A_BYTES + SB + half, &tmBlo, &full_bar[stage], k0, nh, 3);
+            tma_load_2d_multicast(s + 2 * SA + half, &tmBhi, &full_bar[stage], k0, nh, 3);
+            tma_load_2d_multicast(s + 2 * SA + SB + half, &tmBlo, &full_bar[stage], k0, nh, 3);
           } else {
-            tma_load_2d(s + 2 * S_A_BYTES, &tmBhi, &full_bar[stage], k0, n0);
-            tma_load_2d(s + 2 * S_A_BYTES + SB, &tmBlo, &full_bar[stage], k0, n0);
+            tma_load_2d(s + 2 * SA, &tmBhi, &full_bar[stage], k0, n0);
+            tma_load_2d(s + 2 * SA + SB, &tmBlo, &full_bar[stage], k0, n0);
           }
           if (++stage == NST) { stage = 0; phase ^= 1; }
         }
@@ -282,8 +293,8 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
         s_tile_coords(t, rows_w, p.tiles_n, tm, tn);
         if (CL) tm = 2 * tm + crank;
         if (s_tile_skipped<SN>(p.tri, tm, tn)) continue;
-        for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
-          const int kb1 = min(kblocks, kb0 + S_KCHUNK_BLOCKS);
+        for (int kb0 = 0; kb0 < kblocks; kb0 += kchunk) {
+          const int kb1 = min(kblocks, kb0 + kchunk);
           mbar_wait(&tempty_bar[as], aphase ^ 1);
           tc_fence_after();
           const uint32_t tacc = tmem_base + (uint32_t)(as * SN);
@@ -292,12 +303,12 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
             tc_fence_after();
             const uint32_t s = smem_u32(smem + stage * STAGE);
 #pragma unroll
-            for (int ks = 0; ks < SK_ / 8; ks++) {
+            for (int ks = 0; ks < SKT / 8; ks++) {
               const uint32_t ko = ks * 32;  // 8 floats
-              const uint64_t ahi = make_kmajor_sw128_desc(s + ko);
-              const uint64_t alo = make_kmajor_sw128_desc(s + S_A_BYTES + ko);
-              const uint64_t bhi = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + ko);
-              const uint64_t blo = make_kmajor_sw128_desc(s + 2 * S_A_BYTES + SB + ko);
+              const uint64_t ahi = make_kmajor_desc<SWZ>(s + ko);
+              const uint64_t alo = make_kmajor_desc<SWZ>(s + SA + ko);
+              const uint64_t bhi = make_kmajor_desc<SWZ>(s + 2 * SA + ko);
+              const uint64_t blo = make_kmajor_desc<SWZ>(s + 2 * SA + SB + ko);
               umma_tf32(tacc, ahi, blo, idesc, (kb > kb0 || ks) ? 1u : 0u);
               umma_tf32(tacc, alo, bhi, idesc, 1u);
               umma_tf32(tacc, ahi, bhi, idesc, 1u);
@@ -334,7 +345,7 @@ sgemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmAhi, const __grid_cons
       // and four of the eight 32-column groups of the tile — and C is touched once per tile.
       // (Summing the chunks into C through memory cost 64 GB of extra traffic at N = 16384.)
       float run[SN / 64][32];
-      for (int kb0 = 0; kb0 < kblocks; kb0 += S_KCHUNK_BLOCKS) {
+      for (int kb0 = 0; kb0 < kblocks; kb0 += kchunk) {
         const bool first = kb0 == 0;
         mbar_wait(&tfull_bar[as], aphase);
         tc_fence_after();
@@ -401,14 +412,18 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   if (m > (int64_t)1 << 30 || n > (int64_t)1 << 30 || k > (int64_t)1 << 30) return false;
   static DeviceOnce attr;
   if (attr.pending(ctx.device)) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 256>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256)));
-    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<true, 256>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256)));
-    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 128>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(128)));
-    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 64>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(64)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 256, 16>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256, 16)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<true, 256, 16>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256, 16)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 256, 32>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256, 32)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<true, 256, 32>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(256, 32)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 128, 32>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(128, 32)));
+    LA_CUDA_CHECK(cudaFuncSetAttribute(sgemm_tf32x3_kernel<false, 64, 32>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, s_smem_bytes(64, 32)));
     attr.mark(ctx.device);
   }
   Arena::Mark mk = ctx.arena.mark();
@@ -430,8 +445,10 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   }
   // pairs of CTAs sharing B tiles: full products with at least two tile rows and enough tiles to
   // fill the machine with pairs
-  static const bool no_cluster = getenv("LA_B200_SGEMM_NO_CLUSTER") != nullptr;
-  const bool cluster = !no_cluster && tri == TriFull && ceil_div(m, SM_) >= 2 &&
+  // (measured with the four-stage ring: 240 TFLOP/s paired against 260 unpaired at N = 16384 —
+  // the pair's lock-step costs more than the L2 traffic it saves; kept behind LA_B200_SGEMM_CLUSTER)
+  static const bool use_cluster = getenv("LA_B200_SGEMM_CLUSTER") != nullptr;
+  const bool cluster = use_cluster && tri == TriFull && ceil_div(m, SM_) >= 2 &&
                        ceil_div(m, SM_) * ceil_div(n, 256) >= 2 * (int64_t)ctx.sm_count;
   // tile width: 256 unless a narrower tile keeps more SMs busy (score = fraction of the SMs'
   // time spent on tiles x relative efficiency of the shape, as for the FP64 kernel)
@@ -450,11 +467,15 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
     }
   }
   const uint32_t bbox = cluster ? 128 : (uint32_t)sn;
+  // 256-wide tiles: 16-float stages (48 KB, four in the ring); LA_B200_SGEMM_SK=32 keeps two 96 KB ones
+  static const int sk_env = getenv("LA_B200_SGEMM_SK") ? atoi(getenv("LA_B200_SGEMM_SK")) : 16;
+  const int skt = sn == 256 ? (sk_env == 32 ? 32 : 16) : 32;
+  const CUtensorMapSwizzle swz = skt == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   CUtensorMap tAh, tAl, tBh, tBl;
-  bool ok = make_tensor_map_2d(&tAh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Ahi, k, m, ldk * 4, SK_, SM_, CU_TENSOR_MAP_SWIZZLE_128B) &&
-            make_tensor_map_2d(&tAl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Alo, k, m, ldk * 4, SK_, SM_, CU_TENSOR_MAP_SWIZZLE_128B) &&
-            make_tensor_map_2d(&tBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Bhi, k, n, ldk * 4, SK_, bbox, CU_TENSOR_MAP_SWIZZLE_128B) &&
-            make_tensor_map_2d(&tBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Blo, k, n, ldk * 4, SK_, bbox, CU_TENSOR_MAP_SWIZZLE_128B);
+  bool ok = make_tensor_map_2d(&tAh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Ahi, k, m, ldk * 4, skt, SM_, swz) &&
+            make_tensor_map_2d(&tAl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Alo, k, m, ldk * 4, skt, SM_, swz) &&
+            make_tensor_map_2d(&tBh, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Bhi, k, n, ldk * 4, skt, bbox, swz) &&
+            make_tensor_map_2d(&tBl, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, Blo, k, n, ldk * 4, skt, bbox, swz);
   if (!ok) {
     ctx.arena.release(mk);
     return false;
@@ -465,6 +486,11 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   p.C = C; p.ldc = ldc; p.tri = tri;
   p.tiles_m = (int)ceil_div(m, SM_);
   p.tiles_n = (int)ceil_div(n, (int64_t)sn);
+  // terms per tensor-memory accumulation chunk (the tensor core truncates when it accumulates,
+  // a bias that grows with the chunk): measured at N = 16384, error against FP64 / TFLOP/s:
+  // 512 -> 3.6e-6 / 262, 256 -> 1.8e-6 / 252, 128 -> 9.3e-7 / 245, 64 -> 5.4e-7 / 232
+  static const int kc_env = getenv("LA_B200_SGEMM_KCHUNK") ? atoi(getenv("LA_B200_SGEMM_KCHUNK")) : 256;
+  p.kchunk_terms = kc_env >= 32 ? kc_env / 32 * 32 : 256;
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
   if (cluster) {
@@ -473,7 +499,7 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(S_THREADS);
-    cfg.dynamicSmemBytes = s_smem_bytes(256);
+    cfg.dynamicSmemBytes = s_smem_bytes(256, skt);
     cfg.stream = ctx.stream;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
@@ -482,15 +508,20 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    LA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sgemm_tf32x3_kernel<true, 256>, tAh, tAl, tBh, tBl, p));
+    if (skt == 16)
+      LA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sgemm_tf32x3_kernel<true, 256, 16>, tAh, tAl, tBh, tBl, p));
+    else
+      LA_CUDA_CHECK(cudaLaunchKernelEx(&cfg, sgemm_tf32x3_kernel<true, 256, 32>, tAh, tAl, tBh, tBl, p));
   } else {
     const int grid = tiles < sms ? tiles : sms;
-    if (sn == 256)
-      sgemm_tf32x3_kernel<false, 256><<<grid, S_THREADS, s_smem_bytes(256), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+    if (sn == 256 && skt == 16)
+      sgemm_tf32x3_kernel<false, 256, 16><<<grid, S_THREADS, s_smem_bytes(256, 16), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+    else if (sn == 256)
+      sgemm_tf32x3_kernel<false, 256, 32><<<grid, S_THREADS, s_smem_bytes(256, 32), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
     else if (sn == 128)
-      sgemm_tf32x3_kernel<false, 128><<<grid, S_THREADS, s_smem_bytes(128), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+      sgemm_tf32x3_kernel<false, 128, 32><<<grid, S_THREADS, s_smem_bytes(128, 32), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
     else
-      sgemm_tf32x3_kernel<false, 64><<<grid, S_THREADS, s_smem_bytes(64), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
+      sgemm_tf32x3_kernel<false, 64, 32><<<grid, S_THREADS, s_smem_bytes(64, 32), ctx.stream>>>(tAh, tAl, tBh, tBl, p);
   }
   LA_CUDA_CHECK(cudaGetLastError());
   ctx.arena.release(mk);
