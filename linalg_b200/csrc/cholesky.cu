@@ -276,7 +276,9 @@ int64_t potrf_block_width(int64_t n) {
   static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
   static const int nbo_env = getenv("LA_B200_CHOL_NBO") ? atoi(getenv("LA_B200_CHOL_NBO")) : 0;
   if (n < 4096 || la_disabled) return n;
-  return nbo_env > 0 ? nbo_env : (n >= 8192 ? 1024 : 512);
+  // (measured, tools/chol_sweep.sh: 512 beats 1024 by 17 % at N = 8192 and 4 % at 16384; from
+  // N = 32768 on the two are equal and the wider block halves the number of steps)
+  return nbo_env > 0 ? nbo_env : (n >= 32768 ? 1024 : 512);
 }
 
 template <typename T>
@@ -295,7 +297,7 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
     return;
   }
   static const int side_sms_env = getenv("LA_B200_CHOL_SIDE_SMS") ? atoi(getenv("LA_B200_CHOL_SIDE_SMS")) : 0;
-  const int side_sms = side_sms_env > 0 ? side_sms_env : 8;
+  const int side_sms = side_sms_env > 0 ? side_sms_env : (n >= 16384 ? 4 : 8);
   Context* side = side_context(ctx);
   {
     // first-use allocations of the side context happen before anything is enqueued
