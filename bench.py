@@ -373,7 +373,10 @@ def dist_legs(world, rank):
     for kind, r in (("potrf", d), ("getrf", e)):
         out.update({f"dist_{kind}_n": DIST_N, f"dist_{kind}_nb": DIST_NB, f"dist_{kind}_grid": r["grid"],
                     f"dist_{kind}_ms": r["ms"], f"dist_{kind}_tflops": r["tflops"],
-                    f"dist_{kind}_residual": r["residual"], f"dist_{kind}_info": r["info"]})
+                    f"dist_{kind}_residual": r["residual"], f"dist_{kind}_info": r["info"],
+                    f"dist_{kind}_solve_ms": r["solve_ms"]})
+        out["dist_potrf_solve_max_rel_err" if kind == "potrf" else "dist_getrf_solve_residual"] = \
+            r["solve_max_rel_err" if kind == "potrf" else "solve_residual"]
         if rank == 0:
             out[f"dist_{kind}_1gpu_ms"] = single[kind]["ms"]
             out[f"dist_{kind}_1gpu_residual"] = single[kind]["residual"]

@@ -192,6 +192,18 @@ class DevOps:
         self.dev.trsm(self.dev.LEFT, self.dev.LOWER, self.dev.NO_TRANS, self.dev.UNIT, m, n, 1.0,
                       tri, self._ld(tri), b, self._ld(b))
 
+    def trsm_left(self, tri, b, *, lower, unit=False, conj_trans=False):
+        """b <- op(tri)^-1 b with tri the named triangle of an m x m block, b: m x n."""
+        m, n = b.shape[1], b.shape[0]
+        d = self.dev
+        d.trsm(d.LEFT, d.LOWER if lower else d.UPPER, d.CONJ_TRANS if conj_trans else d.NO_TRANS,
+               d.UNIT if unit else d.NON_UNIT, m, n, 1.0, tri, self._ld(tri), b, self._ld(b))
+
+    def gemm_cn_sub(self, c, a, b):                # c <- c - a^H * b ; a: k x m, b: k x n, c: m x n
+        m, n, k = c.shape[1], c.shape[0], a.shape[1]
+        self.dev.gemm(self.dev.CONJ_TRANS, self.dev.NO_TRANS, m, n, k, -1.0, a, self._ld(a), b,
+                      self._ld(b), 1.0, c, self._ld(c))
+
     def gemm_nt_sub(self, c, a, b):                # c <- c - a * b^H ; a: m x k, b: n x k, c: m x n
         m, n, k = c.shape[1], c.shape[0], a.shape[0]
         with self._limited():
@@ -405,6 +417,116 @@ def getrf_block_cyclic(a_local: torch.Tensor, ipiv: torch.Tensor, n: int, nb: in
         apply(k, panel, piv, k + 2, nblk)
         apply(k, panel, piv, 0, k, left=True)
     return _reduce_info(ops.info_value(), dv)
+
+
+def _gather_blocks(parts, n, nb, nrhs, like):
+    """x (nrhs, n) on every rank from the blocks {k: (nrhs, nb)} held by their owners."""
+    x = torch.zeros((nrhs, n), dtype=like.dtype, device=like.device)
+    for k, v in parts.items():
+        x[:, k * nb: (k + 1) * nb] = v
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(x)
+    return x
+
+
+def potrs_block_cyclic(l_local: torch.Tensor, b: torch.Tensor, n: int, nb: int, ops,
+                       grid: Grid | None = None):
+    """Solve A X = B with the 2-D block-cyclic Cholesky factor left by `potrf_block_cyclic`
+    (cho_solve, src/linalg/cholesky.cr:81-90 -> ?potrs).  `b` is the (nrhs, n) right-hand side,
+    the same on every rank; returns X (nrhs, n) on every rank.
+
+    Two block substitutions.  L Y = B: the contributions L_ik y_k are accumulated where L_ik lives;
+    block k is solved by the owner of L_kk after a reduction along its grid row, and y_k goes down
+    its grid column.  L^H X = Y: contributions L_jk^H x_j accumulate per column block, are reduced
+    down the grid column, and x_k goes along the grid row.  Four small collectives per block: the
+    solve is bound by their latency, not by bandwidth or flops.
+    """
+    grid = grid or Grid()
+    lay = BlockCyclic(n, nb, grid)
+    P, Q, p, q = grid.P, grid.Q, grid.p, grid.q
+    nblk, mloc, nloc = lay.nblk, lay.mloc, lay.nloc
+    nrhs = b.shape[0]
+    acc = torch.zeros((nrhs, max(mloc, 1)), dtype=b.dtype, device=b.device)    # minus sum L_ik y_k
+    y = {}
+    for k in range(nblk):
+        pk, qk = k % P, k % Q
+        owner = grid.rank_of(pk, qk)
+        t = None
+        if p == pk:
+            lr = (k - p) // P * nb
+            t = acc[:, lr: lr + nb].clone()
+            if Q > 1:
+                dist.reduce(t, dst=owner, group=grid.row_group)
+        if q == qk:
+            lc = (k - q) // Q * nb
+            yk = torch.empty((nrhs, nb), dtype=b.dtype, device=b.device)
+            if p == pk:
+                yk.copy_(b[:, k * nb: (k + 1) * nb] + t)
+                ops.trsm_left(l_local[lc: lc + nb, lr: lr + nb], yk, lower=True)
+                y[k] = yk
+            if P > 1:
+                dist.broadcast(yk, src=owner, group=grid.col_group)
+            r0 = lay.lrow_from(k + 1)
+            if mloc - r0 > 0:
+                ops.gemm_nn_sub(acc[:, r0:], l_local[lc: lc + nb, r0:], yk)
+    acc2 = torch.zeros((nrhs, max(nloc, 1)), dtype=b.dtype, device=b.device)   # minus sum L_jk^H x_j
+    x = {}
+    for k in range(nblk - 1, -1, -1):
+        pk, qk = k % P, k % Q
+        owner = grid.rank_of(pk, qk)
+        t = None
+        if q == qk:
+            lc = (k - q) // Q * nb
+            t = acc2[:, lc: lc + nb].clone()
+            if P > 1:
+                dist.reduce(t, dst=owner, group=grid.col_group)
+        if p == pk:
+            lr = (k - p) // P * nb
+            xk = torch.empty((nrhs, nb), dtype=b.dtype, device=b.device)
+            if q == qk:
+                xk.copy_(y[k] + t)
+                ops.trsm_left(l_local[lc: lc + nb, lr: lr + nb], xk, lower=True, conj_trans=True)
+                x[k] = xk
+            if Q > 1:
+                dist.broadcast(xk, src=owner, group=grid.row_group)
+            c1 = lay.lcol_from(k)                # my column blocks left of k
+            if c1 > 0:
+                ops.gemm_cn_sub(acc2[:, :c1], l_local[:c1, lr: lr + nb], xk)
+    return _gather_blocks(x, n, nb, nrhs, b)
+
+
+def getrs_block_cyclic(lu_local: torch.Tensor, ipiv: torch.Tensor, b: torch.Tensor, n: int, nb: int,
+                       ops, grid: Grid | None = None):
+    """Solve A X = B with the block-column LU left by `getrf_block_cyclic` (LUMatrix#solve,
+    src/linalg/lu.cr:151-162 -> ?getrs 'N').  `b`: (nrhs, n), the same on every rank (it is
+    overwritten by the row interchanges); returns X (nrhs, n) on every rank."""
+    grid = grid or Grid(1, dist.get_world_size() if dist.is_initialized() else 1)
+    if grid.P != 1:
+        raise ValueError("getrs_block_cyclic works on block columns: use a 1 x Q grid")
+    lay = BlockCyclic(n, nb, grid)
+    Q, q, nblk = grid.Q, grid.q, lay.nblk
+    nrhs = b.shape[0]
+    ops.laswp(b, ipiv, 0, n)
+    y, x = {}, {}
+    for upper in (False, True):
+        acc = torch.zeros((nrhs, n), dtype=b.dtype, device=b.device)       # minus the contributions
+        order = range(nblk - 1, -1, -1) if upper else range(nblk)
+        for k in order:
+            k0 = k * nb
+            t = acc[:, k0: k0 + nb].clone()
+            if Q > 1:
+                dist.reduce(t, dst=k % Q, group=grid.row_group)
+            if q == k % Q:
+                lc = (k - q) // Q * nb
+                blk = lu_local[lc: lc + nb]                                    # my block column k
+                v = ((y[k] if upper else b[:, k0: k0 + nb]) + t).contiguous()
+                ops.trsm_left(blk[:, k0: k0 + nb], v, lower=not upper, unit=not upper)
+                (x if upper else y)[k] = v
+                if upper and k0 > 0:
+                    ops.gemm_nn_sub(acc[:, :k0], blk[:, :k0], v)
+                if not upper and n - k0 - nb > 0:
+                    ops.gemm_nn_sub(acc[:, k0 + nb:], blk[:, k0 + nb:], v)
+    return _gather_blocks(x, n, nb, nrhs, b)
 
 
 def lstsq_tsqr(a_local: torch.Tensor, b_local: torch.Tensor, ops, group=None):

@@ -133,6 +133,16 @@ def getrf_residual(a_local, ipiv, lay, n, collective=True):
     return float(((pax - lux).norm() / (a2.sqrt() * x.norm())).item())
 
 
+def _matvec(gen, lay, n, x, collective=True):
+    """A x for the matrix defined by `gen` from this rank's blocks (all-reduced)."""
+    rows_g, cols_g = lay.global_rows().cuda(), lay.global_cols().cuda()
+    out = torch.zeros(n, dtype=torch.float64, device="cuda")
+    for c0 in range(0, len(cols_g), CHUNK_COLS):
+        c1 = min(c0 + CHUNK_COLS, len(cols_g))
+        out.index_add_(0, rows_g, gen(rows_g, cols_g[c0:c1]).T @ x[cols_g[c0:c1]])
+    return _allreduce(out, collective)
+
+
 def run_potrf(n, nb, grid, reserve_sms=0, reps=1, warm_n=None):
     """Timed distributed Cholesky on the synthetic SPD matrix; returns a dict of results."""
     ops = ladist.DevOps(reserve_sms=reserve_sms)
@@ -151,10 +161,16 @@ def run_potrf(n, nb, grid, reserve_sms=0, reps=1, warm_n=None):
         ms, info = _timed(lambda: ladist.potrf_block_cyclic(a_local, n, nb, ops, grid))
         best = min(best, ms)
     res = potrf_residual(a_local, lay, n)
+    # cho_solve with the distributed factor: S x = S x0, one right-hand side
+    x0 = _probe(n, 9)
+    rhs = _matvec(lambda r, c: spd_block(r, c, n), lay, n, x0).view(1, n)
+    solve_ms, xs = _timed(lambda: ladist.potrs_block_cyclic(a_local, rhs, n, nb, ops, grid))
+    solve_err = float(((xs[0] - x0).abs().max() / x0.abs().max()).item())
     del a_local
     torch.cuda.empty_cache()
     return {"n": n, "nb": nb, "grid": f"{grid.P}x{grid.Q}", "ms": best, "info": info,
-            "tflops": n ** 3 / 3.0 / best * 1e-9, "residual": res, "reserve_sms": reserve_sms}
+            "tflops": n ** 3 / 3.0 / best * 1e-9, "residual": res, "reserve_sms": reserve_sms,
+            "solve_ms": solve_ms, "solve_max_rel_err": solve_err}
 
 
 def run_getrf(n, nb, grid, reserve_sms=0, reps=1, warm_n=None):
@@ -177,10 +193,20 @@ def run_getrf(n, nb, grid, reserve_sms=0, reps=1, warm_n=None):
         ms, info = _timed(lambda: ladist.getrf_block_cyclic(a_local, ipiv, n, nb, ops, grid))
         best = min(best, ms)
     res = getrf_residual(a_local, ipiv, lay, n)
+    # LA.solve with the distributed factors: A x = A x0, one right-hand side; the error is judged
+    # through the residual (a random dense matrix of this size is not well conditioned)
+    x0 = _probe(n, 10)
+    rhs = _matvec(dense_block, lay, n, x0).view(1, n)
+    b0 = rhs.clone()
+    solve_ms, xs = _timed(lambda: ladist.getrs_block_cyclic(a_local, ipiv, rhs, n, nb, ops, grid))
+    # a_local holds the factors now: the residual uses the generator again
+    r = _matvec(dense_block, lay, n, xs[0]) - b0[0]
+    solve_res = float((r.norm() / (float(n) * 0.5774 * xs[0].norm())).item())   # ||A||_F ~ n / sqrt(3)
     del a_local
     torch.cuda.empty_cache()
     return {"n": n, "nb": nb, "grid": f"1x{grid.Q}", "ms": best, "info": info,
-            "tflops": 2.0 * n ** 3 / 3.0 / best * 1e-9, "residual": res, "reserve_sms": reserve_sms}
+            "tflops": 2.0 * n ** 3 / 3.0 / best * 1e-9, "residual": res, "reserve_sms": reserve_sms,
+            "solve_ms": solve_ms, "solve_residual": solve_res}
 
 
 class _OneRank:

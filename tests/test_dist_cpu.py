@@ -37,6 +37,17 @@ class CpuOps:
         C, A, B = c.numpy().T, a.numpy().T, b.numpy().T
         c.copy_(torch.from_numpy(np.ascontiguousarray((C - A @ B.conj().T).T)))
 
+    def trsm_left(self, tri, b, *, lower, unit=False, conj_trans=False):
+        import scipy.linalg as sl
+        Tm = tri.numpy().T
+        X = sl.solve_triangular(Tm, b.numpy().T, lower=lower, unit_diagonal=unit,
+                                trans="C" if conj_trans else "N")
+        b.copy_(torch.from_numpy(np.ascontiguousarray(X.T)))
+
+    def gemm_cn_sub(self, c, a, b):
+        C, A, B = c.numpy().T, a.numpy().T, b.numpy().T
+        c.copy_(torch.from_numpy(np.ascontiguousarray((C - A.conj().T @ B).T)))
+
     def gemm_nn_sub(self, c, a, b):
         C, A, B = c.numpy().T, a.numpy().T, b.numpy().T
         c.copy_(torch.from_numpy(np.ascontiguousarray((C - A @ B).T)))
@@ -112,7 +123,10 @@ def _chol_worker(rank, world, port, P, Q, n, nb, out):
         rows, cols = lay.global_rows().numpy(), lay.global_cols().numpy()
         a_local = torch.from_numpy(np.ascontiguousarray(S[np.ix_(rows, cols)].T))   # (nloc, mloc)
         info = ladist.potrf_block_cyclic(a_local, n, nb, CpuOps(), grid)
-        out[rank] = (info, rows, cols, a_local.numpy().T.copy())
+        rhs = np.random.default_rng(5).random((n, 3))
+        x = ladist.potrs_block_cyclic(a_local, torch.from_numpy(np.ascontiguousarray(rhs.T)), n, nb,
+                                      CpuOps(), grid)
+        out[rank] = (info, rows, cols, a_local.numpy().T.copy(), x.numpy().T.copy())
     finally:
         dist.destroy_process_group()
 
@@ -127,10 +141,13 @@ def test_block_cyclic_cholesky_on_process_grids(P, Q, n, nb):
     S = _spd(n)
     Lref = np.linalg.cholesky(S)
     L = np.zeros((n, n))
+    rhs = np.random.default_rng(5).random((n, 3))
+    xref = np.linalg.solve(S, rhs)
     for rank in range(world):
-        info, rows, cols, loc = out[rank]
+        info, rows, cols, loc, x = out[rank]
         assert info == 0
         L[np.ix_(rows, cols)] = loc
+        assert np.abs(x - xref).max() < 1e-11 * np.abs(xref).max()      # cho_solve on every rank
     assert np.allclose(np.tril(L), Lref, atol=1e-12)
 
 
@@ -170,6 +187,9 @@ def _lu_worker(rank, world, port, n, nb, out):
         a_local = torch.from_numpy(np.ascontiguousarray(A[:, cols].T))              # (nloc, n)
         ipiv = torch.zeros(n, dtype=torch.int32)
         info = ladist.getrf_block_cyclic(a_local, ipiv, n, nb, CpuOps(), grid)
+        rhs = np.random.default_rng(6).random((n, 2))
+        xs = ladist.getrs_block_cyclic(a_local, ipiv, torch.from_numpy(np.ascontiguousarray(rhs.T)),
+                                       n, nb, CpuOps(), grid)
         # tall-skinny least squares: rows split over the ranks
         m, nn = 240, 12
         rng = np.random.default_rng(7)
@@ -178,7 +198,8 @@ def _lu_worker(rank, world, port, n, nb, out):
         r0, r1 = ladist.shard_columns(m, world, rank)
         x = ladist.lstsq_tsqr(torch.from_numpy(np.ascontiguousarray(At[r0:r1].T)),
                               torch.from_numpy(np.ascontiguousarray(b[r0:r1].T)), CpuOps())
-        out[rank] = (info, cols, a_local.numpy().T.copy(), ipiv.numpy().copy(), x.numpy().T.copy())
+        out[rank] = (info, cols, a_local.numpy().T.copy(), ipiv.numpy().copy(), x.numpy().T.copy(),
+                     xs.numpy().T.copy())
     finally:
         dist.destroy_process_group()
 
@@ -193,8 +214,10 @@ def test_block_cyclic_lu_has_lapack_pivots_and_tsqr_matches(world, n, nb):
     A = np.random.default_rng(11).random((n, n))
     LUref, pivref = sl.lu_factor(A)                  # LAPACK dgetrf, 0-based pivots
     LU = np.zeros((n, n))
+    xsol = np.linalg.solve(A, np.random.default_rng(6).random((n, 2)))
     for rank in range(world):
-        info, cols, loc, ipiv, _ = out[rank]
+        info, cols, loc, ipiv, _, xs = out[rank]
+        assert np.abs(xs - xsol).max() < 1e-9 * np.abs(xsol).max()      # LUMatrix#solve
         assert info == 0
         assert np.array_equal(ipiv - 1, pivref)
         LU[:, cols] = loc

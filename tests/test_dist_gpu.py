@@ -24,6 +24,10 @@ def test_block_cyclic_cholesky_single_rank_matches_oracle(oracle_abi):
     L = np.tril(a.cpu().numpy().T)
     assert np.abs(L @ L.T - S).max() / np.abs(S).max() < 1e-12
     assert np.allclose(L, np.linalg.cholesky(S), atol=1e-11)
+    rhs = rng.random((n, 3))
+    x = ladist.potrs_block_cyclic(a, torch.from_numpy(np.ascontiguousarray(rhs.T)).cuda(), n, nb,
+                                  ladist.DevOps())
+    assert np.abs(x.cpu().numpy().T - np.linalg.solve(S, rhs)).max() < 1e-11
 
 
 def test_block_cyclic_cholesky_reports_first_bad_pivot():
@@ -45,6 +49,10 @@ def test_block_cyclic_lu_single_rank_has_lapack_pivots():
     LUref, pivref = sl.lu_factor(A)
     assert np.array_equal(ipiv.cpu().numpy() - 1, pivref)
     assert checks.lu_residual(A, a.cpu().numpy().T, ipiv.cpu().numpy()) < 1e-12
+    rhs = np.random.default_rng(6).random((n, 2))
+    x = ladist.getrs_block_cyclic(a, ipiv, torch.from_numpy(np.ascontiguousarray(rhs.T)).cuda(), n, nb,
+                                  ladist.DevOps())
+    assert checks.solve_residual(A, x.cpu().numpy().T, rhs) < 1e-12
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32, torch.complex128])
