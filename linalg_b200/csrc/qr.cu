@@ -223,7 +223,7 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
 // panel is 2 * (jb + 1) * jb / 2 * rows * sizeof(T) bytes, quadratic in its width: geqrf therefore
 // factors tall matrices in 8-column panels inside a recursive block structure.
 template <typename T, int JB, int U>
-__global__ void __launch_bounds__(QR_NT)
+__global__ void __launch_bounds__(QR_NT, ((JB <= 8 && !Traits<T>::is_complex) ? 2 : 1))
 qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
                        QrExchange<T>* xch, int64_t rpc) {
   __shared__ T s_f[QR_MAX_JB];
