@@ -62,13 +62,13 @@ DIST_COMM_CTAS = int(os.environ.get("LA_DIST_COMM_CTAS", "8"))
 # kernel time shares of one factorisation at N = 16384 from the ncu launch lists (serialised,
 # cold caches: shares, not absolutes); refreshed whenever the kernels change
 FACTOR_PROFILE = {
-    "dgetrf": {"source": "profiles/r1h_dgetrf16384_launches.csv",
-               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 125.0,
-                              "lu_panel_kernel (480 leaves)": 43.7, "laswp_*": 17.6,
-                              "trsm_dmma_kernel": 11.3}},
-    "dpotrf": {"source": "profiles/r1d_dpotrf16384_launches.csv",
-               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 65.0,
-                              "potf2_kernel (120 leaves)": 12.0, "trsm_dmma_kernel": 5.5}},
+    "dgetrf": {"source": "profiles/r2c_dgetrf16384_launches.csv",
+               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 32.6,
+                              "lu_panel_kernel (242 leaves)": 21.6, "laswp_*": 7.3,
+                              "trsm_dmma_kernel": 5.4}},
+    "dpotrf": {"source": "profiles/r2c_dpotrf16384_launches.csv",
+               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 52.7,
+                              "potf2_kernel (129 leaves)": 13.5, "trsm_dmma_kernel": 6.0}},
 }
 
 

@@ -8,13 +8,18 @@
 //   * a packing pass writes the four K-major ("k contiguous") operands Ahi, Alo (m x k) and
 //     Bhi, Blo (n x k) into workspace, absorbing op(A)/op(B); the main kernel is a pure
 //     K-major x K-major product;
-//   * persistent kernel, one CTA per SM, tile 128 x 256 x 32, 2-stage ring of TMA loads
-//     (128-byte swizzle) -> 12 tcgen05.mma (M=128, N=256, K=8) per stage issued by one thread
-//     -> accumulator in TMEM, double buffered (2 x 256 columns) so that the epilogue of tile t
-//     overlaps the MMAs of tile t+1;
+//   * persistent kernel, one CTA per SM, tile 128 x 256 (128 / 64 columns for products with few
+//     tiles), a ring of four 48 KB stages of 16 floats of k (64-byte rows, 64-byte swizzle) fed by
+//     TMA -> six tcgen05.mma (M=128, N=256, K=8) per stage issued by one thread -> accumulator in
+//     TMEM, double buffered (2 x 256 columns) so that the epilogue of one chunk overlaps the
+//     MMAs of the next;
+//   * the tensor core truncates when it accumulates: k is cut into chunks (256 terms) whose sums
+//     are added in FP32 in the epilogue warps' registers, C is touched once per tile;
 //   * warp roles: 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..11 = epilogue (two
 //     warps per TMEM lane quarter; tcgen05.ld 32 lanes x 32 columns, alpha/beta, coalesced
-//     column-major loads/stores issued 32 at a time).
+//     column-major loads/stores issued 32 at a time);
+//   * optional (LA_B200_SGEMM_CLUSTER): clusters of two CTAs sharing their B tile by TMA
+//     multicast.
 // Algorithmic work 2*m*n*k flops; the tensor pipe executes 3x that in TF32.
 #include "la_internal.h"
 #include "tma_utils.cuh"

@@ -3,7 +3,8 @@
 The reference has no distributed path; what shards naturally is stated in SURVEY.md §8(e):
 
   * GEMM: B and C split by block columns over the ranks, A replicated, no data-path collective
-    (`shard_columns`, used by bench.py).
+    (`shard_columns`, used by bench.py); with operands in host memory every rank uploads 1/N of A
+    and the slices are all-gathered over NVLink (`HostGemmPlan`).
   * Cholesky (`potrf_block_cyclic`): 2-D block-cyclic layout on a P x Q process grid (block
     (i, j) lives on grid position (i mod P, j mod Q)).  Per block column k: the owner of the
     diagonal block factors it and sends it down its grid column; the P ranks of that column solve
@@ -13,10 +14,11 @@ The reference has no distributed path; what shards naturally is stated in SURVEY
     trailing matrix, restricted to the blocks on or below the diagonal (staircase-masked product).
     Look-ahead: the ranks that hold block column k+1 update that column first, factor it and
     start its exchange on a second stream before they touch the rest of the trailing matrix.
+    `potrs_block_cyclic` solves with the distributed factor (cho_solve).
   * LU (`getrf_block_cyclic`): block columns dealt cyclically to the ranks (a 1 x Q grid), so a
     panel and its pivot search stay on one GPU; the factored panel and its pivots are broadcast,
     every rank applies the interchanges, the triangular solve and the rank-nb update to its own
-    columns, with the same look-ahead.
+    columns, with the same look-ahead.  `getrs_block_cyclic` solves with the distributed factors.
   * Tall-skinny least squares (`lstsq_tsqr`): rows split over the ranks, local QR of [A_i | b_i],
     all-gather of the small R factors, QR of the stack, triangular solve.
 
