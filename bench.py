@@ -63,12 +63,12 @@ DIST_COMM_CTAS = int(os.environ.get("LA_DIST_COMM_CTAS", "8"))
 # cold caches: shares, not absolutes); refreshed whenever the kernels change
 FACTOR_PROFILE = {
     "dgetrf": {"source": "profiles/r2c_dgetrf16384_launches.csv",
-               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 32.6,
-                              "lu_panel_kernel (242 leaves)": 21.6, "laswp_*": 7.3,
-                              "trsm_dmma_kernel": 5.4}},
+               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 125.5,
+                              "lu_panel_kernel (32-column leaves)": 44.6, "laswp_*": 17.1,
+                              "trsm_dmma_kernel": 10.9}},
     "dpotrf": {"source": "profiles/r2c_dpotrf16384_launches.csv",
-               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 52.7,
-                              "potf2_kernel (129 leaves)": 13.5, "trsm_dmma_kernel": 6.0}},
+               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 105.3,
+                              "potf2_kernel (128-column leaves)": 26.9, "trsm_dmma_kernel": 12.0}},
 }
 
 
