@@ -8,6 +8,7 @@
 #include "la_internal.h"
 #include <type_traits>
 #include <cooperative_groups.h>
+#include <vector>
 
 namespace la {
 
@@ -41,14 +42,26 @@ __global__ void laswp_kernel(int64_t n, T* __restrict__ A, int64_t lda, int64_t 
   }
 }
 
-struct LuPlan { int nb0; };  // leaf panel width for this matrix height
+// Row interchanges inside a panel are queued and flushed together: in the recursion an
+// interchange of a node's left columns is directly followed by interchanges of other columns
+// (its parent's), with no other work between them, and a launch in this dependent chain costs
+// more than the interchange itself.
+struct SwapJob { int64_t col0; int ncols, k1, k2; };
+struct LuPlan {
+  int nb0;                       // leaf panel width for this matrix height
+  std::vector<SwapJob> pending;  // queued interchanges of the panel being factored
+};
+template <typename T>
+void flush_swaps(Context& ctx, int64_t m, T* A, int64_t lda, const int* ipiv, LuPlan& plan);
 
 // Factor columns [j0, j0+jn) of the m-row matrix A below row j0 (all earlier updates
-// applied); pivots are global row indices.
+// applied); pivots are global row indices.  Interchanges may still be queued on return:
+// the caller flushes them (flush_swaps) before it touches the panel's columns.
 template <typename T>
 void getrf_rec(Context& ctx, int64_t m, T* A, int64_t lda, int* ipiv, int* d_info, int64_t j0,
-               int64_t jn, const LuPlan& plan) {
+               int64_t jn, LuPlan& plan) {
   if (jn <= plan.nb0) {
+    flush_swaps<T>(ctx, m, A, lda, ipiv, plan);
     lu_panel<T>(ctx, m - j0, (int)jn, A + j0 + j0 * lda, lda, ipiv + j0, j0, d_info);
     return;
   }
@@ -62,12 +75,13 @@ void getrf_rec(Context& ctx, int64_t m, T* A, int64_t lda, int* ipiv, int* d_inf
   T* A22 = A + (j0 + n1) + (j0 + n1) * lda;
   const T* A11 = A + j0 + j0 * lda;
   const T* A21 = A + (j0 + n1) + j0 * lda;
-  laswp_rows<T>(ctx, m, n2, A + (j0 + n1) * lda, lda, j0, j0 + n1, ipiv);
+  plan.pending.push_back(SwapJob{j0 + n1, (int)n2, (int)j0, (int)(j0 + n1)});
+  flush_swaps<T>(ctx, m, A, lda, ipiv, plan);
   trsm<T>(ctx, Left, Lower, OpN, Unit, n1, n2, one<T>(), A11, lda, A12, lda);
   gemm<T>(ctx, OpN, OpN, m - j0 - n1, n2, n1, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(),
           A22, lda);
   getrf_rec<T>(ctx, m, A, lda, ipiv, d_info, j0 + n1, n2, plan);
-  laswp_rows<T>(ctx, m, n1, A + j0 * lda, lda, j0 + n1, j0 + jn, ipiv);
+  plan.pending.push_back(SwapJob{j0, (int)n1, (int)(j0 + n1), (int)(j0 + jn)});
 }
 
 
@@ -166,6 +180,103 @@ void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k
   ctx.arena.release(mk);
 }
 
+namespace {
+
+constexpr int LASWP_MAX_JOBS = 6;
+struct SwapJobs {
+  int njobs;
+  long long col0[LASWP_MAX_JOBS];
+  int ncols[LASWP_MAX_JOBS], k1[LASWP_MAX_JOBS], k2[LASWP_MAX_JOBS];
+  int cta0[LASWP_MAX_JOBS + 1];            // first CTA of each job
+};
+
+// Up to LASWP_MAX_JOBS interchange jobs (columns, pivot range) in one launch.  Every CTA builds
+// the net permutation of its job in shared memory (as laswp_prep_kernel does) and applies it to
+// its share of the job's columns.  For the narrow column ranges inside a panel.
+template <typename T>
+__global__ void __launch_bounds__(256)
+laswp_jobs_kernel(int m, T* __restrict__ A, int64_t lda, const int* __restrict__ ipiv, SwapJobs jobs) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  int j = 0;
+  while (j + 1 < jobs.njobs && (int)blockIdx.x >= jobs.cta0[j + 1]) j++;
+  const int k1 = jobs.k1[j], npiv = jobs.k2[j] - k1, mapn = m - k1;
+  int* content = reinterpret_cast<int*>(smem_raw);
+  int* piv = content + mapn;
+  T* buf = reinterpret_cast<T*>(smem_raw + (((size_t)(mapn + npiv) * sizeof(int) + 15) & ~(size_t)15));
+  for (int i = threadIdx.x; i < mapn; i += blockDim.x) content[i] = k1 + i;
+  for (int e = threadIdx.x; e < npiv; e += blockDim.x) piv[e] = ipiv[k1 + e] - 1 - k1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int e = 0; e < npiv; e++) {
+      const int p = piv[e];
+      const int a = content[e], b = content[p];
+      content[e] = b;
+      content[p] = a;
+    }
+  }
+  __syncthreads();
+  const int nent = 2 * npiv;
+  const int nc = jobs.ncols[j], first = (int)blockIdx.x - jobs.cta0[j], step = jobs.cta0[j + 1] - jobs.cta0[j];
+  for (int c = first; c < nc; c += step) {
+    T* col = A + (jobs.col0[j] + c) * lda;
+    for (int e = threadIdx.x; e < nent; e += blockDim.x) {
+      const int src = e < npiv ? content[e] : content[piv[e - npiv]];
+      buf[e] = col[src];
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < nent; e += blockDim.x) {
+      const int dst = e < npiv ? k1 + e : k1 + piv[e - npiv];
+      const int src = e < npiv ? content[e] : content[piv[e - npiv]];
+      if (dst != src) col[dst] = buf[e];
+    }
+    __syncthreads();
+  }
+}
+
+constexpr size_t LASWP_JOBS_SMEM = 200 * 1024;
+
+template <typename T>
+void flush_swaps(Context& ctx, int64_t m, T* A, int64_t lda, const int* ipiv, LuPlan& plan) {
+  if (plan.pending.empty()) return;
+  static DeviceOnce attr;
+  if (attr.pending(ctx.device)) {
+    LA_CUDA_CHECK(cudaFuncSetAttribute(laswp_jobs_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)LASWP_JOBS_SMEM));
+    attr.mark(ctx.device);
+  }
+  SwapJobs jobs;
+  jobs.njobs = 0;
+  jobs.cta0[0] = 0;
+  size_t smem = 0;
+  auto launch = [&] {
+    if (jobs.njobs == 0) return;
+    laswp_jobs_kernel<T><<<(unsigned)jobs.cta0[jobs.njobs], 256, smem, ctx.stream>>>((int)m, A, lda, ipiv, jobs);
+    LA_CUDA_CHECK(cudaGetLastError());
+    jobs.njobs = 0;
+    smem = 0;
+  };
+  for (const SwapJob& jb : plan.pending) {
+    if (jb.ncols <= 0 || jb.k2 <= jb.k1) continue;
+    const size_t need = (((size_t)(m - jb.k1 + (jb.k2 - jb.k1)) * sizeof(int) + 15) & ~(size_t)15) +
+                        (size_t)2 * (jb.k2 - jb.k1) * sizeof(T);
+    if (need > LASWP_JOBS_SMEM || jb.ncols > 1024 || m > 0x7fffffff) {
+      launch();                        // keep the order: everything queued before goes first
+      laswp_rows<T>(ctx, m, jb.ncols, A + jb.col0 * lda, lda, jb.k1, jb.k2, ipiv);
+      continue;
+    }
+    if (jobs.njobs == LASWP_MAX_JOBS) launch();
+    const int q = jobs.njobs++;
+    jobs.col0[q] = jb.col0; jobs.ncols[q] = jb.ncols; jobs.k1[q] = jb.k1; jobs.k2[q] = jb.k2;
+    const int ctas = jb.ncols < 64 ? jb.ncols : 64;
+    jobs.cta0[q + 1] = jobs.cta0[q] + ctas;
+    if (need > smem) smem = need;
+  }
+  launch();
+  plan.pending.clear();
+}
+
+}  // namespace
+
 template <typename T>
 void laswp(Context& ctx, int64_t n, T* A, int64_t lda, int64_t k1, int64_t k2, const int* d_ipiv,
            bool reverse) {
@@ -247,7 +358,10 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     const int64_t jb = NB < k - j0 ? NB : k - j0;
     const bool tl_on = panel_done || j0 == 0;
     if (tl_on && lookahead) TL(ctx.stream);
-    if (!panel_done) getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
+    if (!panel_done) {
+      getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
+      flush_swaps<T>(ctx, m, A, lda, d_ipiv, plan);
+    }
     panel_done = false;
     if (j0 > 0) laswp_rows<T>(ctx, m, j0, A, lda, j0, j0 + jb, d_ipiv);
     const int64_t nr = n - j0 - jb;  // columns to the right
@@ -284,6 +398,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));
       side->sm_limit = side_sms;
       getrf_rec<T>(*side, m, A, lda, d_ipiv, d_info, j1, jb1, plan);
+      flush_swaps<T>(*side, m, A, lda, d_ipiv, plan);
       TL(side->stream);
       LA_CUDA_CHECK(cudaEventRecord(side->ev[0], side->stream));
       // The trailing update runs on the SMs the side stream leaves free — but only for as long
