@@ -225,8 +225,10 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
 template <typename T, int JB, int U>
 __global__ void __launch_bounds__(QR_NT, ((JB <= 8 && !Traits<T>::is_complex) ? 2 : 1))
 qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
-                       QrExchange<T>* xch, int64_t rpc) {
+                       QrExchange<T>* xch, int64_t rpc, T* __restrict__ Vc, int64_t ldv,
+                       T* __restrict__ Tout, int64_t ldt) {
   __shared__ T s_f[QR_MAX_JB];
+  __shared__ T s_tau[QR_MAX_JB];
   __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
   __shared__ T s_scale, s_beta;
   const int tid = threadIdx.x, lane = tid & 31;
@@ -345,10 +347,90 @@ qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __
       if (c == js) {
         s_scale = sc;
         s_beta = beta;
+        s_tau[js] = tj;
         if (blockIdx.x == 0) tau[js] = tj;
       }
     }
     __syncthreads();
+  }
+  // ---- optional epilogue (8-column panels): one more pass over the finished panel writes the
+  // clean copy of the reflectors (unit diagonal, zeros above) and accumulates G = V^H V; after a
+  // last grid barrier CTA 0 turns G and tau into the panel's T factor (?larft).  This replaces a
+  // copy kernel, a Gram product, its reduction and a ?larft launch per panel.
+  if constexpr (JB <= 8) {
+    if (Vc != nullptr) {
+      constexpr int NG = JB * (JB + 1) / 2;
+      T g[NG];
+#pragma unroll
+      for (int i = 0; i < NG; i++) g[i] = zero<T>();
+      for (int64_t r = tid; r < nr; r += QR_NT) {
+        const int64_t gr = rs + r;
+        T v[JB];
+#pragma unroll
+        for (int c = 0; c < JB; c++) {
+          const T a = c < jb ? base[(int64_t)c * lda + r] : zero<T>();
+          v[c] = (c < jb && gr > c) ? a : ((c < jb && gr == c) ? one<T>() : zero<T>());
+        }
+#pragma unroll
+        for (int c = 0; c < JB; c++)
+          if (c < jb) Vc[(int64_t)c * ldv + gr] = v[c];
+        int idx = 0;
+#pragma unroll
+        for (int j = 0; j < JB; j++)
+#pragma unroll
+          for (int i = 0; i <= j; i++) {
+            g[idx] = fma_(conj_(v[i]), v[j], g[idx]);
+            idx++;
+          }
+      }
+      // block reduction through s_red (8 warps x 32 slots; NG <= 36 needs two rounds)
+      // (partial sums go to the parity half the last column pass did not use: every CTA has left
+      // that half behind before any CTA can be here)
+      T* gp = &xch->part[kmax & 1][0][0];
+      for (int base_i = 0; base_i < NG; base_i += 32) {
+#pragma unroll
+        for (int i = 0; i < NG; i++) {
+          if (i >= base_i && i < base_i + 32) {
+            const T sgm = warp_sum<T>(g[i]);
+            if (lane == 0) s_red[warp][i - base_i] = sgm;
+          }
+        }
+        __syncthreads();
+        if (tid < 32 && base_i + tid < NG) {
+          T sgm = zero<T>();
+          for (int w = 0; w < QR_NT / 32; w++) sgm = add(sgm, s_red[w][tid]);
+          st_cg<T>(&gp[(int64_t)blockIdx.x * NG + base_i + tid], sgm);
+        }
+        __syncthreads();
+      }
+      target += (unsigned)G;
+      grid_barrier(&xch->barrier, target);
+      if (blockIdx.x == 0) {
+        __shared__ T s_g[NG];
+        if (tid < NG) {
+          T sgm = zero<T>();
+          for (int cta = 0; cta < G; cta++) sgm = add(sgm, ld_cg<T>(&gp[(int64_t)cta * NG + tid]));
+          s_g[tid] = sgm;
+        }
+        __syncthreads();
+        if (tid == 0) {
+          // G(i, j), i <= j, sits at j * (j + 1) / 2 + i
+          T Tl[JB][JB];
+          for (int i = 0; i < jb; i++) {
+            for (int r2 = 0; r2 < jb; r2++) Tl[r2][i] = zero<T>();
+            const T ti = s_tau[i];
+            for (int r2 = 0; r2 < i; r2++) {
+              T sgm = zero<T>();
+              for (int c = r2; c < i; c++) sgm = fma_(Tl[r2][c], s_g[i * (i + 1) / 2 + c], sgm);
+              Tl[r2][i] = mul(neg(ti), sgm);
+            }
+            Tl[i][i] = ti;
+          }
+          for (int i = 0; i < jb; i++)
+            for (int r2 = 0; r2 < jb; r2++) Tout[r2 + (int64_t)i * ldt] = Tl[r2][i];
+        }
+      }
+    }
   }
 }
 
@@ -391,7 +473,8 @@ struct QrWork {
 // launch the streaming kernel on as many co-resident CTAs as the occupancy allows (at least
 // 1024 rows each): the more loads in flight, the closer a pass gets to the HBM bandwidth
 template <typename T, int JB, int U>
-void launch_stream(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch) {
+void launch_stream(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch,
+                   T* Vc = nullptr, int64_t ldv = 0, T* Tout = nullptr, int64_t ldt = 0) {
   static int per_sm[DeviceOnce::kMax] = {};
   const int dev = ctx.device >= 0 && ctx.device < DeviceOnce::kMax ? ctx.device : 0;
   if (per_sm[dev] == 0) {
@@ -409,7 +492,8 @@ void launch_stream(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, 
   if (G < 1) G = 1;
   int64_t rpc = round_up(ceil_div(mp, G), 2);
   G = ceil_div(mp, rpc);
-  void* sargs[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc};
+  if (G * (JB * (JB + 1) / 2) > (int64_t)QR_MAX_CTAS * QR_MAX_JB) Vc = nullptr;   // (never with JB = 8)
+  void* sargs[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &Vc, &ldv, &Tout, &ldt};
   LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_stream_kernel<T, JB, U>,
                                             dim3((unsigned)G), dim3(QR_NT), sargs, 0, ctx.stream));
 }
@@ -422,8 +506,11 @@ bool qr_panel_is_tall(Context& ctx, int64_t mp) {
          QR_SMEM_BUDGET;
 }
 
+// Returns true when the panel kernel also produced the clean reflectors in Vc and the panel's T
+// factor in Tout (streamed 8-column panels); otherwise the caller builds them.
 template <typename T>
-void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch) {
+bool qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch,
+              T* Vc = nullptr, int64_t ldv = 0, T* Tout = nullptr, int64_t ldt = 0) {
   int64_t G = ceil_div(mp, 512);
   if (G > ctx.sm_count) G = ctx.sm_count;
   if (G < 1) G = 1;
@@ -441,7 +528,11 @@ void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
   }
   LA_CUDA_CHECK(cudaMemsetAsync(&xch->barrier, 0, sizeof(unsigned), ctx.stream));
   if (!use_smem) {
-    if (jb <= 8) launch_stream<T, 8, 4>(ctx, mp, jb, A, lda, tau, xch);
+    if (jb <= 8) {
+      const bool fuse = Vc != nullptr && Tout != nullptr && mp >= jb;
+      launch_stream<T, 8, 4>(ctx, mp, jb, A, lda, tau, xch, fuse ? Vc : nullptr, ldv, Tout, ldt);
+      return fuse;
+    }
     else if (jb <= 16) launch_stream<T, 16, 2>(ctx, mp, jb, A, lda, tau, xch);
     else {
       if constexpr (Traits<T>::is_complex) {
@@ -451,11 +542,12 @@ void qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
         launch_stream<T, 32, 1>(ctx, mp, jb, A, lda, tau, xch);
       }
     }
-    return;
+    return false;
   }
   void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem};
   LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_kernel<T>, dim3((unsigned)G),
                                             dim3(QR_NT), args, smem, ctx.stream));
+  return false;
 }
 
 template <typename T>
@@ -574,7 +666,7 @@ void qr_rec(Context& ctx, int64_t m, T* A, int64_t lda, T* tau, int64_t j0, int6
   const int64_t mp = m - j0;
   if (jn <= w.leaf) {
     T* P = A + j0 + j0 * lda;
-    qr_panel<T>(ctx, mp, (int)jn, P, lda, tau + j0, w.xch);
+    if (qr_panel<T>(ctx, mp, (int)jn, P, lda, tau + j0, w.xch, Vn, w.ldv, Tn, QR_NB)) return;
     const int64_t kk = mp < jn ? mp : jn;      // reflectors actually produced
     copy_triangle<T>(ctx, Lower, true, mp, jn, P, lda, Vn, w.ldv);
     gemm<T>(ctx, OpC, OpN, kk, kk, mp, one<T>(), Vn, w.ldv, Vn, w.ldv, zero<T>(), w.G, QR_MAX_JB);
