@@ -1,23 +1,35 @@
 // la_b200 — LU panel kernel: partial-pivoting LU of an m x jb (jb <= 32) panel in ONE
 // cooperative launch (the leaf of ?getrf, src/linalg/lu.cr:74-80 -> ?getrf_).
 //
-// The panel is distributed by contiguous row slices over G CTAs and lives in their shared
-// memory for the whole launch.  Partial pivoting needs one global decision per column; the
-// serial chain of N such decisions bounds ?getrf, so the exchange is built for latency:
-//   * every CTA publishes its best candidate (|value|, row index) together with the candidate
-//     row's current contents; the owner of row j publishes row j;
-//   * publication uses 16-byte (payload, tag) packets written with single vector stores and
-//     polled by the readers ("LL" protocol): a packet is valid when its tag equals the step's
-//     sequence number, so there is no barrier, no fence and no atomic on the critical path —
-//     one L2 write->read per column;
-//   * all CTAs derive the same winner (max |a|, ties -> smallest row index = i?amax's "first
-//     maximal element"), the two owners swap rows in place, everyone scales and updates its
-//     rows and folds the arg-max of the next column into the same pass.
+// The panel is distributed by contiguous row slices over G CTAs; every thread keeps its row(s)
+// in registers for the whole launch.  Partial pivoting needs one global decision per column, and
+// the serial chain of N such decisions bounds ?getrf, so everything is arranged around the
+// length of that chain:
+//   * rows never move.  A row carries its current LAPACK position; an interchange swaps two
+//     positions, the pivot row freezes (it then holds U(j, j:)) and every row is written to its
+//     final position once, at the end;
+//   * the registers of a row rotate by one column per step (the rank-1 update writes column c
+//     into the register of column c-1), so the current column is always register 0 and the code
+//     of a step does not depend on the column: no dispatch, nothing that is executed only once;
+//     finished L entries go to shared memory;
+//   * the update of column j is split: its head (the entries of column j+1, all the next
+//     arg-max needs) runs as soon as the pivot row is known, its tail runs while warp 0 waits
+//     for the other CTAs;
+//   * the CTA first agrees on its candidate, then only that row is staged (a single lane
+//     writing a row costs as much as a full warp doing so); a row staged while its tail is
+//     pending is completed by warp 0, one entry per lane;
+//   * every CTA publishes its candidate (|value|, position) together with the row's contents in
+//     16-byte (payload, tag) packets written with single vector stores and polled by the readers
+//     ("LL" protocol): a packet is valid when its tag equals the step's sequence number, so there
+//     is no barrier, no fence and no atomic on the critical path — one L2 write->read per column;
+//     1 / pivot is computed by the candidate's CTA after the row has left and travels behind it;
+//   * all CTAs derive the same winner (max |a|, ties -> smallest position = i?amax's "first
+//     maximal element").
 // Buffers are double-buffered by column parity; tags grow monotonically from launch to launch
 // within one factorisation; every factorisation clears the area and restarts the sequence
 // (lu_panel_begin), so a call enqueues the same work whatever ran before it and the 32-bit
 // sequence cannot wrap.
-// Bytes per column step (algorithmic): (jb-j) * rows * sizeof(T) read+written in SHARED memory;
+// Bytes per column step (algorithmic): (jb-j) * rows * sizeof(T) read+written in registers;
 // HBM traffic is one read and one write of the panel per launch: 2*m*jb*sizeof(T).
 #include "la_internal.h"
 #include <new>
@@ -29,7 +41,6 @@ namespace {
 constexpr int LU_NT = 512;
 constexpr int LU_MAX_JB = 32;
 constexpr int LU_MAX_CTAS = 160;
-constexpr size_t LU_SMEM_BUDGET = 136 * 1024;   // row slice; the landing areas come on top
 constexpr size_t LU_SMEM_TOTAL = 224 * 1024;
 
 struct __align__(16) LLPacket {
@@ -44,9 +55,9 @@ template <typename T> struct MaxJb { static constexpr int N = LU_MAX_JB; };
 template <> struct MaxJb<zcomplex> { static constexpr int N = 16; };
 
 struct LuExchange {
-  LLPacket hdr[2][LU_MAX_CTAS];                       // data = |a| (double bits); tag = seq<<32 | row
-  LLPacket row[2][LU_MAX_CTAS][LU_MAX_JB * 2];        // candidate row contents
-  LLPacket rowj[2][LU_MAX_JB * 2];                    // contents of row j
+  LLPacket hdr[2][LU_MAX_CTAS];                       // data = |a| (double bits); tag = seq<<32 | position
+  LLPacket row[2][LU_MAX_CTAS][LU_MAX_JB * 2];        // candidate row, columns j.. (rotated)
+  LLPacket rinv[2][LU_MAX_CTAS][2];                   // 1 / (the candidate's entry in column j)
 };
 
 __device__ __forceinline__ void ll_store(LLPacket* p, unsigned long long data,
@@ -95,6 +106,40 @@ template <> __device__ __forceinline__ zcomplex ll_get<zcomplex>(const LLPacket*
   return v;
 }
 
+// Two values polled together, so that the two L2 round trips overlap.
+template <typename T>
+__device__ __forceinline__ void ll_get2(const LLPacket* p, const LLPacket* q, unsigned seq, T& u, T& v);
+template <>
+__device__ __forceinline__ void ll_get2<double>(const LLPacket* p, const LLPacket* q, unsigned seq,
+                                                double& u, double& v) {
+  unsigned long long d1, t1, d2, t2;
+  do { ll_load(p, d1, t1); ll_load(q, d2, t2); }
+  while ((unsigned)(t1 >> 32) != seq || (unsigned)(t2 >> 32) != seq);
+  u = __longlong_as_double((long long)d1);
+  v = __longlong_as_double((long long)d2);
+}
+template <>
+__device__ __forceinline__ void ll_get2<float>(const LLPacket* p, const LLPacket* q, unsigned seq,
+                                               float& u, float& v) {
+  unsigned long long d1, t1, d2, t2;
+  do { ll_load(p, d1, t1); ll_load(q, d2, t2); }
+  while ((unsigned)(t1 >> 32) != seq || (unsigned)(t2 >> 32) != seq);
+  u = __uint_as_float((unsigned)d1);
+  v = __uint_as_float((unsigned)d2);
+}
+template <>
+__device__ __forceinline__ void ll_get2<zcomplex>(const LLPacket* p, const LLPacket* q, unsigned seq,
+                                                  zcomplex& u, zcomplex& v) {
+  unsigned long long d[4], t[4];
+  do {
+    ll_load(p, d[0], t[0]); ll_load(p + 1, d[1], t[1]);
+    ll_load(q, d[2], t[2]); ll_load(q + 1, d[3], t[3]);
+  } while ((unsigned)(t[0] >> 32) != seq || (unsigned)(t[1] >> 32) != seq ||
+           (unsigned)(t[2] >> 32) != seq || (unsigned)(t[3] >> 32) != seq);
+  u.x = __longlong_as_double((long long)d[0]); u.y = __longlong_as_double((long long)d[1]);
+  v.x = __longlong_as_double((long long)d[2]); v.y = __longlong_as_double((long long)d[3]);
+}
+
 // Pivot candidates are compared through integer keys: for non-negative doubles the IEEE bit
 // pattern orders like the value, and integer compares are several times shorter than FP64 ones
 // on the serial path of every column.  NaN magnitudes get key 0 (they never win, as in i?amax,
@@ -137,43 +182,6 @@ __device__ __forceinline__ void warp_argmax_redux(ukey& v, int& i) {
   i = (int)mi;
 }
 
-// One elimination step on a row held in registers: l = a[J] / pivot, a[c] -= l * prow[c] for
-// c > J, and the key of the next column's entry.  J is a compile-time constant so that a[]
-// never leaves the register file.
-template <typename T, int JBM, int J>
-__device__ __forceinline__ void eliminate(T (&a)[JBM], const T* __restrict__ prow, T rinv, T pivot,
-                                          bool use_recip, ukey& next_key) {
-  const T l = use_recip ? mul(a[J], rinv) : div_(a[J], pivot);
-  a[J] = l;
-#pragma unroll
-  for (int c = J + 1; c < JBM; c++) a[c] = fnma_(l, prow[c], a[c]);
-  if (J + 1 < JBM) next_key = key_of((double)abs1(a[J + 1 < JBM ? J + 1 : J]));
-}
-
-template <typename T, int JBM, int J>
-struct Dispatch {
-  __device__ __forceinline__ static void run(int j, T (&a)[JBM], const T* prow, T rinv, T pivot,
-                                             bool use_recip, ukey& nk) {
-    if (j == J) eliminate<T, JBM, J>(a, prow, rinv, pivot, use_recip, nk);
-    else Dispatch<T, JBM, J + 1>::run(j, a, prow, rinv, pivot, use_recip, nk);
-  }
-};
-template <typename T, int JBM>
-struct Dispatch<T, JBM, JBM> {
-  __device__ __forceinline__ static void run(int, T (&)[JBM], const T*, T, T, bool, ukey&) {}
-};
-
-template <typename T, int JBM, int J>
-struct KeyAt {
-  __device__ __forceinline__ static ukey get(int j, const T (&a)[JBM]) {
-    return j == J ? key_of((double)abs1(a[J])) : KeyAt<T, JBM, J + 1>::get(j, a);
-  }
-};
-template <typename T, int JBM>
-struct KeyAt<T, JBM, JBM> {
-  __device__ __forceinline__ static ukey get(int, const T (&)[JBM]) { return 0; }
-};
-
 // LU with partial pivoting of an m x jb panel (m >= jb, jb <= JBM), R rows per thread (rows
 // rs + r * LU_NT + tid of the CTA's slice of R * LU_NT rows), rows in REGISTERS for the whole
 // launch (the elimination would otherwise be bound by the shared-memory bandwidth of the few SMs
@@ -187,14 +195,18 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   constexpr int W = Words<T>::N;
   constexpr int NW = LU_NT / 32;
   constexpr int JBM = MaxJb<T>::N / R;
+  constexpr int PS = JBM + 2;                      // stride of a pivot-row buffer
+  constexpr int NONE = 0x7fffffff;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int G = gridDim.x;
-  T* cand = reinterpret_cast<T*>(smem_raw);      // cand[w * JBM + c]: each warp's best row
-  T* prow2 = cand + NW * JBM;                    // prow2[par][c]: the pivot row of column j
-  T* rj2 = prow2 + 2 * JBM;                      // rj2[par][c]: row j of the panel
+  T* Ls = reinterpret_cast<T*>(smem_raw);          // Ls[c * rpc + local row]: finished L entries
+  T* cand = Ls + (size_t)JBM * R * LU_NT;          // cand[c]: the CTA's candidate row as staged
+  T* prow2 = cand + PS;                            // prow2[par][c]: pivot row of column j, columns j + c
+  T* misc = prow2 + 2 * PS;                        // [par]: 1 / pivot; [2]: l of the candidate's pending tail
   __shared__ ukey sval[NW];
   __shared__ int sidx[NW];
   __shared__ int s_pi[2];
+  __shared__ int s_cand_raw;                       // the staged candidate lacks the tail of column j-1
 
   const int tid = threadIdx.x, lane = tid & 31;
   // broadcast from lane 0: tells the compiler that the warp index is warp-uniform, so that the
@@ -204,8 +216,12 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   const int rs = blockIdx.x * rpc;                 // rpc == R * LU_NT rows per CTA
   const int gr0 = rs + tid;                        // this thread's rows: gr0 + r * LU_NT
 
-  T a[R][JBM];
-  ukey nk[R];
+  T a[R][JBM];     // a[r][c]: column (current column + c) of the row
+  T lprev[R];      // the row's multiplier of the column whose tail is pending
+  ukey nk[R];      // key of a[r][0]
+  int pos[R];      // the row's current position in the panel (LAPACK's row index)
+  unsigned act = 0;   // bit r: row r is in play (valid and not yet a pivot row)
+  unsigned pend = 0;  // bit r: the tail of the previous column is pending
 #pragma unroll
   for (int r = 0; r < R; r++) {
     const int gr = gr0 + r * LU_NT;
@@ -213,136 +229,159 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
     for (int c = 0; c < JBM; c++)
       a[r][c] = (gr < m && c < jb) ? A[(int64_t)gr + (int64_t)c * lda] : zero<T>();
     nk[r] = gr < m ? key_of((double)abs1(a[r][0])) : 0;
+    lprev[r] = zero<T>();
+    pos[r] = gr;
+    if (gr < m) act |= 1u << r;
   }
+  if (tid < 2 * PS) prow2[tid] = zero<T>();
 
-  // Two block barriers per column.  Everything the barriers separate is double-buffered by
-  // column parity (prow2, rj2, s_pi, the exchange packets) or is only touched by warp 0 between
-  // them (cand, sval, sidx), so column j+1's first phase may start while slower warps are still
-  // eliminating column j.
   for (int j = 0; j < jb; j++) {
     const int par = j & 1;
     const unsigned seq = seq_base + (unsigned)j + 1u;
-    T* prow = prow2 + par * JBM;
-    T* rj = rj2 + par * JBM;
-    const bool own_j = j >= rs && j < rs + R * LU_NT;
+    T* prow = prow2 + par * PS;
+    const T* pp = prow2 + (par ^ 1) * PS;          // pivot row of column j-1 (pending tails)
     TRACE(0);
-    // ---- arg-max of column j over the rows gr >= j: per warp, then across warps
+    // ---- arg-max of column j over the rows in play: per thread, per warp, per CTA
     ukey bv = 0;
-    int bi = 0x7fffffff;
+    int bi = NONE;
 #pragma unroll
-    for (int r = 0; r < R; r++) {   // this thread's best row (rows ascend with r: ties keep the first)
-      const int gr = gr0 + r * LU_NT;
-      if (gr < m && gr >= j && (bi == 0x7fffffff || nk[r] > bv)) { bv = nk[r]; bi = gr; }
-    }
-    const int mine = bi;
+    for (int r = 0; r < R; r++)
+      if (((act >> r) & 1u) && (bi == NONE || nk[r] > bv || (nk[r] == bv && pos[r] < bi))) {
+        bv = nk[r]; bi = pos[r];
+      }
     warp_argmax_redux(bv, bi);
-#pragma unroll
-    for (int r = 0; r < R; r++) {
-      const int gr = gr0 + r * LU_NT;
-      if (gr == bi && mine == bi && gr < m) {   // this lane owns the warp's best row: stage it
-#pragma unroll
-        for (int c = 0; c < JBM; c++) cand[warp * JBM + c] = a[r][c];
-      }
-      if (gr == j) {                            // this lane owns row j
-#pragma unroll
-        for (int c = 0; c < JBM; c++) rj[c] = a[r][c];
-      }
-    }
     if (lane == 0) { sval[warp] = bv; sidx[warp] = bi; }
     __syncthreads();
     TRACE(1);
+    ukey cv = lane < NW ? sval[lane] : 0;
+    int ci = lane < NW ? sidx[lane] : NONE;
+    warp_argmax_redux(cv, ci);                      // every warp: the CTA's candidate
+    // ---- its owner stages it as it is (registers 0..JBM-1 and the pending multiplier)
+#pragma unroll
+    for (int r = 0; r < R; r++)
+      if (((act >> r) & 1u) && pos[r] == ci) {
+#pragma unroll
+        for (int c = 0; c < JBM; c++) cand[c] = a[r][c];
+        misc[2] = lprev[r];
+        s_cand_raw = (int)((pend >> r) & 1u);
+      }
+    __syncthreads();
+    TRACE(2);
     if (warp == 0) {
-      ukey cv = lane < NW ? sval[lane] : 0;
-      int ci = lane < NW ? sidx[lane] : 0x7fffffff;
-      const int myw = lane;
-      warp_argmax_redux(cv, ci);
-      // the warp whose entry won (smallest warp among equals holds the smallest row)
-      const bool have = ci != 0x7fffffff;
-      const unsigned wm = __ballot_sync(0xffffffffu, lane < NW && sidx[myw < NW ? myw : 0] == ci && have);
-      const int wwin = have ? __ffs(wm) - 1 : 0;
-      const T crow = (have && lane < JBM) ? cand[wwin * JBM + lane] : zero<T>();
+      const bool have = ci != NONE;
+      // the candidate in the coordinates of column j: entry 0 is final (the head wrote it); with
+      // a pending tail entry c >= 1 is still in register c+1 and lacks l * (pivot row j-1)[c+1]
+      T crow = zero<T>();
+      if (have && lane < JBM) {
+        if (!s_cand_raw || lane == 0) crow = cand[lane];
+        else if (lane + 1 < JBM) crow = fnma_(misc[2], pp[lane + 1], cand[lane + 1]);
+      }
+      const T cpiv = have ? cand[0] : zero<T>();
+      // a zero pivot leaves the trailing columns alone (?getf2): its row goes out as zeros
+      if (is_zero(cpiv) && lane >= 1) crow = zero<T>();
+      const T crinv = is_zero(cpiv) ? zero<T>() : recip(cpiv);
       if (G == 1) {  // single CTA: no global exchange
         if (lane < JBM) prow[lane] = crow;
-        if (lane == 0) { s_pi[par] = ci; ipiv[j] = row0 + ci + 1; }
+        if (lane == 0) { s_pi[par] = ci; ipiv[j] = row0 + ci + 1; misc[par] = crinv; }
       } else {
-        // publish this CTA's candidate (|value|, row) with the row's contents, and row j
+        // publish this CTA's candidate (|value|, position) with the row's contents
         if (lane == 0)
           ll_store(&xch->hdr[par][blockIdx.x], cv,
                    ((unsigned long long)seq << 32) | (unsigned)(have ? ci : 0xffffffffu));
         if (lane < JBM) ll_put<T>(&xch->row[par][blockIdx.x][lane * W], crow, seq);
-        if (own_j && lane < JBM) ll_put<T>(&xch->rowj[par][lane * W], rj[lane], seq);
-        TRACE(2);
-        // every CTA's header, one (or a few) per lane -> the same winner everywhere
-        ukey pv = 0;
-        int pi = 0x7fffffff, pg = 0;
-        for (int g = lane; g < G; g += 32) {
-          unsigned long long d, t;
-          ll_wait(&xch->hdr[par][g], seq, d, t);
-          const unsigned uidx = (unsigned)(t & 0xffffffffull);
-          const int idx = uidx == 0xffffffffu ? 0x7fffffff : (int)uidx;
-          if (idx != 0x7fffffff && (pi == 0x7fffffff || d > pv || (d == pv && idx < pi))) {
-            pv = d; pi = idx; pg = g;
-          }
-        }
-        int pi_w = pi;
-        warp_argmax_redux(pv, pi_w);
-        const unsigned gm = __ballot_sync(0xffffffffu, pi == pi_w && pi_w != 0x7fffffff);
-        const int src = gm ? __ffs(gm) - 1 : 0;
-        pg = __shfl_sync(0xffffffffu, pg, src);
+        if (lane == 0) ll_put<T>(&xch->rinv[par][blockIdx.x][0], crinv, seq);
         TRACE(3);
-        // only the winner's row is fetched (it was published together with its header)
-        if (lane < JBM)
-          prow[lane] = pg == (int)blockIdx.x ? crow : ll_get<T>(&xch->row[par][pg][lane * W], seq);
-        if (lane == 0) {
-          s_pi[par] = pi_w;
-          if (blockIdx.x == 0) ipiv[j] = row0 + pi_w + 1;
+      }
+    }
+    // ---- pending tails (column j-1), while the packets travel
+#pragma unroll
+    for (int r = 0; r < R; r++)
+      if ((pend >> r) & 1u) {
+#pragma unroll
+        for (int c = 2; c < JBM; c++) a[r][c - 1] = fnma_(lprev[r], pp[c], a[r][c]);
+        a[r][JBM - 1] = zero<T>();
+      }
+    pend = 0;
+    if (warp == 0 && G > 1) {
+      // every CTA's header, one (or a few) per lane -> the same winner everywhere
+      ukey pv = 0;
+      int pi = NONE, pg = 0;
+      for (int g = lane; g < G; g += 32) {
+        unsigned long long d, t;
+        ll_wait(&xch->hdr[par][g], seq, d, t);
+        const unsigned uidx = (unsigned)(t & 0xffffffffull);
+        const int idx = uidx == 0xffffffffu ? NONE : (int)uidx;
+        if (idx != NONE && (pi == NONE || d > pv || (d == pv && idx < pi))) {
+          pv = d; pi = idx; pg = g;
         }
       }
-    } else if (warp == 1 && G > 1 && !own_j) {
-      // row j comes from its owner CTA
-      if (lane < JBM) rj[lane] = ll_get<T>(&xch->rowj[par][lane * W], seq);
+      int pi_w = pi;
+      warp_argmax_redux(pv, pi_w);
+      const unsigned gm = __ballot_sync(0xffffffffu, pi == pi_w && pi_w != NONE);
+      const int src = gm ? __ffs(gm) - 1 : 0;
+      pg = __shfl_sync(0xffffffffu, pg, src);
+      TRACE(4);
+      // only the winner's row is fetched (it was published together with its header), and the
+      // reciprocal that followed it
+      T prv, rv;
+      ll_get2<T>(&xch->row[par][pg][(lane < JBM ? lane : 0) * W], &xch->rinv[par][pg][0], seq,
+                 prv, rv);
+      if (lane < JBM) prow[lane] = prv;
+      if (lane == 0) {
+        misc[par] = rv;
+        s_pi[par] = pi_w;
+        if (blockIdx.x == 0) ipiv[j] = row0 + pi_w + 1;
+      }
     }
     __syncthreads();
-    TRACE(4);
+    TRACE(5);
+    // ---- the interchange (positions only), then the head of the elimination: scale column j,
+    //      update column j+1 (into register 0), key of its entry
     const int pi = s_pi[par];
-    // ---- row interchange j <-> pi in the registers of the two owners
-    if (pi != j) {
-#pragma unroll
-      for (int r = 0; r < R; r++) {
-        const int gr = gr0 + r * LU_NT;
-        if (gr == pi) {
-#pragma unroll
-          for (int c = 0; c < JBM; c++) a[r][c] = rj[c];
-        } else if (gr == j) {
-#pragma unroll
-          for (int c = 0; c < JBM; c++) a[r][c] = prow[c];
-        }
-      }
-    }
-    // ---- eliminate: scale column j, rank-1 update, key of the next column's entry
-    const T pivot = prow[j];
+    const T pivot = prow[0];
+    const T p1 = prow[1];
+    const T rinv = misc[par];
     const bool zero_pivot = is_zero(pivot);
     if (zero_pivot && blockIdx.x == 0 && tid == 0) atomicCAS(info, 0, row0 + j + 1);
     const bool use_recip = (Real)abs1(pivot) >= sfmin<Real>();
-    const T rinv = zero_pivot ? zero<T>() : recip(pivot);
 #pragma unroll
-    for (int r = 0; r < R; r++) {
-      const int gr = gr0 + r * LU_NT;
-      nk[r] = 0;
-      if (gr < m && gr > j) {
-        if (!zero_pivot) Dispatch<T, JBM, 0>::run(j, a[r], prow, rinv, pivot, use_recip, nk[r]);
-        else nk[r] = KeyAt<T, JBM, 0>::get(j + 1, a[r]);   // as ?getf2: no scaling, no update
+    for (int r = 0; r < R; r++)
+      if ((act >> r) & 1u) {
+        if (pos[r] == pi) {           // the pivot row: now at position j, holding U(j, j:)
+          pos[r] = j;
+          act &= ~(1u << r);
+        } else {
+          if (pos[r] == j) pos[r] = pi;
+          const T l = zero_pivot ? a[r][0]
+                                 : (use_recip ? mul(a[r][0], rinv) : div_(a[r][0], pivot));
+          Ls[(size_t)j * rpc + r * LU_NT + tid] = l;
+          lprev[r] = l;
+          if (JBM > 1) {
+            a[r][0] = fnma_(l, p1, a[r][JBM > 1 ? 1 : 0]);
+            nk[r] = key_of((double)abs1(a[r][0]));
+            pend |= 1u << r;
+          }
+        }
       }
-    }
-    TRACE(5);
+    TRACE(6);
   }
+  // ---- every row goes to its final position: L entries from shared memory; a pivot row (frozen
+  //      at column p = its position) adds U(p, p:) from its registers.  The tail still pending here
+  //      belongs to column jb-1 and would touch columns >= jb only.
 #pragma unroll
   for (int r = 0; r < R; r++) {
     const int gr = gr0 + r * LU_NT;
     if (gr < m) {
+      const int p = pos[r];
+      const bool frozen = !((act >> r) & 1u);
+      const int nl = frozen ? p : jb;
+      T* dst = A + (int64_t)p;
+      for (int c = 0; c < nl; c++) dst[(int64_t)c * lda] = Ls[(size_t)c * rpc + r * LU_NT + tid];
+      if (frozen) {
 #pragma unroll
-      for (int c = 0; c < JBM; c++)
-        if (c < jb) A[(int64_t)gr + (int64_t)c * lda] = a[r][c];
+        for (int c = 0; c < JBM; c++)
+          if (p + c < jb) dst[(int64_t)(p + c) * lda] = a[r][c];
+      }
     }
   }
 }
@@ -424,7 +463,7 @@ static void lu_panel_launch(Context& ctx, int64_t m, int jb, T* A, int64_t lda, 
     fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
     abort();
   }
-  size_t smem = ((size_t)(LU_NT / 32) * JBM + 4 * (size_t)JBM) * sizeof(T) + 16;
+  size_t smem = ((size_t)MaxJb<T>::N * LU_NT + 3 * (size_t)(JBM + 2) + 4) * sizeof(T) + 16;
   int mi = (int)m, row0i = (int)row0, rpci = (int)rpc;
   unsigned seq_base = st->seq;
   st->seq += 64;
