@@ -17,7 +17,9 @@ namespace la {
 template <typename T>
 void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
               int* d_info);
-int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes);
+int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes, bool wide);
+int lu_panel_ctas(Context& ctx, int64_t m, size_t elem_bytes, bool wide);
+bool lu_panel_wide_ok(int64_t m);
 void lu_panel_prepare(Context& ctx);
 void lu_panel_begin(Context& ctx, int64_t m);
 
@@ -48,7 +50,7 @@ __global__ void laswp_kernel(int64_t n, T* __restrict__ A, int64_t lda, int64_t 
 // more than the interchange itself.
 struct SwapJob { int64_t col0; int ncols, k1, k2; };
 struct LuPlan {
-  int nb0;                       // leaf panel width for this matrix height
+  int nb0;                       // leaf width for the panel being factored (depends on its height)
   std::vector<SwapJob> pending;  // queued interchanges of the panel being factored
 };
 template <typename T>
@@ -315,7 +317,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   const int64_t k = m < n ? m : n;
   if (k <= 0) return;
   LuPlan plan;
-  const int64_t nb0 = lu_panel_max_width(ctx, m, sizeof(T));
+  const int64_t nb0 = lu_panel_max_width(ctx, m, sizeof(T), false);
   if (nb0 < 1) {
     fprintf(stderr, "la_b200: getrf: %lld rows exceed the panel kernel's capacity\n", (long long)m);
     abort();
@@ -359,6 +361,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     const bool tl_on = panel_done || j0 == 0;
     if (tl_on && lookahead) TL(ctx.stream);
     if (!panel_done) {
+      plan.nb0 = lu_panel_max_width(ctx, m - j0, sizeof(T), true);   // nothing else runs beside it
       getrf_rec<T>(ctx, m, A, lda, d_ipiv, d_info, j0, jb, plan);
       flush_swaps<T>(ctx, m, A, lda, d_ipiv, plan);
     }
@@ -378,16 +381,23 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     const int64_t j1 = j0 + jb;
     const int64_t jb1 = j1 < k ? (NB < k - j1 ? NB : k - j1) : 0;
     if (lookahead && jb1 > 0 && nr > jb1) {
-      // the next panel has m - j1 rows: its cooperative leaf needs that many SMs / 512, the rest
-      // of the side stream's work is happy with 16
-      const int64_t ctas1 = ceil_div(m - j1, (int64_t)512);
+      // Timing model of the step (ms; B200, FP64): the trailing update on the whole GPU, and the
+      // next panel (m - j1 rows) when its own updates get plenty of SMs or just those of its
+      // leaves.  The panel is a chain of latency-bound launches whose length hardly depends on
+      // its height.
+      static const double model_scale = getenv("LA_B200_LU_MODEL") ? atof(getenv("LA_B200_LU_MODEL")) : 1.1;
+      const double h = (double)(m - j1) / 16384.0;
+      const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / 33.0e9;
+      const double pan_free_ms = 1.5 + 0.3 * h;
+      const double pan_tight_ms = model_scale * (1.6 + 0.9 * h);
+      // the wide leaf needs twice the SMs per row: worth it once the update is small beside the panel
+      const bool wide = lu_panel_wide_ok(m - j1) && upd_ms < 0.5 * pan_free_ms;
+      const int64_t ctas1 = lu_panel_ctas(ctx, m - j1, sizeof(T), wide);
       int side_sms = (int)(ctas1 < 16 ? 16 : ctas1);
       {
         // late steps: the trailing update is shorter than the panel, so the panel's own
         // GEMMs / TRSMs get the SMs the update does not need to finish in the panel's time
-        const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / 31.0e9;
-        const double pan_ms = 1.6 + 1.5 * (double)(m - j1) / 16384.0;
-        const int need = (int)(ctx.sm_count * upd_ms / pan_ms) + 1;
+        const int need = (int)(ctx.sm_count * upd_ms / pan_free_ms) + 1;
         int spare = ctx.sm_count - (need < 32 ? 32 : need);
         if (spare > 116) spare = 116;
         if (spare > side_sms) side_sms = spare;
@@ -397,6 +407,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       LA_CUDA_CHECK(cudaEventRecord(ctx.ev[0], ctx.stream));
       LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));
       side->sm_limit = side_sms;
+      plan.nb0 = lu_panel_max_width(ctx, m - j1, sizeof(T), wide);
       getrf_rec<T>(*side, m, A, lda, d_ipiv, d_info, j1, jb1, plan);
       flush_swaps<T>(*side, m, A, lda, d_ipiv, plan);
       TL(side->stream);
@@ -406,9 +417,8 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       // update that outlasts the panel merely keeps a few SMs idle, one that ends early stalls
       // the whole device); the rest of it is launched on all SMs once the panel is done.
       const int64_t rest = nr - jb1;
-      static const double model_scale = getenv("LA_B200_LU_MODEL") ? atof(getenv("LA_B200_LU_MODEL")) : 1.25;
-      const double panel_ms = model_scale * (1.6 + 1.5 * (double)(m - j1) / 16384.0);
-      const double flop_per_ms = 31.0e9 * (double)(ctx.sm_count - side_sms) / 148.0;
+      const double panel_ms = side_sms > ctas1 + 16 ? pan_free_ms : pan_tight_ms;
+      const double flop_per_ms = 33.0e9 * (double)(ctx.sm_count - side_sms) / 148.0;
       int64_t c1 = (int64_t)(panel_ms * flop_per_ms / (2.0 * (double)mr * (double)jb));
       c1 = round_up(c1 > 0 ? c1 : 1, (int64_t)128);
       if (c1 + 1024 >= rest) c1 = rest;

@@ -38,7 +38,9 @@ namespace la {
 
 namespace {
 
-constexpr int LU_NT = 512;
+constexpr int LU_NT = 512;        // threads (= rows per CTA with one row per thread) of the standard leaf
+constexpr int LU_NT_WIDE = 256;   // the wide leaf: half the threads, rows twice as long
+constexpr int LU_WIDE_MAX_CTAS = 32;
 constexpr int LU_MAX_JB = 32;
 constexpr int LU_MAX_CTAS = 160;
 constexpr size_t LU_SMEM_TOTAL = 224 * 1024;
@@ -56,7 +58,8 @@ template <> struct MaxJb<zcomplex> { static constexpr int N = 16; };
 
 struct LuExchange {
   LLPacket hdr[2][LU_MAX_CTAS];                       // data = |a| (double bits); tag = seq<<32 | position
-  LLPacket row[2][LU_MAX_CTAS][LU_MAX_JB * 2];        // candidate row, columns j.. (rotated)
+  LLPacket row[2][LU_MAX_CTAS * LU_MAX_JB];           // candidate rows, columns j.. (rotated): CTA g's
+                                                      // starts at packet g * (leaf width in words)
   LLPacket rinv[2][LU_MAX_CTAS][2];                   // 1 / (the candidate's entry in column j)
 };
 
@@ -106,39 +109,49 @@ template <> __device__ __forceinline__ zcomplex ll_get<zcomplex>(const LLPacket*
   return v;
 }
 
-// Two values polled together, so that the two L2 round trips overlap.
-template <typename T>
-__device__ __forceinline__ void ll_get2(const LLPacket* p, const LLPacket* q, unsigned seq, T& u, T& v);
-template <>
-__device__ __forceinline__ void ll_get2<double>(const LLPacket* p, const LLPacket* q, unsigned seq,
-                                                double& u, double& v) {
-  unsigned long long d1, t1, d2, t2;
-  do { ll_load(p, d1, t1); ll_load(q, d2, t2); }
-  while ((unsigned)(t1 >> 32) != seq || (unsigned)(t2 >> 32) != seq);
-  u = __longlong_as_double((long long)d1);
-  v = __longlong_as_double((long long)d2);
+template <typename T> __device__ __forceinline__ T from_words(const unsigned long long* d);
+template <> __device__ __forceinline__ double from_words<double>(const unsigned long long* d) {
+  return __longlong_as_double((long long)d[0]);
 }
-template <>
-__device__ __forceinline__ void ll_get2<float>(const LLPacket* p, const LLPacket* q, unsigned seq,
-                                               float& u, float& v) {
-  unsigned long long d1, t1, d2, t2;
-  do { ll_load(p, d1, t1); ll_load(q, d2, t2); }
-  while ((unsigned)(t1 >> 32) != seq || (unsigned)(t2 >> 32) != seq);
-  u = __uint_as_float((unsigned)d1);
-  v = __uint_as_float((unsigned)d2);
+template <> __device__ __forceinline__ float from_words<float>(const unsigned long long* d) {
+  return __uint_as_float((unsigned)d[0]);
 }
-template <>
-__device__ __forceinline__ void ll_get2<zcomplex>(const LLPacket* p, const LLPacket* q, unsigned seq,
-                                                  zcomplex& u, zcomplex& v) {
-  unsigned long long d[4], t[4];
+template <> __device__ __forceinline__ zcomplex from_words<zcomplex>(const unsigned long long* d) {
+  zcomplex v;
+  v.x = __longlong_as_double((long long)d[0]);
+  v.y = __longlong_as_double((long long)d[1]);
+  return v;
+}
+// This lane's EPL entries (lane, lane + 32, ...) of a published row of `width` entries together
+// with the reciprocal that follows it: all packets are polled in one loop, so that their L2
+// round trips overlap.
+template <typename T, int EPL>
+__device__ __forceinline__ void ll_get_row(const LLPacket* row, int lane, int width,
+                                           const LLPacket* rinvp, unsigned seq, T (&v)[EPL], T& rv) {
+  constexpr int W = Words<T>::N;
+  constexpr int NP = (EPL + 1) * W;
+  unsigned long long d[NP], t[NP];
+  bool ok;
   do {
-    ll_load(p, d[0], t[0]); ll_load(p + 1, d[1], t[1]);
-    ll_load(q, d[2], t[2]); ll_load(q + 1, d[3], t[3]);
-  } while ((unsigned)(t[0] >> 32) != seq || (unsigned)(t[1] >> 32) != seq ||
-           (unsigned)(t[2] >> 32) != seq || (unsigned)(t[3] >> 32) != seq);
-  u.x = __longlong_as_double((long long)d[0]); u.y = __longlong_as_double((long long)d[1]);
-  v.x = __longlong_as_double((long long)d[2]); v.y = __longlong_as_double((long long)d[3]);
+    ok = true;
+#pragma unroll
+    for (int e = 0; e < EPL; e++) {
+      const int c = lane + 32 * e < width ? lane + 32 * e : 0;
+#pragma unroll
+      for (int w = 0; w < W; w++) ll_load(row + c * W + w, d[e * W + w], t[e * W + w]);
+    }
+#pragma unroll
+    for (int w = 0; w < W; w++) ll_load(rinvp + w, d[EPL * W + w], t[EPL * W + w]);
+#pragma unroll
+    for (int i = 0; i < NP; i++) ok = ok && (unsigned)(t[i] >> 32) == seq;
+  } while (!ok);
+#pragma unroll
+  for (int e = 0; e < EPL; e++) v[e] = from_words<T>(d + e * W);
+  rv = from_words<T>(d + EPL * W);
 }
+
+// 16 bytes of a row at a time (the staging store of a candidate row)
+template <typename T> struct alignas(16) Vec16 { T v[16 / sizeof(T)]; };
 
 // Pivot candidates are compared through integer keys: for non-negative doubles the IEEE bit
 // pattern orders like the value, and integer compares are several times shorter than FP64 ones
@@ -187,20 +200,22 @@ __device__ __forceinline__ void warp_argmax_redux(ukey& v, int& i) {
 // launch (the elimination would otherwise be bound by the shared-memory bandwidth of the few SMs
 // that hold the panel).  R * JBM is constant (MaxJb<T>): the common case is one row of 32 columns
 // per thread; panels taller than sm_count * LU_NT rows trade leaf width for rows per thread.
-template <typename T, int R>
-__global__ void __launch_bounds__(LU_NT)
+template <typename T, int R, int NT>
+__global__ void __launch_bounds__(NT)
 lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__ ipiv, int row0,
                 int* info, LuExchange* xch, int rpc, unsigned seq_base) {
   using Real = typename Traits<T>::real;
   constexpr int W = Words<T>::N;
-  constexpr int NW = LU_NT / 32;
-  constexpr int JBM = MaxJb<T>::N / R;
+  constexpr int NW = NT / 32;
+  constexpr int JBM = MaxJb<T>::N * (LU_NT / NT) / R;   // R * NT * JBM is the same for all variants
+  constexpr int EPL = (JBM + 31) / 32;             // row entries per lane of warp 0
   constexpr int PS = JBM + 2;                      // stride of a pivot-row buffer
+  constexpr int VE = 16 / (int)sizeof(T);          // entries per 16-byte store
   constexpr int NONE = 0x7fffffff;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int G = gridDim.x;
   T* Ls = reinterpret_cast<T*>(smem_raw);          // Ls[c * rpc + local row]: finished L entries
-  T* cand = Ls + (size_t)JBM * R * LU_NT;          // cand[c]: the CTA's candidate row as staged
+  T* cand = Ls + (size_t)JBM * R * NT;          // cand[c]: the CTA's candidate row as staged
   T* prow2 = cand + PS;                            // prow2[par][c]: pivot row of column j, columns j + c
   T* misc = prow2 + 2 * PS;                        // [par]: 1 / pivot; [2]: l of the candidate's pending tail
   __shared__ ukey sval[NW];
@@ -213,8 +228,8 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   // reductions / ballots / shuffles under `if (warp == 0)` are emitted inline and not as
   // re-convergence (WARPSYNC.COLLECTIVE) sequences
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-  const int rs = blockIdx.x * rpc;                 // rpc == R * LU_NT rows per CTA
-  const int gr0 = rs + tid;                        // this thread's rows: gr0 + r * LU_NT
+  const int rs = blockIdx.x * rpc;                 // rpc == R * NT rows per CTA
+  const int gr0 = rs + tid;                        // this thread's rows: gr0 + r * NT
 
   T a[R][JBM];     // a[r][c]: column (current column + c) of the row
   T lprev[R];      // the row's multiplier of the column whose tail is pending
@@ -224,7 +239,7 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   unsigned pend = 0;  // bit r: the tail of the previous column is pending
 #pragma unroll
   for (int r = 0; r < R; r++) {
-    const int gr = gr0 + r * LU_NT;
+    const int gr = gr0 + r * NT;
 #pragma unroll
     for (int c = 0; c < JBM; c++)
       a[r][c] = (gr < m && c < jb) ? A[(int64_t)gr + (int64_t)c * lda] : zero<T>();
@@ -260,8 +275,21 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
 #pragma unroll
     for (int r = 0; r < R; r++)
       if (((act >> r) & 1u) && pos[r] == ci) {
+        // (columns j .. jb-1 only, one register further with a pending tail)
+        const int live = jb - j + 1;
+        if (JBM >= VE) {
 #pragma unroll
-        for (int c = 0; c < JBM; c++) cand[c] = a[r][c];
+          for (int c = 0; c + VE <= JBM; c += VE)
+            if (c < live) {
+              Vec16<T> v;
+#pragma unroll
+              for (int i = 0; i < VE; i++) v.v[i] = a[r][c + i];
+              *reinterpret_cast<Vec16<T>*>(cand + c) = v;
+            }
+        } else {
+#pragma unroll
+          for (int c = 0; c < JBM; c++) cand[c] = a[r][c];
+        }
         misc[2] = lprev[r];
         s_cand_raw = (int)((pend >> r) & 1u);
       }
@@ -271,26 +299,43 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
       const bool have = ci != NONE;
       // the candidate in the coordinates of column j: entry 0 is final (the head wrote it); with
       // a pending tail entry c >= 1 is still in register c+1 and lacks l * (pivot row j-1)[c+1]
-      T crow = zero<T>();
-      if (have && lane < JBM) {
-        if (!s_cand_raw || lane == 0) crow = cand[lane];
-        else if (lane + 1 < JBM) crow = fnma_(misc[2], pp[lane + 1], cand[lane + 1]);
+      T crow[EPL];
+#pragma unroll
+      for (int e = 0; e < EPL; e++) {
+        const int c = lane + 32 * e;
+        crow[e] = zero<T>();
+        if (have && c < JBM) {
+          if (!s_cand_raw || c == 0) crow[e] = cand[c];
+          else if (c + 1 < JBM) crow[e] = fnma_(misc[2], pp[c + 1], cand[c + 1]);
+        }
       }
       const T cpiv = have ? cand[0] : zero<T>();
       // a zero pivot leaves the trailing columns alone (?getf2): its row goes out as zeros
-      if (is_zero(cpiv) && lane >= 1) crow = zero<T>();
-      const T crinv = is_zero(cpiv) ? zero<T>() : recip(cpiv);
+      if (is_zero(cpiv)) {
+#pragma unroll
+        for (int e = 0; e < EPL; e++)
+          if (lane + 32 * e >= 1) crow[e] = zero<T>();
+      }
+      TRACE(7);
       if (G == 1) {  // single CTA: no global exchange
-        if (lane < JBM) prow[lane] = crow;
+#pragma unroll
+        for (int e = 0; e < EPL; e++)
+          if (lane + 32 * e < JBM) prow[lane + 32 * e] = crow[e];
+        const T crinv = is_zero(cpiv) ? zero<T>() : recip(cpiv);
         if (lane == 0) { s_pi[par] = ci; ipiv[j] = row0 + ci + 1; misc[par] = crinv; }
       } else {
-        // publish this CTA's candidate (|value|, position) with the row's contents
+        // publish this CTA's candidate (|value|, position) with the row's contents; the
+        // reciprocal is worked out once they are on their way
         if (lane == 0)
           ll_store(&xch->hdr[par][blockIdx.x], cv,
                    ((unsigned long long)seq << 32) | (unsigned)(have ? ci : 0xffffffffu));
-        if (lane < JBM) ll_put<T>(&xch->row[par][blockIdx.x][lane * W], crow, seq);
-        if (lane == 0) ll_put<T>(&xch->rinv[par][blockIdx.x][0], crinv, seq);
+        LLPacket* mine = &xch->row[par][(size_t)blockIdx.x * (JBM * W)];
+#pragma unroll
+        for (int e = 0; e < EPL; e++)
+          if (lane + 32 * e < JBM) ll_put<T>(&mine[(lane + 32 * e) * W], crow[e], seq);
         TRACE(3);
+        const T crinv = is_zero(cpiv) ? zero<T>() : recip(cpiv);
+        if (lane == 0) ll_put<T>(&xch->rinv[par][blockIdx.x][0], crinv, seq);
       }
     }
     // ---- pending tails (column j-1), while the packets travel
@@ -323,10 +368,12 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
       TRACE(4);
       // only the winner's row is fetched (it was published together with its header), and the
       // reciprocal that followed it
-      T prv, rv;
-      ll_get2<T>(&xch->row[par][pg][(lane < JBM ? lane : 0) * W], &xch->rinv[par][pg][0], seq,
-                 prv, rv);
-      if (lane < JBM) prow[lane] = prv;
+      T prv[EPL], rv;
+      ll_get_row<T, EPL>(&xch->row[par][(size_t)pg * (JBM * W)], lane, JBM, &xch->rinv[par][pg][0],
+                         seq, prv, rv);
+#pragma unroll
+      for (int e = 0; e < EPL; e++)
+        if (lane + 32 * e < JBM) prow[lane + 32 * e] = prv[e];
       if (lane == 0) {
         misc[par] = rv;
         s_pi[par] = pi_w;
@@ -354,7 +401,7 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
           if (pos[r] == j) pos[r] = pi;
           const T l = zero_pivot ? a[r][0]
                                  : (use_recip ? mul(a[r][0], rinv) : div_(a[r][0], pivot));
-          Ls[(size_t)j * rpc + r * LU_NT + tid] = l;
+          Ls[(size_t)j * rpc + r * NT + tid] = l;
           lprev[r] = l;
           if (JBM > 1) {
             a[r][0] = fnma_(l, p1, a[r][JBM > 1 ? 1 : 0]);
@@ -370,13 +417,13 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   //      belongs to column jb-1 and would touch columns >= jb only.
 #pragma unroll
   for (int r = 0; r < R; r++) {
-    const int gr = gr0 + r * LU_NT;
+    const int gr = gr0 + r * NT;
     if (gr < m) {
       const int p = pos[r];
       const bool frozen = !((act >> r) & 1u);
       const int nl = frozen ? p : jb;
       T* dst = A + (int64_t)p;
-      for (int c = 0; c < nl; c++) dst[(int64_t)c * lda] = Ls[(size_t)c * rpc + r * LU_NT + tid];
+      for (int c = 0; c < nl; c++) dst[(int64_t)c * lda] = Ls[(size_t)c * rpc + r * NT + tid];
       if (frozen) {
 #pragma unroll
         for (int c = 0; c < JBM; c++)
@@ -422,7 +469,7 @@ void lu_panel_prepare(Context& ctx) { (void)panel_state(ctx); }
 // Start of a factorisation of an m-row matrix on ctx.stream: stale packets of earlier calls are
 // wiped (in stream order) and the launch sequence restarts, so tags never repeat within a call.
 void lu_panel_begin(Context& ctx, int64_t m) {
-  if (m <= LU_NT) return;          // single-CTA leaves exchange nothing
+  if (m <= LU_NT_WIDE) return;     // single-CTA leaves exchange nothing
   LuPanelState* st = panel_state(ctx);
   LA_CUDA_CHECK(cudaMemsetAsync(st->xch, 0, sizeof(LuExchange), ctx.stream));
   st->seq = 64;
@@ -437,46 +484,74 @@ static int lu_rows_per_thread(Context& ctx, int64_t m, int max_jb) {
   return 0;
 }
 
+// The wide leaf (twice the columns on half the threads per CTA) halves the number of leaves and
+// removes the interchange / TRSM / GEMM launches between the two halves; it needs twice the CTAs
+// per row, so it is for panels that are short enough to leave the other SMs to the trailing
+// update.  LA_B200_LU_WIDE=0 turns it off.
+bool lu_panel_wide_ok(int64_t m) {
+  static const bool enabled = !(getenv("LA_B200_LU_WIDE") && atoi(getenv("LA_B200_LU_WIDE")) == 0);
+  return enabled && ceil_div(m, (int64_t)LU_NT_WIDE) <= LU_WIDE_MAX_CTAS;
+}
+
 // Widest leaf the panel kernel takes for an m-row panel (0: the panel is too tall for one
 // cooperative launch: more than sm_count * LU_NT * MaxJb rows).
-int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes) {
+int lu_panel_max_width(Context& ctx, int64_t m, size_t elem_bytes, bool wide) {
   const int base = elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
+  if (wide && lu_panel_wide_ok(m)) return base * (LU_NT / LU_NT_WIDE);
   const int R = lu_rows_per_thread(ctx, m, base);
   return R ? base / R : 0;
 }
 
-template <typename T, int R>
+// CTAs (= SMs) the leaves of an m-row panel occupy.
+int lu_panel_ctas(Context& ctx, int64_t m, size_t elem_bytes, bool wide) {
+  if (wide && lu_panel_wide_ok(m)) return (int)ceil_div(m, (int64_t)LU_NT_WIDE);
+  const int base = elem_bytes > 8 ? MaxJb<zcomplex>::N : LU_MAX_JB;
+  const int R = lu_rows_per_thread(ctx, m, base);
+  return R ? (int)ceil_div(m, (int64_t)R * LU_NT) : 0;
+}
+
+template <typename T, int R, int NT>
 static void lu_panel_launch(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv,
                             int64_t row0, int* d_info) {
   static DeviceOnce attr;
   if (attr.pending(ctx.device)) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T, R>,
+    LA_CUDA_CHECK(cudaFuncSetAttribute(lu_panel_kernel<T, R, NT>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)LU_SMEM_TOTAL));
     attr.mark(ctx.device);
   }
   LuPanelState* st = panel_state(ctx);
-  constexpr int JBM = MaxJb<T>::N / R;
-  const int64_t rpc = (int64_t)R * LU_NT;
+  constexpr int JBM = MaxJb<T>::N * (LU_NT / NT) / R;
+  static_assert(JBM * Words<T>::N <= 2 * LU_MAX_JB, "row packets");
+  const int64_t rpc = (int64_t)R * NT;
   const int64_t G = ceil_div(m, rpc);
-  if (G > LU_MAX_CTAS || G > ctx.sm_count || jb > JBM) {
+  if (G > LU_MAX_CTAS || G > ctx.sm_count || jb > JBM ||
+      G * JBM * Words<T>::N > (int64_t)LU_MAX_CTAS * LU_MAX_JB) {
     fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
     abort();
   }
   size_t smem = ((size_t)MaxJb<T>::N * LU_NT + 3 * (size_t)(JBM + 2) + 4) * sizeof(T) + 16;
   int mi = (int)m, row0i = (int)row0, rpci = (int)rpc;
   unsigned seq_base = st->seq;
-  st->seq += 64;
+  st->seq += 128;
   LuExchange* xch = st->xch;
   void* args[] = {&mi, &jb, &A, &lda, &ipiv, &row0i, &d_info, &xch, &rpci, &seq_base};
-  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lu_panel_kernel<T, R>, dim3((unsigned)G),
-                                            dim3(LU_NT), args, smem, ctx.stream));
+  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)lu_panel_kernel<T, R, NT>, dim3((unsigned)G),
+                                            dim3(NT), args, smem, ctx.stream));
 }
 
 template <typename T>
 void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int64_t row0,
               int* d_info) {
   constexpr int base = MaxJb<T>::N;
+  if (jb > base) {   // only the wide leaf takes this many columns
+    if (!lu_panel_wide_ok(m) || jb > base * (LU_NT / LU_NT_WIDE)) {
+      fprintf(stderr, "la_b200: internal error: LU panel %lld x %d does not fit\n", (long long)m, jb);
+      abort();
+    }
+    lu_panel_launch<T, 1, LU_NT_WIDE>(ctx, m, jb, A, lda, ipiv, row0, d_info);
+    return;
+  }
   // the narrowest R that fits the rows AND still takes jb columns
   int R = lu_rows_per_thread(ctx, m, base);
   if (R == 0 || jb > base / R) {
@@ -484,16 +559,16 @@ void lu_panel(Context& ctx, int64_t m, int jb, T* A, int64_t lda, int* ipiv, int
     abort();
   }
   switch (R) {
-    case 1: lu_panel_launch<T, 1>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
-    case 2: lu_panel_launch<T, 2>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
-    case 4: lu_panel_launch<T, 4>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
-    case 8: lu_panel_launch<T, 8>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 1: lu_panel_launch<T, 1, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 2: lu_panel_launch<T, 2, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 4: lu_panel_launch<T, 4, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
+    case 8: lu_panel_launch<T, 8, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break;
     default:
       if constexpr (base >= 32) {
-        if (R == 16) { lu_panel_launch<T, 16>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
-        if (R == 32) { lu_panel_launch<T, 32>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
+        if (R == 16) { lu_panel_launch<T, 16, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
+        if (R == 32) { lu_panel_launch<T, 32, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
       } else {
-        if (R == 16) { lu_panel_launch<T, 16>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
+        if (R == 16) { lu_panel_launch<T, 16, LU_NT>(ctx, m, jb, A, lda, ipiv, row0, d_info); break; }
       }
       fprintf(stderr, "la_b200: internal error: LU panel rows-per-thread %d\n", R);
       abort();

@@ -16,10 +16,11 @@ for m in (512, 4096, 16384):
     lib.la_b200_debug_panel_trace(out.ctypes.data_as(ctypes.c_void_p))
     t = out.reshape(64, 8)[:32]
     # slots: 0 column start, 1 after barrier A (warp candidates), 2 after barrier B (row staged),
-    # 3 published, 4 winner known, 5 after barrier 2, 6 head done
-    order = [0, 1, 2, 3, 4, 5, 6] if m > 512 else [0, 1, 2, 5, 6]
-    names = ["argmax+barrierA", "pick+stage+barrierB", "fixup+publish", "tails+gather", "fetch+barrier2", "head"] \
-        if m > 512 else ["argmax+barrierA", "pick+stage+barrierB", "warp0+tails+barrier2", "head"]
+    # 7 candidate completed, 3 published, 4 winner known, 5 after barrier 2, 6 head done
+    order = [0, 1, 2, 7, 3, 4, 5, 6] if m > 512 else [0, 1, 2, 5, 6]
+    names = ["argmax+barrierA", "pick+stage+barrierB", "fixup", "publish", "rinv+tails+gather",
+             "fetch+barrier2", "head"] if m > 512 else \
+            ["argmax+barrierA", "pick+stage+barrierB", "warp0+tails+barrier2", "head"]
     d = np.diff(t[:, order], axis=1)[2:30].mean(axis=0).round(0)
     nxt = t[1:, 0] - t[:-1, 6]
     print(f"m={m}: cycles per phase", dict(zip(names, d.tolist())), "loop-back", nxt[2:30].mean().round(0),
