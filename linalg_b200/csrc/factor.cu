@@ -184,6 +184,80 @@ void laswp_rows(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int64_t k
 
 namespace {
 
+// The same on a capped number of CTAs (one per SM the caller may use, beside a kernel of another
+// stream that needs its SMs whole): CB columns per pass keep enough loads in flight.
+template <typename T, int CB>
+__global__ void __launch_bounds__(1024)
+laswp_apply_capped_kernel(int64_t n, T* __restrict__ A, int64_t lda, int nent,
+                          const int* __restrict__ dst, const int* __restrict__ src) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* buf = reinterpret_cast<T*>(smem_raw);
+  for (int64_t c0 = (int64_t)blockIdx.x * CB; c0 < n; c0 += (int64_t)gridDim.x * CB) {
+    for (int e = threadIdx.x; e < nent; e += blockDim.x) {
+      const int64_t s = src[e];
+#pragma unroll
+      for (int i = 0; i < CB; i++)
+        if (c0 + i < n) buf[i * nent + e] = A[(c0 + i) * lda + s];
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < nent; e += blockDim.x) {
+      const int64_t d = dst[e];
+      if (d != src[e]) {
+#pragma unroll
+        for (int i = 0; i < CB; i++)
+          if (c0 + i < n) A[(c0 + i) * lda + d] = buf[i * nent + e];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// Net permutation of ipiv[k1, k2) into `lists` (4 * LASWP_CHUNK ints), for several applications
+// to different column ranges.  False: not representable (too many pivots / rows): use laswp_rows.
+bool laswp_lists(Context& ctx, int64_t m, int64_t k1, int64_t k2, const int* d_ipiv, int* lists) {
+  const int64_t mapn = m - k1;
+  if (k2 - k1 > LASWP_CHUNK || m <= 0 || mapn > LASWP_MAX_MAP) return false;
+  static DeviceOnce attr;
+  if (attr.pending(ctx.device)) {
+    LA_CUDA_CHECK(cudaFuncSetAttribute(laswp_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (LASWP_MAX_MAP + LASWP_CHUNK) * (int)sizeof(int)));
+    attr.mark(ctx.device);
+  }
+  const int npiv = (int)(k2 - k1);
+  laswp_prep_kernel<<<1, 256, (size_t)(mapn + npiv) * sizeof(int), ctx.stream>>>(
+      (int)k1, npiv, (int)mapn, d_ipiv, lists, lists + 2 * LASWP_CHUNK);
+  LA_CUDA_CHECK(cudaGetLastError());
+  return true;
+}
+
+// Apply prepared lists to n columns; honours ctx.sm_limit (one CTA per permitted SM).
+template <typename T>
+void laswp_apply_lists(Context& ctx, int64_t n, T* A, int64_t lda, int npiv, const int* lists) {
+  if (n <= 0) return;
+  const int nent = 2 * npiv;
+  const int* dst = lists;
+  const int* src = lists + 2 * LASWP_CHUNK;
+  if (ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count) {
+    constexpr int CB = 4;
+    static DeviceOnce attr;
+    if (attr.pending(ctx.device)) {
+      LA_CUDA_CHECK(cudaFuncSetAttribute(laswp_apply_capped_kernel<T, CB>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         2 * LASWP_CHUNK * CB * (int)sizeof(T)));
+      attr.mark(ctx.device);
+    }
+    int64_t grid = ceil_div(n, (int64_t)CB);
+    if (grid > ctx.sm_limit) grid = ctx.sm_limit;
+    laswp_apply_capped_kernel<T, CB><<<(unsigned)grid, 1024, (size_t)nent * CB * sizeof(T),
+                                       ctx.stream>>>(n, A, lda, nent, dst, src);
+  } else {
+    int64_t grid = n < (int64_t)ctx.sm_count * 8 ? n : (int64_t)ctx.sm_count * 8;
+    laswp_apply_kernel<T><<<(unsigned)grid, 256, (size_t)nent * sizeof(T), ctx.stream>>>(
+        n, A, lda, nent, dst, src);
+  }
+  LA_CUDA_CHECK(cudaGetLastError());
+}
+
 constexpr int LASWP_MAX_JOBS = 6;
 struct SwapJobs {
   int njobs;
@@ -366,30 +440,49 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       flush_swaps<T>(ctx, m, A, lda, d_ipiv, plan);
     }
     panel_done = false;
-    if (j0 > 0) laswp_rows<T>(ctx, m, j0, A, lda, j0, j0 + jb, d_ipiv);
     const int64_t nr = n - j0 - jb;  // columns to the right
-    if (nr <= 0) continue;
-    T* A12 = A + j0 + (j0 + jb) * lda;
-    laswp_rows<T>(ctx, m, nr, A + (j0 + jb) * lda, lda, j0, j0 + jb, d_ipiv);
-    trsm<T>(ctx, Left, Lower, OpN, Unit, jb, nr, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
-    // rows [j0, j0 + jb) of the whole matrix are final now: later panels interchange rows below
-    if (ctx.on_block_final) ctx.on_block_final(j0, j0 + jb);
     const int64_t mr = m - j0 - jb;
-    if (mr <= 0) continue;
-    const T* A21 = A + (j0 + jb) + j0 * lda;
-    T* A22 = A + (j0 + jb) + (j0 + jb) * lda;
     const int64_t j1 = j0 + jb;
     const int64_t jb1 = j1 < k ? (NB < k - j1 ? NB : k - j1) : 0;
-    if (lookahead && jb1 > 0 && nr > jb1) {
-      // Timing model of the step (ms; B200, FP64): the trailing update on the whole GPU, and the
-      // next panel (m - j1 rows) when its own updates get plenty of SMs or just those of its
-      // leaves.  The panel is a chain of latency-bound launches whose length hardly depends on
-      // its height.
-      static const double model_scale = getenv("LA_B200_LU_MODEL") ? atof(getenv("LA_B200_LU_MODEL")) : 1.1;
-      const double h = (double)(m - j1) / 16384.0;
-      const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / 33.0e9;
-      const double pan_free_ms = 1.5 + 0.3 * h;
-      const double pan_tight_ms = model_scale * (1.6 + 0.9 * h);
+    const bool ahead = lookahead && jb1 > 0 && nr > jb1 && mr > 0;
+    // Timing model of the step (ms; B200, FP64): the trailing update on the whole GPU, and the
+    // next panel (m - j1 rows) when its own updates get plenty of SMs or just those of its
+    // leaves.  The panel is a chain of latency-bound launches whose length hardly depends on
+    // its height.
+    static const double model_scale = getenv("LA_B200_LU_MODEL") ? atof(getenv("LA_B200_LU_MODEL")) : 1.1;
+    static const bool split_env = !(getenv("LA_B200_LU_SPLIT") && atoi(getenv("LA_B200_LU_SPLIT")) == 0);
+    const double h = (double)(m - j1) / 16384.0;
+    const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / 33.0e9;
+    const double pan_free_ms = 1.5 + 0.3 * h;
+    const double pan_tight_ms = model_scale * (1.6 + 0.9 * h);
+    // Steps whose update is shorter than the next panel are bound by the chain
+    //   interchanges -> U12 -> update of the next panel's columns -> next panel,
+    // so those columns go first and everything else (the other columns' interchanges and U12)
+    // runs beside the panel, on the SMs it leaves free.
+    Arena::Mark step_mk = ctx.arena.mark();
+    int* lists = nullptr;
+    static const double split_frac = getenv("LA_B200_LU_SPLIT_FRAC") ? atof(getenv("LA_B200_LU_SPLIT_FRAC")) : 0.6;
+    bool split = ahead && split_env && upd_ms < split_frac * pan_free_ms;
+    if (split) {
+      lists = ctx.alloc<int>(4 * LASWP_CHUNK);
+      split = laswp_lists(ctx, m, j0, j0 + jb, d_ipiv, lists);
+    }
+    T* A12 = A + j0 + (j0 + jb) * lda;
+    if (!split) {
+      if (j0 > 0) laswp_rows<T>(ctx, m, j0, A, lda, j0, j0 + jb, d_ipiv);
+      if (nr <= 0) { ctx.arena.release(step_mk); continue; }
+      laswp_rows<T>(ctx, m, nr, A + (j0 + jb) * lda, lda, j0, j0 + jb, d_ipiv);
+      trsm<T>(ctx, Left, Lower, OpN, Unit, jb, nr, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
+      // rows [j0, j0 + jb) of the whole matrix are final now: later panels interchange rows below
+      if (ctx.on_block_final) ctx.on_block_final(j0, j0 + jb);
+    } else {
+      laswp_apply_lists<T>(ctx, jb1, A + j1 * lda, lda, (int)jb, lists);
+      trsm<T>(ctx, Left, Lower, OpN, Unit, jb, jb1, one<T>(), A + j0 + j0 * lda, lda, A12, lda);
+    }
+    if (mr <= 0) { ctx.arena.release(step_mk); continue; }
+    const T* A21 = A + (j0 + jb) + j0 * lda;
+    T* A22 = A + (j0 + jb) + (j0 + jb) * lda;
+    if (ahead) {
       // the wide leaf needs twice the SMs per row: worth it once the update is small beside the panel
       const bool wide = lu_panel_wide_ok(m - j1) && upd_ms < 0.5 * pan_free_ms;
       const int64_t ctas1 = lu_panel_ctas(ctx, m - j1, sizeof(T), wide);
@@ -397,8 +490,12 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       {
         // late steps: the trailing update is shorter than the panel, so the panel's own
         // GEMMs / TRSMs get the SMs the update does not need to finish in the panel's time
-        const int need = (int)(ctx.sm_count * upd_ms / pan_free_ms) + 1;
-        int spare = ctx.sm_count - (need < 32 ? 32 : need);
+        // (a split step also runs the deferred interchanges and U12 there: bandwidth-bound work
+        // that wants a fair number of SMs)
+        const double beside_ms = upd_ms + (split ? 0.15 + 0.25 * (double)(j0 + nr) / 16384.0 : 0.0);
+        const int need = (int)(ctx.sm_count * beside_ms / pan_free_ms) + 1;
+        const int floor_sms = split ? 64 : 32;
+        int spare = ctx.sm_count - (need < floor_sms ? floor_sms : need);
         if (spare > 116) spare = 116;
         if (spare > side_sms) side_sms = spare;
       }
@@ -417,13 +514,20 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
       // update that outlasts the panel merely keeps a few SMs idle, one that ends early stalls
       // the whole device); the rest of it is launched on all SMs once the panel is done.
       const int64_t rest = nr - jb1;
+      const int keep = ctx.sm_limit;
+      ctx.sm_limit = ctx.sm_count - side_sms;
+      if (split) {
+        if (j0 > 0) laswp_apply_lists<T>(ctx, j0, A, lda, (int)jb, lists);
+        laswp_apply_lists<T>(ctx, rest, A + (j1 + jb1) * lda, lda, (int)jb, lists);
+        trsm<T>(ctx, Left, Lower, OpN, Unit, jb, rest, one<T>(), A + j0 + j0 * lda, lda,
+                A12 + jb1 * lda, lda);
+        if (ctx.on_block_final) ctx.on_block_final(j0, j0 + jb);
+      }
       const double panel_ms = side_sms > ctas1 + 16 ? pan_free_ms : pan_tight_ms;
       const double flop_per_ms = 33.0e9 * (double)(ctx.sm_count - side_sms) / 148.0;
       int64_t c1 = (int64_t)(panel_ms * flop_per_ms / (2.0 * (double)mr * (double)jb));
       c1 = round_up(c1 > 0 ? c1 : 1, (int64_t)128);
       if (c1 + 1024 >= rest) c1 = rest;
-      const int keep = ctx.sm_limit;
-      ctx.sm_limit = ctx.sm_count - side_sms;
       gemm<T>(ctx, OpN, OpN, mr, c1, jb, from_real<T>(-1.0), A21, lda, A12 + jb1 * lda, lda,
               one<T>(), A22 + jb1 * lda, lda);
       ctx.sm_limit = keep;
@@ -437,6 +541,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     } else {
       gemm<T>(ctx, OpN, OpN, mr, nr, jb, from_real<T>(-1.0), A21, lda, A12, lda, one<T>(), A22, lda);
     }
+    ctx.arena.release(step_mk);
   }
 }
 

@@ -125,10 +125,11 @@ def test_host_potrf_moves_only_the_named_triangle(n, lower, product_abi):
     assert np.abs(R - S).max() / np.abs(S).max() < 1e-13
 
 
-@pytest.mark.parametrize("m,n", [(4608, 4608), (8300, 8300), (9000, 5000)])
+@pytest.mark.parametrize("m,n", [(4608, 4608), (8300, 8300), (9000, 5000), (16384, 16384)])
 def test_host_getrf_streams_block_rows_home(m, n, product_abi, oracle_abi):
     # the host-pointer dgetrf_ sends every finished block row home while it is still factoring
-    # (shim_lapack.cu); factors and pivots must equal LAPACK's as for the small cases
+    # (shim_lapack.cu); factors and pivots must equal LAPACK's as for the small cases.  16384 is
+    # the benchmark size: look-ahead on the side stream, standard and wide leaves, split steps
     import ctypes as C
     from linalg_b200 import ffi
     rng = np.random.default_rng(13)
