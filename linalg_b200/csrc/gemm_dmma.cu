@@ -94,10 +94,11 @@ struct GemmParams {
   int64_t ldc;
   int tri;
   int tiles_m, tiles_n, num_tiles;
-  int ksplit;     // > 1: split-K, raw partial sums go to `partial` (one m x n slab per split)
+  int ksplit;     // > 1: split-K: the tiles from `whole_tiles` on are cut into ksplit k-ranges whose
+                  // raw sums go to `partial` (a dense BM x BN tile per (split, tile))
   int kchunk;     // k-blocks per split
+  int whole_tiles;  // leading tiles (in enumeration order) that are not split
   double* partial;
-  int64_t ld_part;
   int zmode;      // 1: rows are interleaved (re, im) parts of a complex matrix (gemm_z.cu)
   int herm_diag;  // zmode only: store 0 in the imaginary part of the diagonal
   int full_enum;  // masked product, few tiles: enumerate all tiles and skip the masked-out ones
@@ -230,6 +231,26 @@ __device__ __forceinline__ void tile_coords(int tri, int t, int tiles_m, int til
   tn = r / gsz;
 }
 
+// Work unit w of a launch: whole tiles first, then (tile, k-range) pieces of the split tiles.
+struct WorkUnit { int t, split, kb0, kb1; bool part; };
+__device__ __forceinline__ WorkUnit decode_unit(const GemmParams& p, int w, int num_tiles, int kblocks) {
+  WorkUnit u;
+  if (w < p.whole_tiles) {
+    u.t = w; u.split = 0; u.kb0 = 0; u.kb1 = kblocks; u.part = false;
+  } else {
+    const int x = w - p.whole_tiles, ns = num_tiles - p.whole_tiles;
+    u.t = p.whole_tiles + x % ns;
+    u.split = x / ns;
+    u.kb0 = u.split * p.kchunk;
+    u.kb1 = min(kblocks, u.kb0 + p.kchunk);
+    u.part = p.ksplit > 1;
+  }
+  return u;
+}
+__host__ __device__ __forceinline__ int work_units(const GemmParams& p) {
+  return p.whole_tiles + (p.num_tiles - p.whole_tiles) * p.ksplit;
+}
+
 // zmode products enumerate all tiles and skip those entirely outside the stored triangle of the
 // COMPLEX matrix (complex row = real row >> 1).
 template <int BN_>
@@ -308,8 +329,10 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const bool beta_zero = p.beta == 0.0, beta_one = p.beta == 1.0 && p.use_red;
     int abuf = 0;
     uint32_t aphase = 0;
-    for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
-      const int t = w % num_tiles, split = w / num_tiles;
+    const int nunits = work_units(p);
+    for (int w = blockIdx.x; w < nunits; w += gridDim.x) {
+      const WorkUnit wu = decode_unit(p, w, num_tiles, kblocks);
+      const int t = wu.t, split = wu.split;
       int tm, tn;
       tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
       if (!tile_active<BN>(p, tm, tn)) continue;
@@ -332,13 +355,12 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         uint32_t v[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + abuf * 256 + h * 128 + jc * 16, v);
         if (col >= p.n) continue;
-        if (p.ksplit > 1) {  // raw partial sums; alpha/beta are applied by the reduction pass
-          double* Pcol = p.partial + ((int64_t)split * p.n + col) * p.ld_part;
+        if (wu.part) {  // raw partial sums; alpha/beta are applied by the reduction pass
+          const int64_t slot = (int64_t)split * (num_tiles - p.whole_tiles) + (t - p.whole_tiles);
+          double* Pcol = p.partial + (slot * BN + (col - (int64_t)tn * BN)) * BM + (cw & 1) * 64 + gid;
 #pragma unroll
-          for (int i = 0; i < 8; i++) {
-            const int64_t row = row_base + i * 8;
-            if (row < p.m) Pcol[row] = __hiloint2double((int)v[2 * i + 1], (int)v[2 * i]);
-          }
+          for (int i = 0; i < 8; i++)
+            Pcol[i * 8] = __hiloint2double((int)v[2 * i + 1], (int)v[2 * i]);
           continue;
         }
         double* Ccol = p.C + col * p.ldc;
@@ -390,13 +412,14 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tma_prefetch_desc(&tmB);
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
-        const int t = w % num_tiles, split = w / num_tiles;
+      const int nunits = work_units(p);
+      for (int w = blockIdx.x; w < nunits; w += gridDim.x) {
+        const WorkUnit wu = decode_unit(p, w, num_tiles, kblocks);
         int tm, tn;
-        tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+        tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, wu.t, p.tiles_m, p.tiles_n, tm, tn);
         if (!tile_active<BN>(p, tm, tn)) continue;
         const int m0 = tm * BM, n0 = tn * BN;
-        const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
+        const int kb0 = wu.kb0, kb1 = wu.kb1;
         for (int kb = kb0; kb < kb1; kb++) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -448,14 +471,15 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // this warp's slot in tensor memory: lane quarter warp % 4, columns (warp / 4) * 128
     const uint32_t tslot = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 128;
 
-    for (int w = blockIdx.x; w < num_tiles * p.ksplit; w += gridDim.x) {
-      const int t = w % num_tiles, split = w / num_tiles;
+    const int nunits = work_units(p);
+    for (int w = blockIdx.x; w < nunits; w += gridDim.x) {
+      const WorkUnit wu = decode_unit(p, w, num_tiles, kblocks);
       int tm, tn;
-      tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, t, p.tiles_m, p.tiles_n, tm, tn);
+      tile_coords((p.zmode || p.full_enum) ? TriFull : p.tri, wu.t, p.tiles_m, p.tiles_n, tm, tn);
       if (!tile_active<BN>(p, tm, tn)) continue;
-      const int kb0 = split * p.kchunk, kb1 = min(kblocks, kb0 + p.kchunk);
+      const int kb0 = wu.kb0, kb1 = wu.kb1;
 
-      if (!beta_zero && p.ksplit == 1) {
+      if (!beta_zero && !wu.part) {
         // pull the C tile into L2 while the main loop runs: thread t covers column t/2, four
         // 128-byte lines of its 128 rows
         const int64_t col = (int64_t)tn * BN + (threadIdx.x >> 1);
@@ -543,18 +567,26 @@ dgemm_dmma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
 }
 
-// C = alpha * sum_s partial_s + beta * C   (split-K reduction)
-__global__ void splitk_reduce_kernel(int64_t m, int64_t n, int ksplit, const double* __restrict__ part,
-                                     int64_t ld_part, double alpha, double beta,
-                                     double* __restrict__ C, int64_t ldc) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= m) return;
-  for (int64_t j = blockIdx.y; j < n; j += gridDim.y) {
-    double s = 0.0;
-    for (int sp = 0; sp < ksplit; sp++) s += part[((int64_t)sp * n + j) * ld_part + i];
-    double v = alpha * s;
-    if (beta != 0.0) v = fma(beta, C[i + j * ldc], v);
-    C[i + j * ldc] = v;
+// C = alpha * sum_s partial_s + beta * C over the split tiles (split-K reduction): one CTA per
+// tile, the sums in a fixed order (results do not depend on how the pieces were scheduled).
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(GemmParams p, int bn) {
+  // blockIdx.x: split tile; blockIdx.y: a group of columns of the tile (two columns per pass)
+  const int ns = p.num_tiles - p.whole_tiles;
+  const int o = blockIdx.x;
+  int tm, tn;
+  tile_coords(TriFull, p.whole_tiles + o, p.tiles_m, p.tiles_n, tm, tn);
+  const int i = threadIdx.x % BM;
+  for (int j = blockIdx.y * 2 + threadIdx.x / BM; j < bn; j += gridDim.y * 2) {
+    const int64_t row = (int64_t)tm * BM + i, col = (int64_t)tn * bn + j;
+    if (row >= p.m || col >= p.n) continue;
+    double sum = 0.0;
+    for (int sp = 0; sp < p.ksplit; sp++)
+      sum += p.partial[(((int64_t)sp * ns + o) * bn + j) * BM + i];
+    double v = p.alpha * sum;
+    double* c = p.C + row + col * p.ldc;
+    if (p.beta != 0.0) v = fma(p.beta, *c, v);
+    *c = v;
   }
 }
 
@@ -566,7 +598,7 @@ void launch(Context& ctx, const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     LA_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr.mark(ctx.device);
   }
-  int tiles = p.num_tiles * p.ksplit;
+  int tiles = work_units(p);
   const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
   int grid = tiles < sms ? tiles : sms;
   kern<<<grid, NTHREADS, SMEM_BYTES, ctx.stream>>>(tmA, tmB, p);
@@ -688,26 +720,67 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
   else if (tri == TriUpper) p.num_tiles = tri_tile_count(p.tiles_n, p.tiles_m);
   else p.num_tiles = p.tiles_m * p.tiles_n;
   if (p.num_tiles <= 0) return true;
-  // split-K for products with few output tiles and a long k (V^H C in QR, Gram matrices)
+  // split-K: for products with few output tiles and a long k (V^H C in QR, Gram matrices) every
+  // tile is cut; for products whose tiles fill the SMs a non-integer number of times (N = 2048:
+  // 256 tiles on 148 SMs) only the tiles of the last, partial wave are, so that its pieces fill
+  // the machine again.  Partial sums are reduced in a fixed order by a second kernel.
   p.ksplit = 1;
   p.kchunk = (int)ceil_div(k, BK);
+  p.whole_tiles = 0;
   p.partial = nullptr;
-  p.ld_part = 0;
   Arena::Mark mk = ctx.arena.mark();
   {
     const int kblocks = (int)ceil_div(k, BK);
     const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
+    static const bool hybrid_on = !(getenv("LA_B200_GEMM_HYBRID") && atoi(getenv("LA_B200_GEMM_HYBRID")) == 0);
     // (contexts that must not allocate — allow_side_stream == false — never split)
-    if (ctx.allow_side_stream && tri == TriFull && !stair && p.num_tiles * 4 <= sms &&
-        kblocks >= 128) {
-      int S = sms / p.num_tiles;
+    const bool may_split = ctx.allow_side_stream && tri == TriFull && !stair && !zmode;
+    int S = 1, whole = 0;
+    if (may_split && p.num_tiles * 4 <= sms && kblocks >= 128) {
+      S = sms / p.num_tiles;
       if (S > kblocks / 32) S = kblocks / 32;
-      if (S >= 2) {
-        p.kchunk = (int)ceil_div(kblocks, S);
-        p.ksplit = (int)ceil_div(kblocks, p.kchunk);
-        p.ld_part = round_up(m, 2);
-        p.partial = ctx.alloc<double>((size_t)p.ksplit * (size_t)n * (size_t)p.ld_part);
+    } else if (may_split && hybrid_on && kblocks >= 64 && p.num_tiles < 24 * sms) {
+      // cost in k-block times of one tile; a work unit costs its k-blocks plus a fixed part
+      // (pipeline fill, accumulator hand-over); units are dealt round-robin to the CTAs
+      static const double ovh = getenv("LA_B200_GEMM_OVH") ? atof(getenv("LA_B200_GEMM_OVH")) : 4.0;
+      static const double red_bw = getenv("LA_B200_GEMM_REDBW") ? atof(getenv("LA_B200_GEMM_REDBW")) : 4.0e6;
+      auto makespan = [&](int wh, int sp) {
+        const int units = wh + (p.num_tiles - wh) * sp;
+        const int G = units < sms ? units : sms;
+        const double piece = (double)ceil_div(kblocks, sp) + ovh;
+        double worst = 0.0;
+        for (int b = 0; b < G; b++) {
+          double t = 0.0;
+          for (int w = b; w < units; w += G) t += w < wh ? (double)kblocks + ovh : piece;
+          if (t > worst) worst = t;
+        }
+        // the reduction pass: partial tiles read once, C read and written
+        if (sp > 1) {
+          const double bytes = (double)(p.num_tiles - wh) * BM * bn * 8.0 * (sp + 2);
+          worst += (8.0 + bytes / red_bw) / (2.18 * bn / 128.0);   // us -> k-block times
+        }
+        return worst;
+      };
+      const double base = makespan(p.num_tiles, 1);
+      double best = base * 0.95;
+      const int wh_full = (p.num_tiles / sms) * sms;
+      const int cand_s[5] = {2, 3, 4, 6, 8};
+      for (int ci = 0; ci < 5; ci++) {
+        if (kblocks / cand_s[ci] < 16) break;
+        for (int pass = 0; pass < 2; pass++) {
+          const int wh = pass == 0 ? wh_full : 0;
+          if (pass == 1 && wh_full == 0) break;
+          if (wh >= p.num_tiles) continue;
+          const double c = makespan(wh, cand_s[ci]);
+          if (c < best) { best = c; S = cand_s[ci]; whole = wh; }
+        }
       }
+    }
+    if (S >= 2) {
+      p.kchunk = (int)ceil_div(kblocks, S);
+      p.ksplit = (int)ceil_div(kblocks, p.kchunk);
+      p.whole_tiles = whole;
+      p.partial = ctx.alloc<double>((size_t)p.ksplit * (size_t)(p.num_tiles - whole) * BM * bn);
     }
   }
   if (bn == 32) {
@@ -727,9 +800,12 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     else launch<false, false, 4>(ctx, tmA, tmB, p);
   }
   if (p.ksplit > 1) {
-    dim3 g((unsigned)ceil_div(m, 128), (unsigned)(n < 1024 ? n : 1024));
-    splitk_reduce_kernel<<<g, 128, 0, ctx.stream>>>(m, n, p.ksplit, p.partial, p.ld_part, alpha,
-                                                    beta, C, ldc);
+    const int ns = p.num_tiles - p.whole_tiles;
+    // enough CTAs to fill the machine whatever the number of split tiles
+    int gy = (int)ceil_div((int64_t)8 * ctx.sm_count, (int64_t)ns);
+    if (gy > bn / 2) gy = bn / 2;
+    if (gy < 1) gy = 1;
+    splitk_reduce_kernel<<<dim3((unsigned)ns, (unsigned)gy), 256, 0, ctx.stream>>>(p, bn);
     LA_CUDA_CHECK(cudaGetLastError());
   }
   ctx.arena.release(mk);
