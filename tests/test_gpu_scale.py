@@ -43,6 +43,33 @@ def test_dgemm_is_repeatable_and_right_at_scale(ta, tb, m, n, k):
             assert torch.equal(C, first), f"launch {rep} differs from launch 0"
 
 
+@pytest.mark.parametrize("ta,tb,m,n,k,alpha,beta", [
+    ("N", "N", 1792, 1792, 1792, 1.0, 0.0),      # 196 tiles on 148 SMs: the last 48 are split along k
+    ("T", "N", 2304, 2304, 2304, -0.5, 1.0),
+    ("N", "T", 3840, 3700, 1500, 2.0, -1.5),     # ragged edge tiles among the split ones
+    ("N", "N", 200, 300, 40000, 1.0, 0.25)])     # few tiles, long k: every tile split
+def test_dgemm_split_tiles_are_repeatable_and_right(ta, tb, m, n, k, alpha, beta):
+    # products whose tiles do not fill the SMs a whole number of times cut the tiles of the last
+    # wave (or all of them) along k and reduce the pieces in a fixed order
+    op = {"N": dev.NO_TRANS, "T": dev.TRANS}
+    ar, ac = (m, k) if ta == "N" else (k, m)
+    br, bc = (k, n) if tb == "N" else (n, k)
+    A, B, C0 = _rand((ac, ar), 31), _rand((bc, br), 32), _rand((n, m), 33)
+    Am = A.T if ta == "N" else A
+    Bm = B.T if tb == "N" else B
+    ref = (beta * C0.T + alpha * (Am @ Bm)).T
+    first = None
+    for rep in range(6):
+        C = C0.clone()
+        dev.gemm(op[ta], op[tb], m, n, k, alpha, A, ar, B, br, beta, C, m)
+        if first is None:
+            first = C
+            assert dev.last_gemm_path() == 1
+            assert (C - ref).abs().max().item() < 2e-14 * k
+        else:
+            assert torch.equal(C, first), f"launch {rep} differs from launch 0"
+
+
 def test_masked_rank_k_update_is_repeatable_and_right_at_scale():
     n, k = 15360, 512
     A, C0 = _rand((k, n), 4), _rand((n, n), 5)
