@@ -734,12 +734,12 @@ bool gemm_dmma_f64_ex(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t 
     const int sms = ctx.sm_limit > 0 && ctx.sm_limit < ctx.sm_count ? ctx.sm_limit : ctx.sm_count;
     static const bool hybrid_on = !(getenv("LA_B200_GEMM_HYBRID") && atoi(getenv("LA_B200_GEMM_HYBRID")) == 0);
     // (contexts that must not allocate — allow_side_stream == false — never split)
-    const bool may_split = ctx.allow_side_stream && tri == TriFull && !stair && !zmode;
+    const bool may_split = ctx.allow_side_stream && tri == TriFull && !stair;
     int S = 1, whole = 0;
     if (may_split && p.num_tiles * 4 <= sms && kblocks >= 128) {
       S = sms / p.num_tiles;
       if (S > kblocks / 32) S = kblocks / 32;
-    } else if (may_split && hybrid_on && kblocks >= 64 && p.num_tiles < 24 * sms) {
+    } else if (may_split && !zmode && hybrid_on && kblocks >= 64 && p.num_tiles < 24 * sms) {
       // cost in k-block times of one tile; a work unit costs its k-blocks plus a fixed part
       // (pipeline fill, accumulator hand-over); units are dealt round-robin to the CTAs
       static const double ovh = getenv("LA_B200_GEMM_OVH") ? atof(getenv("LA_B200_GEMM_OVH")) : 4.0;

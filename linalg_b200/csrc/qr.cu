@@ -31,6 +31,9 @@ struct QrExchange {
   unsigned int pad[63];
   T part[2][QR_MAX_CTAS][QR_MAX_JB];  // per-CTA partial sums s_c
   T rowj[2][QR_MAX_JB];               // row j of the panel
+  // streamed panels that take two reflectors per pass: the sums against column j+1 and row j+1
+  T part2[2][QR_MAX_CTAS][QR_MAX_JB];
+  T rowj2[2][QR_MAX_JB];
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
@@ -227,10 +230,18 @@ __global__ void __launch_bounds__(QR_NT, ((JB <= 8 && !Traits<T>::is_complex) ? 
 qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
                        QrExchange<T>* xch, int64_t rpc, T* __restrict__ Vc, int64_t ldv,
                        T* __restrict__ Tout, int64_t ldt) {
-  __shared__ T s_f[QR_MAX_JB];
+  // Two reflectors per pass where the panel is narrow (JB <= 8): a pass applies reflectors
+  // ja0, ja0+1 and accumulates the sums against BOTH of the next two columns; the second
+  // reflector's sums after the first one has been applied follow algebraically (the reflector
+  // is a rank-1 change of the columns), so a panel of 8 needs 5 passes and grid barriers, not 9.
+  // The derived norm is a difference: when it cancels badly the second reflector is left to a
+  // pass of its own.
+  constexpr bool PAIR = JB <= 8 && !Traits<T>::is_complex;   // (complex: the registers do not allow it)
+  __shared__ T s_f[2][QR_MAX_JB];
   __shared__ T s_tau[QR_MAX_JB];
-  __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
-  __shared__ T s_scale, s_beta;
+  __shared__ T s_red[2][QR_NT / 32][QR_MAX_JB];
+  __shared__ T s_scale[2], s_beta[2];
+  __shared__ int s_napply;
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
   const int G = gridDim.x;
@@ -240,118 +251,201 @@ qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __
   const int kmax = (int)(mp < jb ? mp : jb);
   unsigned target = 0;
 
-  // pass(ja): apply reflector ja (ja >= 0; scale/f/beta in shared memory) to the owned rows and
-  // accumulate, for the next reflector js = ja+1, the sums s_c = sum_{r > js} conj(a(r,js)) a(r,c)
-  for (int ja = -1; ja < kmax; ja++) {
-    const int js = ja + 1;
-    T acc[JB];
+  // pass: apply reflectors ja0 .. ja0+na-1 (scale/f/beta in shared memory) to the owned rows and
+  // accumulate, for js = ja0+na (and js2 = js+1), the sums s_c = sum_{r > js} conj(a(r,js)) a(r,c)
+  // (s2_c = sum_{r > js} conj(a(r,js2)) a(r,c)); rows js and js2 are published as they are.
+  int ja0 = 0, na = 0, pass = 0;
+  while (true) {
+    const int js = ja0 + na;
+    const int js2 = js + 1;
+    const bool two = PAIR && js2 < kmax;
+    T acc[JB], acc2[PAIR ? JB : 1];
 #pragma unroll
     for (int c = 0; c < JB; c++) acc[c] = zero<T>();
-    const T scale = ja >= 0 ? s_scale : zero<T>();
-    const int c_lo = ja >= 0 ? ja : 0;
+#pragma unroll
+    for (int c = 0; c < (PAIR ? JB : 1); c++) acc2[c] = zero<T>();
+    T scale[2], betav[2];
+    scale[0] = na > 0 ? s_scale[0] : zero<T>();
+    scale[1] = na > 1 ? s_scale[1] : zero<T>();
+    betav[0] = na > 0 ? s_beta[0] : zero<T>();
+    betav[1] = na > 1 ? s_beta[1] : zero<T>();
     for (int64_t r0 = tid; r0 < nr; r0 += (int64_t)U * QR_NT) {
       T a[U][JB];
       bool live[U];
 #pragma unroll
       for (int u = 0; u < U; u++) {
         const int64_t r = r0 + (int64_t)u * QR_NT;
-        live[u] = r < nr && rs + r >= ja;         // rows above ja are finished rows of R
+        live[u] = r < nr && rs + r >= ja0;        // rows above ja0 are finished rows of R
 #pragma unroll
         for (int c = 0; c < JB; c++)
-          a[u][c] = (live[u] && c >= c_lo && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
+          a[u][c] = (live[u] && c >= ja0 && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
       }
 #pragma unroll
       for (int u = 0; u < U; u++) {
         if (!live[u]) continue;
         const int64_t r = r0 + (int64_t)u * QR_NT;
         const int64_t gr = rs + r;
-        if (ja >= 0) {
-          if (gr == ja) {                           // the reflector's own row: v = 1
+#pragma unroll
+        for (int i = 0; i < (PAIR ? 2 : 1); i++) {
+          if (i >= na) continue;
+          const int q = ja0 + i;
+          if (gr == q) {                            // the reflector's own row: v = 1
 #pragma unroll
             for (int c = 0; c < JB; c++) {
-              if (c == ja) a[u][c] = s_beta;
-              else if (c > ja && c < jb) a[u][c] = sub(a[u][c], s_f[c]);
+              if (c == q) a[u][c] = betav[i];
+              else if (c > q && c < jb) a[u][c] = sub(a[u][c], s_f[i][c]);
             }
-          } else {                                  // gr > ja: v = x * scale
+          } else if (gr > q) {                      // v = x * scale
             T v = zero<T>();
 #pragma unroll
             for (int c = 0; c < JB; c++)
-              if (c == ja) { v = mul(a[u][c], scale); a[u][c] = v; }
+              if (c == q) { v = mul(a[u][c], scale[i]); a[u][c] = v; }
 #pragma unroll
             for (int c = 0; c < JB; c++)
-              if (c > ja && c < jb) a[u][c] = fnma_(v, s_f[c], a[u][c]);
+              if (c > q && c < jb) a[u][c] = fnma_(v, s_f[i][c], a[u][c]);
           }
+        }
+        if (na > 0) {
 #pragma unroll
           for (int c = 0; c < JB; c++)
-            if (c >= ja && c < jb) base[(int64_t)c * lda + r] = a[u][c];
+            if (c >= ja0 && c < jb) base[(int64_t)c * lda + r] = a[u][c];
         }
         if (js < kmax) {
           if (gr == js) {                           // next reflector's own row: publish it
 #pragma unroll
             for (int c = 0; c < JB; c++)
-              if (c >= js && c < jb) st_cg<T>(&xch->rowj[js & 1][c], a[u][c]);
+              if (c >= js && c < jb) st_cg<T>(&xch->rowj[pass & 1][c], a[u][c]);
           } else if (gr > js) {
-            T x = zero<T>();
+            T x = zero<T>(), x2 = zero<T>();
 #pragma unroll
-            for (int c = 0; c < JB; c++)
+            for (int c = 0; c < JB; c++) {
               if (c == js) x = conj_(a[u][c]);
+              if (PAIR && c == js2) x2 = conj_(a[u][c]);
+            }
 #pragma unroll
             for (int c = 0; c < JB; c++)
               if (c >= js && c < jb) acc[c] = fma_(x, a[u][c], acc[c]);
+            if (PAIR && two) {
+#pragma unroll
+              for (int c = 0; c < JB; c++)
+                if (c >= js2 && c < jb) acc2[PAIR ? c : 0] = fma_(x2, a[u][c], acc2[PAIR ? c : 0]);
+              if (gr == js2) {                      // the row of the reflector after next
+#pragma unroll
+                for (int c = 0; c < JB; c++)
+                  if (c >= js && c < jb) st_cg<T>(&xch->rowj2[pass & 1][c], a[u][c]);
+              }
+            }
           }
         }
       }
     }
     if (js >= kmax) break;
     // ---- block reduction of the partial sums, publication, grid barrier, global reduction
-    const int par = js & 1;
+    const int par = pass & 1;
 #pragma unroll
     for (int c = 0; c < JB; c++) {
-      const T s = warp_sum<T>(acc[c]);
-      if (lane == 0) s_red[warp][c] = s;
+      const T sa = warp_sum<T>(acc[c]);
+      if (lane == 0) s_red[0][warp][c] = sa;
+      if (PAIR) {
+        const T sb = warp_sum<T>(acc2[PAIR ? c : 0]);
+        if (lane == 0) s_red[1][warp][c] = sb;
+      }
     }
     __syncthreads();
     if (tid < jb && tid >= js) {
-      T s = zero<T>();
-      for (int w = 0; w < QR_NT / 32; w++) s = add(s, s_red[w][tid]);
-      st_cg<T>(&xch->part[par][blockIdx.x][tid], s);
+      T sa = zero<T>(), sb = zero<T>();
+      for (int w = 0; w < QR_NT / 32; w++) {
+        sa = add(sa, s_red[0][w][tid]);
+        if (PAIR) sb = add(sb, s_red[1][w][tid]);
+      }
+      st_cg<T>(&xch->part[par][blockIdx.x][tid], sa);
+      if (PAIR && two) st_cg<T>(&xch->part2[par][blockIdx.x][tid], sb);
     }
     target += (unsigned)G;
     grid_barrier(&xch->barrier, target);
     {
       const int c = tid & 31, grp = tid >> 5;
-      T s = zero<T>();
+      T sa = zero<T>(), sb = zero<T>();
       if (c >= js && c < jb)
-        for (int g = grp; g < G; g += QR_NT / 32) s = add(s, ld_cg<T>(&xch->part[par][g][c]));
-      s_red[grp][c] = s;
+        for (int g = grp; g < G; g += QR_NT / 32) {
+          sa = add(sa, ld_cg<T>(&xch->part[par][g][c]));
+          if (PAIR && two) sb = add(sb, ld_cg<T>(&xch->part2[par][g][c]));
+        }
+      s_red[0][grp][c] = sa;
+      if (PAIR) s_red[1][grp][c] = sb;
     }
     __syncthreads();
     if (tid < 32) {
       const int c = tid;
-      T s = zero<T>();
-      if (c >= js && c < jb)
-        for (int g = 0; g < QR_NT / 32; g++) s = add(s, s_red[g][c]);
-      T rj = (c >= js && c < jb) ? ld_cg<T>(&xch->rowj[par][c]) : zero<T>();
-      T alpha, sj;
-      if constexpr (Traits<T>::is_complex) {
-        alpha.x = __shfl_sync(0xffffffffu, rj.x, js); alpha.y = __shfl_sync(0xffffffffu, rj.y, js);
-        sj.x = __shfl_sync(0xffffffffu, s.x, js); sj.y = 0.0;
-      } else {
-        alpha = __shfl_sync(0xffffffffu, rj, js);
-        sj = __shfl_sync(0xffffffffu, s, js);
+      const bool in = c >= js && c < jb;
+      T s1 = zero<T>(), s2 = zero<T>();
+      if (in)
+        for (int g = 0; g < QR_NT / 32; g++) {
+          s1 = add(s1, s_red[0][g][c]);
+          if (PAIR) s2 = add(s2, s_red[1][g][c]);
+        }
+      const T r1 = in ? ld_cg<T>(&xch->rowj[par][c]) : zero<T>();
+      auto bcast = [](T v, int src) {
+        T o;
+        if constexpr (Traits<T>::is_complex) {
+          o.x = __shfl_sync(0xffffffffu, v.x, src); o.y = __shfl_sync(0xffffffffu, v.y, src);
+        } else {
+          o = __shfl_sync(0xffffffffu, v, src);
+        }
+        return o;
+      };
+      const T alpha1 = bcast(r1, js);
+      const double sigma1 = (double)real_(bcast(s1, js));
+      T beta1, tau1, sc1;
+      householder<T>(alpha1, sigma1, beta1, tau1, sc1);
+      const T w1 = fma_(conj_(sc1), s1, r1);        // w_c = a(js,c) + conj(scale) * s_c
+      const T f1 = mul(conj_(tau1), w1);            // f_c = conj(tau) * w_c
+      s_f[0][c] = f1;
+      int napply = 1;
+      if (PAIR && two) {
+        // column sums after reflector js, over the rows > js:
+        //   P_c = S2_c - conj(f_js2) conj(sc) S1_c - f_c sc conj(S1_js2) + conj(f_js2) f_c |sc|^2 S1_js
+        // row js2 after reflector js: r2'_c = r2_c - (r2_js sc) f_c; its own term leaves the sums.
+        const T r2 = in ? ld_cg<T>(&xch->rowj2[par][c]) : zero<T>();
+        const T f1_2 = bcast(f1, js2);
+        const T s1_2 = bcast(s1, js2);
+        const T v1_2 = mul(bcast(r2, js), sc1);
+        T pc = s2;
+        pc = sub(pc, mul(mul(conj_(f1_2), conj_(sc1)), s1));
+        pc = sub(pc, mul(mul(f1, sc1), conj_(s1_2)));
+        const double sc_abs2 = (double)real_(mul(conj_(sc1), sc1));
+        pc = add(pc, mul(mul(conj_(f1_2), f1), from_real<T>(sc_abs2 * sigma1)));
+        const T r2p = fnma_(v1_2, f1, r2);
+        const T alpha2 = bcast(r2p, js2);
+        const T s2p = sub(pc, mul(conj_(alpha2), r2p));
+        const double sigma2 = (double)real_(bcast(s2p, js2));
+        const double orig2 = (double)real_(bcast(s2, js2));
+        if (sigma2 >= 0.0625 * orig2 && sigma2 == sigma2) {
+          T beta2, tau2, sc2;
+          householder<T>(alpha2, sigma2, beta2, tau2, sc2);
+          const T w2 = fma_(conj_(sc2), s2p, r2p);
+          s_f[1][c] = mul(conj_(tau2), w2);
+          napply = 2;
+          if (c == js2) {
+            s_scale[1] = sc2;
+            s_beta[1] = beta2;
+            s_tau[js2] = tau2;
+            if (blockIdx.x == 0) tau[js2] = tau2;
+          }
+        }
       }
-      T beta, tj, sc;
-      householder<T>(alpha, (double)real_(sj), beta, tj, sc);
-      const T w = fma_(conj_(sc), s, rj);        // w_c = a(js,c) + conj(scale) * s_c
-      s_f[c] = mul(conj_(tj), w);                // f_c = conj(tau) * w_c
       if (c == js) {
-        s_scale = sc;
-        s_beta = beta;
-        s_tau[js] = tj;
-        if (blockIdx.x == 0) tau[js] = tj;
+        s_scale[0] = sc1;
+        s_beta[0] = beta1;
+        s_tau[js] = tau1;
+        if (blockIdx.x == 0) tau[js] = tau1;
+        s_napply = napply;
       }
     }
     __syncthreads();
+    ja0 = js;
+    na = s_napply;
+    pass++;
   }
   // ---- optional epilogue (8-column panels): one more pass over the finished panel writes the
   // clean copy of the reflectors (unit diagonal, zeros above) and accumulates G = V^H V; after a
@@ -386,19 +480,19 @@ qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __
       // block reduction through s_red (8 warps x 32 slots; NG <= 36 needs two rounds)
       // (partial sums go to the parity half the last column pass did not use: every CTA has left
       // that half behind before any CTA can be here)
-      T* gp = &xch->part[kmax & 1][0][0];
+      T* gp = &xch->part[pass & 1][0][0];
       for (int base_i = 0; base_i < NG; base_i += 32) {
 #pragma unroll
         for (int i = 0; i < NG; i++) {
           if (i >= base_i && i < base_i + 32) {
             const T sgm = warp_sum<T>(g[i]);
-            if (lane == 0) s_red[warp][i - base_i] = sgm;
+            if (lane == 0) s_red[0][warp][i - base_i] = sgm;
           }
         }
         __syncthreads();
         if (tid < 32 && base_i + tid < NG) {
           T sgm = zero<T>();
-          for (int w = 0; w < QR_NT / 32; w++) sgm = add(sgm, s_red[w][tid]);
+          for (int w = 0; w < QR_NT / 32; w++) sgm = add(sgm, s_red[0][w][tid]);
           st_cg<T>(&gp[(int64_t)blockIdx.x * NG + base_i + tid], sgm);
         }
         __syncthreads();
