@@ -216,6 +216,95 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
   }
 }
 
+// One pass of the streaming panel kernel over the rows of a CTA (see qr_panel_stream_kernel):
+// apply reflectors ja0 .. ja0+na-1, store, accumulate the sums against columns js = ja0+na and
+// js+1, publish rows js and js+1.  With JA0 >= 0 the pass is compiled for that (ja0, na): every
+// column index is then a constant and the selects / predicates of the generic form (which cost
+// several times the useful instructions) fold away.
+template <typename T, int JB, int U, bool PAIR, int JA0, int NA>
+__device__ __forceinline__ void qr_stream_sweep(
+    T* __restrict__ base, int64_t lda, int64_t nr, int64_t rs, int jb, int kmax, int tid, int ja0_rt,
+    int na_rt, const T (*s_f)[QR_MAX_JB], const T (&scale)[2], const T (&betav)[2],
+    T* __restrict__ rowj_out, T* __restrict__ rowj2_out, T (&acc)[JB], T (&acc2)[PAIR ? JB : 1]) {
+  const int ja0 = JA0 >= 0 ? JA0 : ja0_rt;
+  const int na = JA0 >= 0 ? NA : na_rt;
+  const int js = ja0 + na;
+  const int js2 = js + 1;
+  const bool two = PAIR && js2 < kmax;
+  for (int64_t r0 = tid; r0 < nr; r0 += (int64_t)U * QR_NT) {
+    T a[U][JB];
+    bool live[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t r = r0 + (int64_t)u * QR_NT;
+      live[u] = r < nr && rs + r >= ja0;        // rows above ja0 are finished rows of R
+#pragma unroll
+      for (int c = 0; c < JB; c++)
+        a[u][c] = (live[u] && c >= ja0 && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (!live[u]) continue;
+      const int64_t r = r0 + (int64_t)u * QR_NT;
+      const int64_t gr = rs + r;
+#pragma unroll
+      for (int i = 0; i < (PAIR ? 2 : 1); i++) {
+        if (i >= na) continue;
+        const int q = ja0 + i;
+        if (gr == q) {                            // the reflector's own row: v = 1
+#pragma unroll
+          for (int c = 0; c < JB; c++) {
+            const T fc = s_f[i][c];
+            if (c == q) a[u][c] = betav[i];
+            else if (c > q && c < jb) a[u][c] = sub(a[u][c], fc);
+          }
+        } else if (gr > q) {                      // v = x * scale
+          T v = zero<T>();
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c == q) { v = mul(a[u][c], scale[i]); a[u][c] = v; }
+#pragma unroll
+          for (int c = 0; c < JB; c++) {
+            if (c > q && c < jb) a[u][c] = fnma_(v, s_f[i][c], a[u][c]);
+          }
+        }
+      }
+      if (na > 0) {
+#pragma unroll
+        for (int c = 0; c < JB; c++)
+          if (c >= ja0 && c < jb) base[(int64_t)c * lda + r] = a[u][c];
+      }
+      if (js < kmax) {
+        if (gr == js) {                           // next reflector's own row: publish it
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c >= js && c < jb) st_cg<T>(&rowj_out[c], a[u][c]);
+        } else if (gr > js) {
+          T x = zero<T>(), x2 = zero<T>();
+#pragma unroll
+          for (int c = 0; c < JB; c++) {
+            if (c == js) x = conj_(a[u][c]);
+            if (PAIR && c == js2) x2 = conj_(a[u][c]);
+          }
+#pragma unroll
+          for (int c = 0; c < JB; c++)
+            if (c >= js && c < jb) acc[c] = fma_(x, a[u][c], acc[c]);
+          if (PAIR && two) {
+#pragma unroll
+            for (int c = 0; c < JB; c++)
+              if (c >= js2 && c < jb) acc2[PAIR ? c : 0] = fma_(x2, a[u][c], acc2[PAIR ? c : 0]);
+            if (gr == js2) {                      // the row of the reflector after next
+#pragma unroll
+              for (int c = 0; c < JB; c++)
+                if (c >= js && c < jb) st_cg<T>(&rowj2_out[c], a[u][c]);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Tall panels (the row slice of a CTA does not fit shared memory, e.g. 2^20 x 8): streaming
 // variant.  Same mathematics and the same one-grid-barrier-per-column exchange, but the
@@ -269,75 +358,30 @@ qr_panel_stream_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __
     scale[1] = na > 1 ? s_scale[1] : zero<T>();
     betav[0] = na > 0 ? s_beta[0] : zero<T>();
     betav[1] = na > 1 ? s_beta[1] : zero<T>();
-    for (int64_t r0 = tid; r0 < nr; r0 += (int64_t)U * QR_NT) {
-      T a[U][JB];
-      bool live[U];
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        const int64_t r = r0 + (int64_t)u * QR_NT;
-        live[u] = r < nr && rs + r >= ja0;        // rows above ja0 are finished rows of R
-#pragma unroll
-        for (int c = 0; c < JB; c++)
-          a[u][c] = (live[u] && c >= ja0 && c < jb) ? base[(int64_t)c * lda + r] : zero<T>();
+    T* rowj_out = &xch->rowj[pass & 1][0];
+    T* rowj2_out = &xch->rowj2[pass & 1][0];
+    if constexpr (JB <= 8) {
+      // one compiled pass per (first reflector, number of reflectors)
+#define LA_QR_SWEEP(J, N)                                                                         \
+  case (J) * 3 + (N):                                                                             \
+    qr_stream_sweep<T, JB, U, PAIR, (J) + (N) <= JB ? (J) : 0, (J) + (N) <= JB ? (N) : 0>(         \
+        base, lda, nr, rs, jb, kmax, tid, ja0, na, s_f, scale, betav, rowj_out, rowj2_out, acc,    \
+        acc2);                                                                                    \
+    break;
+      switch (ja0 * 3 + na) {
+        LA_QR_SWEEP(0, 0)
+        LA_QR_SWEEP(0, 1) LA_QR_SWEEP(1, 1) LA_QR_SWEEP(2, 1) LA_QR_SWEEP(3, 1)
+        LA_QR_SWEEP(4, 1) LA_QR_SWEEP(5, 1) LA_QR_SWEEP(6, 1) LA_QR_SWEEP(7, 1)
+        LA_QR_SWEEP(0, 2) LA_QR_SWEEP(1, 2) LA_QR_SWEEP(2, 2) LA_QR_SWEEP(3, 2)
+        LA_QR_SWEEP(4, 2) LA_QR_SWEEP(5, 2) LA_QR_SWEEP(6, 2)
+        default:
+          qr_stream_sweep<T, JB, U, PAIR, -1, 0>(base, lda, nr, rs, jb, kmax, tid, ja0, na, s_f,
+                                                 scale, betav, rowj_out, rowj2_out, acc, acc2);
       }
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        if (!live[u]) continue;
-        const int64_t r = r0 + (int64_t)u * QR_NT;
-        const int64_t gr = rs + r;
-#pragma unroll
-        for (int i = 0; i < (PAIR ? 2 : 1); i++) {
-          if (i >= na) continue;
-          const int q = ja0 + i;
-          if (gr == q) {                            // the reflector's own row: v = 1
-#pragma unroll
-            for (int c = 0; c < JB; c++) {
-              if (c == q) a[u][c] = betav[i];
-              else if (c > q && c < jb) a[u][c] = sub(a[u][c], s_f[i][c]);
-            }
-          } else if (gr > q) {                      // v = x * scale
-            T v = zero<T>();
-#pragma unroll
-            for (int c = 0; c < JB; c++)
-              if (c == q) { v = mul(a[u][c], scale[i]); a[u][c] = v; }
-#pragma unroll
-            for (int c = 0; c < JB; c++)
-              if (c > q && c < jb) a[u][c] = fnma_(v, s_f[i][c], a[u][c]);
-          }
-        }
-        if (na > 0) {
-#pragma unroll
-          for (int c = 0; c < JB; c++)
-            if (c >= ja0 && c < jb) base[(int64_t)c * lda + r] = a[u][c];
-        }
-        if (js < kmax) {
-          if (gr == js) {                           // next reflector's own row: publish it
-#pragma unroll
-            for (int c = 0; c < JB; c++)
-              if (c >= js && c < jb) st_cg<T>(&xch->rowj[pass & 1][c], a[u][c]);
-          } else if (gr > js) {
-            T x = zero<T>(), x2 = zero<T>();
-#pragma unroll
-            for (int c = 0; c < JB; c++) {
-              if (c == js) x = conj_(a[u][c]);
-              if (PAIR && c == js2) x2 = conj_(a[u][c]);
-            }
-#pragma unroll
-            for (int c = 0; c < JB; c++)
-              if (c >= js && c < jb) acc[c] = fma_(x, a[u][c], acc[c]);
-            if (PAIR && two) {
-#pragma unroll
-              for (int c = 0; c < JB; c++)
-                if (c >= js2 && c < jb) acc2[PAIR ? c : 0] = fma_(x2, a[u][c], acc2[PAIR ? c : 0]);
-              if (gr == js2) {                      // the row of the reflector after next
-#pragma unroll
-                for (int c = 0; c < JB; c++)
-                  if (c >= js && c < jb) st_cg<T>(&xch->rowj2[pass & 1][c], a[u][c]);
-              }
-            }
-          }
-        }
-      }
+#undef LA_QR_SWEEP
+    } else {
+      qr_stream_sweep<T, JB, U, PAIR, -1, 0>(base, lda, nr, rs, jb, kmax, tid, ja0, na, s_f, scale,
+                                             betav, rowj_out, rowj2_out, acc, acc2);
     }
     if (js >= kmax) break;
     // ---- block reduction of the partial sums, publication, grid barrier, global reduction
