@@ -376,11 +376,19 @@ tall_update_kernel(int64_t m, int h, int nc, const T* __restrict__ V, int64_t ld
         cv[u] = c0 + u < nc ? C[row + (int64_t)(c0 + u) * ldc] : zero<T>();
         acc[u] = zero<T>();
       }
+      // (16 bytes of Z per shared-memory load: with one load per multiply-add the kernel is bound
+      // by the load pipe, at a third of the memory bandwidth for 32 reflectors)
+      constexpr int EPV = 16 / (int)sizeof(T);
+      struct alignas(16) ZV { T e[EPV]; };
 #pragma unroll
-      for (int j = 0; j < H; j++) {
+      for (int j = 0; j < H; j += EPV) {
 #pragma unroll
         for (int u = 0; u < 4; u++)
-          if (c0 + u < nc) acc[u] = fma_(v[j], zs[(c0 + u) * H + j], acc[u]);
+          if (c0 + u < nc) {
+            const ZV z = *reinterpret_cast<const ZV*>(&zs[(c0 + u) * H + j]);
+#pragma unroll
+            for (int i = 0; i < EPV; i++) acc[u] = fma_(v[j + i], z.e[i], acc[u]);
+          }
       }
 #pragma unroll
       for (int u = 0; u < 4; u++)
