@@ -62,13 +62,13 @@ DIST_COMM_CTAS = int(os.environ.get("LA_DIST_COMM_CTAS", "8"))
 # kernel time shares of one factorisation at N = 16384 from the ncu launch lists (serialised,
 # cold caches: shares, not absolutes); refreshed whenever the kernels change
 FACTOR_PROFILE = {
-    "dgetrf": {"source": "profiles/r2c_dgetrf16384_launches.csv",
-               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 125.5,
-                              "lu_panel_kernel (32-column leaves)": 44.6, "laswp_*": 17.1,
-                              "trsm_dmma_kernel": 10.9}},
-    "dpotrf": {"source": "profiles/r2c_dpotrf16384_launches.csv",
-               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 105.3,
-                              "potf2_kernel (128-column leaves)": 26.9, "trsm_dmma_kernel": 12.0}},
+    "dgetrf": {"source": "profiles/r2g_dgetrf16384_launches.csv",
+               "kernels_ms": {"dgemm_dmma_kernel (trailing + in-panel updates)": 119.9,
+                              "lu_panel_kernel (32- and 64-column leaves)": 35.3, "laswp_*": 13.3,
+                              "trsm_dmma_kernel": 12.3}},
+    "dpotrf": {"source": "profiles/r2g_dpotrf16384_launches.csv",
+               "kernels_ms": {"dgemm_dmma_kernel (HERK / block-column updates)": 53.8,
+                              "potf2_kernel (128-column leaves)": 16.9, "trsm_dmma_kernel": 6.3}},
 }
 
 
