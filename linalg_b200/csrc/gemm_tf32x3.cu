@@ -93,6 +93,97 @@ __global__ void split_kernel(int kcontig, int64_t rows, int64_t k, float scale,
   }
 }
 
+// The same with 64 x 64 tiles and 16-byte accesses on both sides (operands whose base and leading
+// dimension are multiples of four floats): the packing pass is pure memory traffic (2 reads +
+// 4 writes of the operands), 9 % of an N = 16384 product with the 4-byte form above.
+__device__ __forceinline__ void split4(const float4 x, float4& h, float4& l) {
+  h.x = __uint_as_float(to_tf32(x.x)); l.x = __uint_as_float(to_tf32(x.x - h.x));
+  h.y = __uint_as_float(to_tf32(x.y)); l.y = __uint_as_float(to_tf32(x.y - h.y));
+  h.z = __uint_as_float(to_tf32(x.z)); l.z = __uint_as_float(to_tf32(x.z - h.z));
+  h.w = __uint_as_float(to_tf32(x.w)); l.w = __uint_as_float(to_tf32(x.w - h.w));
+}
+__global__ void __launch_bounds__(256)
+split_vec_kernel(int kcontig, int64_t rows, int64_t k, const float* __restrict__ X, int64_t ldx,
+                 float* __restrict__ hi, float* __restrict__ lo, int64_t ldo) {
+  __shared__ float tile[64][65];
+  const int t = threadIdx.x, q4 = (t & 15) * 4, sub = t >> 4;
+  const int64_t nbr = ceil_div(rows, 64), nbk = ceil_div(k, 64);
+  for (int64_t blk = blockIdx.x; blk < nbr * nbk; blk += gridDim.x) {
+    const int64_t r0 = (blk % nbr) * 64, c0 = (blk / nbr) * 64;
+    if (kcontig) {  // element (r, c) stored at X[c + r * ldx]: straight through
+#pragma unroll
+      for (int p = 0; p < 4; p++) {
+        const int64_t r = r0 + p * 16 + sub, c = c0 + q4;
+        if (r >= rows || c >= k) continue;
+        if (c + 3 < k) {
+          float4 h, l;
+          split4(*reinterpret_cast<const float4*>(&X[c + r * ldx]), h, l);
+          *reinterpret_cast<float4*>(&hi[r * ldo + c]) = h;
+          *reinterpret_cast<float4*>(&lo[r * ldo + c]) = l;
+        } else {
+          for (int64_t cc = c; cc < k; cc++) {
+            const float x = X[cc + r * ldx];
+            const float h = __uint_as_float(to_tf32(x));
+            hi[r * ldo + cc] = h;
+            lo[r * ldo + cc] = __uint_as_float(to_tf32(x - h));
+          }
+        }
+      }
+    } else {        // element (r, c) stored at X[r + c * ldx]: transposed through shared memory
+#pragma unroll
+      for (int p = 0; p < 4; p++) {
+        const int cc = p * 16 + sub;
+        const int64_t c = c0 + cc, r = r0 + q4;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < k && r < rows) {
+          if (r + 3 < rows) {
+            x = *reinterpret_cast<const float4*>(&X[r + c * ldx]);
+          } else {
+            x.x = X[r + c * ldx];
+            if (r + 1 < rows) x.y = X[r + 1 + c * ldx];
+            if (r + 2 < rows) x.z = X[r + 2 + c * ldx];
+          }
+        }
+        tile[cc][q4] = x.x; tile[cc][q4 + 1] = x.y; tile[cc][q4 + 2] = x.z; tile[cc][q4 + 3] = x.w;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int p = 0; p < 4; p++) {
+        const int rr = p * 16 + sub;
+        const int64_t r = r0 + rr, c = c0 + q4;
+        if (r >= rows || c >= k) continue;
+        const float4 x = make_float4(tile[q4][rr], tile[q4 + 1][rr], tile[q4 + 2][rr], tile[q4 + 3][rr]);
+        float4 h, l;
+        split4(x, h, l);
+        if (c + 3 < k) {
+          *reinterpret_cast<float4*>(&hi[r * ldo + c]) = h;
+          *reinterpret_cast<float4*>(&lo[r * ldo + c]) = l;
+        } else {
+          const float hv[4] = {h.x, h.y, h.z, h.w}, lv[4] = {l.x, l.y, l.z, l.w};
+          for (int i = 0; c + i < k; i++) { hi[r * ldo + c + i] = hv[i]; lo[r * ldo + c + i] = lv[i]; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// hi/lo packing of one operand (see split_kernel)
+static void launch_split(Context& ctx, bool kcontig, int64_t rows, int64_t k, const float* X,
+                         int64_t ldx, float* hi, float* lo, int64_t ldo) {
+  static const bool old_form = getenv("LA_B200_SGEMM_PACK4B") != nullptr;
+  if (!old_form && ((uintptr_t)X & 15) == 0 && ldx % 4 == 0 && ldo % 4 == 0) {
+    const int64_t nblk = ceil_div(rows, 64) * ceil_div(k, 64);
+    const int64_t cap = (int64_t)ctx.sm_count * 16;
+    split_vec_kernel<<<(unsigned)(nblk < cap ? nblk : cap), 256, 0, ctx.stream>>>(
+        kcontig ? 1 : 0, rows, k, X, ldx, hi, lo, ldo);
+  } else {
+    const int64_t nblk = ceil_div(rows, 32) * ceil_div(k, 32);
+    const unsigned g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
+    split_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>(kcontig ? 1 : 0, rows, k, 1.0f, X, ldx, hi, lo, ldo);
+  }
+}
+
 // ---- tcgen05 helpers -------------------------------------------------------------------------
 template <int SWZ_BYTES>
 __device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t smem_addr) {
@@ -439,13 +530,9 @@ bool gemm_tf32x3(Context& ctx, Op ta, Op tb, int64_t m, int64_t n, int64_t k, fl
   float* Blo = ctx.alloc<float>((size_t)ldk * (size_t)n);
   {
     // op(A)(r, c): ta == N -> A[r + c*lda] (r contiguous); else A[c + r*lda] (k contiguous)
-    int64_t nblk = ceil_div(m, 32) * ceil_div(k, 32);
-    unsigned g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
-    split_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>(ta != OpN, m, k, 1.0f, A, lda, Ahi, Alo, ldk);
+    launch_split(ctx, ta != OpN, m, k, A, lda, Ahi, Alo, ldk);
     // op(B)(c, r) with r the column: tb == N -> B[c + r*ldb] (k contiguous); else B[r + c*ldb]
-    nblk = ceil_div(n, 32) * ceil_div(k, 32);
-    g = (unsigned)(nblk < 65535 * 8 ? nblk : 65535 * 8);
-    split_kernel<<<g, dim3(32, 8), 0, ctx.stream>>>(tb == OpN, n, k, 1.0f, B, ldb, Bhi, Blo, ldk);
+    launch_split(ctx, tb == OpN, n, k, B, ldb, Bhi, Blo, ldk);
     LA_CUDA_CHECK(cudaGetLastError());
   }
   // pairs of CTAs sharing B tiles: full products with at least two tile rows and enough tiles to
