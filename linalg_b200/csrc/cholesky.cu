@@ -272,6 +272,31 @@ static void potrf_twolevel(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda
 //            rest of the trailing matrix -= P' P'^H      (HERK on the remaining SMs, meanwhile)
 // The serial part of the algorithm (n / 128 leaf launches) is thereby hidden behind the tensor
 // core work as long as the trailing update of a step outlasts one diagonal block.
+#ifdef LA_CHOL_TIMELINE
+}  // namespace la
+#include <vector>
+namespace la {
+static std::vector<cudaEvent_t> g_ctl;   // per step: start, after TRSM, after next-column GEMM, side done, HERK done
+static void ctl_mark(cudaStream_t s) {
+  cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s); g_ctl.push_back(e);
+}
+extern "C" void la_b200_debug_chol_timeline() {
+  cudaDeviceSynchronize();
+  for (size_t i = 0; i + 4 < g_ctl.size(); i += 5) {
+    float a, b, c, d;
+    cudaEventElapsedTime(&a, g_ctl[i], g_ctl[i + 1]);
+    cudaEventElapsedTime(&b, g_ctl[i + 1], g_ctl[i + 2]);
+    cudaEventElapsedTime(&c, g_ctl[i + 2], g_ctl[i + 3]);
+    cudaEventElapsedTime(&d, g_ctl[i + 2], g_ctl[i + 4]);
+    printf("step %2zu: trsm %.2f | next-column gemm %.2f | after hand-over: diagonal block +%.2f, herk +%.2f ms\n", i / 5, a, b, c, d);
+  }
+  g_ctl.clear();
+}
+#define CTL(s) ctl_mark(s)
+#else
+#define CTL(s) (void)0
+#endif
+
 int64_t potrf_block_width(int64_t n) {
   static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
   static const int nbo_env = getenv("LA_B200_CHOL_NBO") ? atoi(getenv("LA_B200_CHOL_NBO")) : 0;
@@ -318,9 +343,11 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
     const int64_t K1 = K0 + kb;
     const int64_t kb2 = NBO < r2 ? NBO : r2;
     const int64_t r3 = r2 - kb2;  // order of the trailing matrix beyond the next block column
+    CTL(ctx.stream);
     if (L) {
       trsm<T>(ctx, Right, Lower, OpC, NonUnit, r2, kb, one<T>(), at(K0, K0), lda, at(K1, K0), lda);
       if (ctx.on_block_final) ctx.on_block_final(K0, K1);
+      CTL(ctx.stream);
       gemm<T>(ctx, OpN, OpC, r2, kb2, kb, mone, at(K1, K0), lda, at(K1, K0), lda, one<T>(),
               at(K1, K1), lda, TriLower, Traits<T>::is_complex);
     } else {
@@ -329,10 +356,12 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
       gemm<T>(ctx, OpC, OpN, kb2, r2, kb, mone, at(K0, K1), lda, at(K0, K1), lda, one<T>(),
               at(K1, K1), lda, TriUpper, Traits<T>::is_complex);
     }
+    CTL(ctx.stream);
     LA_CUDA_CHECK(cudaEventRecord(ctx.ev[0], ctx.stream));
     LA_CUDA_CHECK(cudaStreamWaitEvent(side->stream, ctx.ev[0], 0));
     side->sm_limit = side_sms;
     potrf_twolevel<T>(*side, uplo, kb2, at(K1, K1), lda, d_info, K1);
+    CTL(side->stream);
     LA_CUDA_CHECK(cudaEventRecord(side->ev[0], side->stream));
     if (r3 > 0) {
       const int keep = ctx.sm_limit;
@@ -343,6 +372,7 @@ void potrf(Context& ctx, Uplo uplo, int64_t n, T* A, int64_t lda, int* d_info) {
         herk<T>(ctx, Upper, OpC, r3, kb, -1.0, at(K0, K1 + kb2), lda, 1.0, at(K1 + kb2, K1 + kb2), lda);
       ctx.sm_limit = keep;
     }
+    CTL(ctx.stream);
     LA_CUDA_CHECK(cudaStreamWaitEvent(ctx.stream, side->ev[0], 0));
   }
 }
