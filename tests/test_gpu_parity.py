@@ -358,10 +358,13 @@ def test_geqrf_matches_lapack_conventions(rng, dt, shape, product_abi, oracle_ab
 
 
 @pytest.mark.parametrize("dt,m,n", [(np.float64, 150000, 40), (np.complex128, 70000, 24),
-                                    (np.float32, 250000, 20)], ids=IDS[1:] + IDS[:1])
+                                    (np.float32, 250000, 20), (np.float64, 600000, 24),
+                                    (np.complex128, 300000, 12), (np.float32, 1200000, 10)],
+                         ids=IDS[1:] + IDS[:1] + ["d-streamed", "z-streamed", "s-streamed"])
 def test_tall_skinny_qr_streaming_panels(rng, dt, m, n, product_abi, oracle_abi):
     # panels whose row slices exceed shared memory take the streaming panel kernel and the
-    # split-K products V^H C / V^H V (BASELINE config c5 is 2^20 x 512)
+    # split-K products V^H C / V^H V (BASELINE config c5 is 2^20 x 512); the first three shapes
+    # have 8-column leaves that still fit shared memory, the "streamed" ones do not
     A = _rand(rng, (m, n), dt, -0.5)
     B = _rand(rng, (m, 2), dt, -0.5)
 
@@ -375,6 +378,32 @@ def test_tall_skinny_qr_streaming_panels(rng, dt, m, n, product_abi, oracle_abi)
     assert checks.rel(r - rr, rr) < tol
     assert checks.rel(tau - rtau, rtau) < tol
     assert checks.rel(x - xr, xr) < 100 * tol
+
+
+def test_tall_skinny_qr_with_nearly_parallel_columns(rng, product_abi, oracle_abi):
+    # The streamed 8-column leaf derives the second reflector of a pair from sums taken before
+    # the first one is applied; when that difference cancels (a column nearly parallel to its
+    # left neighbour) it must fall back to a pass of its own.  Columns 5 and 11 are the second
+    # of their pairs: R's small diagonal entries and the orthogonality of Q show whether it did.
+    m, n = 600000, 16                    # 8-column panels of this height are streamed, not held in smem
+    A = _rand(rng, (m, n), np.float64, -0.5)
+    A[:, 5] = A[:, 4] + 1e-7 * _rand(rng, (m,), np.float64, -0.5)
+    A[:, 11] = 3.0 * A[:, 10] - 1e-9 * _rand(rng, (m,), np.float64, -0.5)
+    A = np.asfortranarray(A)
+
+    def run():
+        q, r = la.GeneralMatrix(A).qr()
+        return q.raw, r.raw[:n]
+
+    (q, r), (rq, rr) = _both(run, product_abi, oracle_abi)
+    nrm = np.linalg.norm(A)
+    assert np.linalg.norm(q @ r - A) / nrm < 1e-13
+    assert np.abs(q.T @ q - np.eye(n)).max() < 1e-12
+    # the tiny diagonal entries (1e-7 and 1e-9 of a column norm) agree in magnitude with LAPACK's
+    for c in (5, 11):
+        assert abs(abs(r[c, c]) - abs(rr[c, c])) < 1e-5 * abs(rr[c, c]) + 1e-13 * nrm
+    well = [c for c in range(n) if c not in (5, 11)]
+    assert np.abs(np.abs(np.diagonal(r))[well] - np.abs(np.diagonal(rr))[well]).max() < 1e-9 * nrm
 
 
 @pytest.mark.parametrize("dt", DTYPES, ids=IDS)
