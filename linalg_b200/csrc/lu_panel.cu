@@ -150,8 +150,24 @@ __device__ __forceinline__ void ll_get_row(const LLPacket* row, int lane, int wi
   rv = from_words<T>(d + EPL * W);
 }
 
-// 16 bytes of a row at a time (the staging store of a candidate row)
-template <typename T> struct alignas(16) Vec16 { T v[16 / sizeof(T)]; };
+// 16 bytes of a row at a time (the staging store of a candidate row), through an explicit 32-bit
+// shared-memory address: with generic pointers the compiler re-derived the shared window
+// (S2R SR_CgaCtaId + LEA) in front of every one of the 16 predicated stores, ~40 cycles each on
+// the serial path of a column.
+__device__ __forceinline__ uint32_t lu_smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+template <typename T> __device__ __forceinline__ void sts16(uint32_t addr, const T* v);
+template <> __device__ __forceinline__ void sts16<double>(uint32_t addr, const double* v) {
+  asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v[0]), "d"(v[1]) : "memory");
+}
+template <> __device__ __forceinline__ void sts16<float>(uint32_t addr, const float* v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v[0]), "f"(v[1]),
+               "f"(v[2]), "f"(v[3]) : "memory");
+}
+template <> __device__ __forceinline__ void sts16<zcomplex>(uint32_t addr, const zcomplex* v) {
+  asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v[0].x), "d"(v[0].y) : "memory");
+}
 
 // Pivot candidates are compared through integer keys: for non-negative doubles the IEEE bit
 // pattern orders like the value, and integer compares are several times shorter than FP64 ones
@@ -223,6 +239,8 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
   __shared__ int s_pi[2];
   __shared__ int s_cand_raw;                       // the staged candidate lacks the tail of column j-1
 
+  uint32_t cand_s = lu_smem_u32(cand);
+  asm volatile("" : "+r"(cand_s));   // opaque: keep it in a register instead of re-deriving it per store
   const int tid = threadIdx.x, lane = tid & 31;
   // broadcast from lane 0: tells the compiler that the warp index is warp-uniform, so that the
   // reductions / ballots / shuffles under `if (warp == 0)` are emitted inline and not as
@@ -280,12 +298,7 @@ lu_panel_kernel(int m, int jb, T* __restrict__ A, int64_t lda, int* __restrict__
         if (JBM >= VE) {
 #pragma unroll
           for (int c = 0; c + VE <= JBM; c += VE)
-            if (c < live) {
-              Vec16<T> v;
-#pragma unroll
-              for (int i = 0; i < VE; i++) v.v[i] = a[r][c + i];
-              *reinterpret_cast<Vec16<T>*>(cand + c) = v;
-            }
+            if (c < live) sts16<T>(cand_s + c * (uint32_t)sizeof(T), &a[r][c]);
         } else {
 #pragma unroll
           for (int c = 0; c < JBM; c++) cand[c] = a[r][c];
