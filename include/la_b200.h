@@ -315,6 +315,14 @@ int la_b200_set_sm_limit(int sms);
                              int64_t ldb, void* stream);                                          \
   int la_b200_##X##laset_dev(int uplo, int64_t m, int64_t n, const void* alpha, const void* beta, \
                              T* a, int64_t lda, void* stream);                                    \
+  /* the element-wise steps between the products of a resident chain (the reference's          \
+     Matrix#add!, scalar multiples and map(&.abs): src/linalg/matrix.cr, expm.cr:112-166):     \
+     B <- alpha A + beta B (B is not read when beta == 0; alpha / beta by pointer), and          \
+     B <- |A| (modulus, zero imaginary part for complex) */                                      \
+  int la_b200_##X##geadd_dev(int64_t m, int64_t n, const void* alpha, const T* a, int64_t lda,    \
+                             const void* beta, T* b, int64_t ldb, void* stream);                  \
+  int la_b200_##X##geabs_dev(int64_t m, int64_t n, const T* a, int64_t lda, T* b, int64_t ldb,    \
+                             void* stream);                                                       \
   int la_b200_##X##getrs_dev(int trans, int64_t n, int64_t nrhs, const T* a, int64_t lda,         \
                              const int* ipiv, T* b, int64_t ldb, void* stream);                   \
   int la_b200_##X##potrf_dev(int uplo, int64_t n, T* a, int64_t lda, int* info, void* stream);    \

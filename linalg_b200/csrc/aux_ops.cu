@@ -137,6 +137,31 @@ __global__ void lacpy_kernel(int part, int64_t m, int64_t n, const T* __restrict
   for (int64_t j = blockIdx.y; j < n; j += gridDim.y)
     if (part == 0 || (part == 1 && i <= j) || (part == 2 && i >= j)) B[i + j * ldb] = A[i + j * lda];
 }
+// B <- alpha A + beta B (beta == 0: B is not read) and B <- |A|: the element-wise steps between
+// the products of a resident chain (Matrix#add!, scalar multiples, map(&.abs) in the reference)
+template <typename T>
+__global__ void geadd_kernel(int64_t m, int64_t n, T alpha, const T* __restrict__ A, int64_t lda,
+                             T beta, int beta_zero, T* __restrict__ B, int64_t ldb) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  for (int64_t j = blockIdx.y; j < n; j += gridDim.y) {
+    const T x = mul(alpha, A[i + j * lda]);
+    B[i + j * ldb] = beta_zero ? x : add(x, mul(beta, B[i + j * ldb]));
+  }
+}
+template <typename T>
+__global__ void geabs_kernel(int64_t m, int64_t n, const T* __restrict__ A, int64_t lda,
+                             T* __restrict__ B, int64_t ldb) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  for (int64_t j = blockIdx.y; j < n; j += gridDim.y) {
+    const T a = A[i + j * lda];
+    double r;
+    if constexpr (Traits<T>::is_complex) r = hypot(a.x, a.y);
+    else r = fabs((double)a);
+    B[i + j * ldb] = from_real<T>(r);
+  }
+}
 template <typename T>
 __global__ void laset_kernel(int part, int64_t m, int64_t n, T alpha, T beta, T* __restrict__ A,
                              int64_t lda) {
@@ -350,6 +375,30 @@ void zlaset_(const char* uplo, const int* m, const int* n, const void* alpha, co
     laset_kernel<T><<<g, 256, 0, (cudaStream_t)stream>>>(part_from_char((char)uplo), m, n,        \
                                                          *(const T*)alpha, *(const T*)beta,       \
                                                          (T*)a, lda);                             \
+    return cudaGetLastError() == cudaSuccess ? 0 : -100;                                          \
+  }                                                                                               \
+  int la_b200_##X##geadd_dev(int64_t m, int64_t n, const void* alpha, const VT* a, int64_t lda,   \
+                             const void* beta, VT* b, int64_t ldb, void* stream) {                \
+    if (m < 0) return -1;                                                                         \
+    if (n < 0) return -2;                                                                         \
+    if (lda < (m > 1 ? m : 1)) return -5;                                                         \
+    if (ldb < (m > 1 ? m : 1)) return -8;                                                         \
+    if (m == 0 || n == 0) return 0;                                                               \
+    const T be = *(const T*)beta;                                                                 \
+    dim3 g((unsigned)ceil_div(m, (int64_t)256), (unsigned)(n < 4096 ? n : 4096));                 \
+    geadd_kernel<T><<<g, 256, 0, (cudaStream_t)stream>>>(m, n, *(const T*)alpha, (const T*)a,     \
+                                                         lda, be, is_zero(be) ? 1 : 0, (T*)b, ldb); \
+    return cudaGetLastError() == cudaSuccess ? 0 : -100;                                          \
+  }                                                                                               \
+  int la_b200_##X##geabs_dev(int64_t m, int64_t n, const VT* a, int64_t lda, VT* b, int64_t ldb,  \
+                             void* stream) {                                                      \
+    if (m < 0) return -1;                                                                         \
+    if (n < 0) return -2;                                                                         \
+    if (lda < (m > 1 ? m : 1)) return -4;                                                         \
+    if (ldb < (m > 1 ? m : 1)) return -6;                                                         \
+    if (m == 0 || n == 0) return 0;                                                               \
+    dim3 g((unsigned)ceil_div(m, (int64_t)256), (unsigned)(n < 4096 ? n : 4096));                 \
+    geabs_kernel<T><<<g, 256, 0, (cudaStream_t)stream>>>(m, n, (const T*)a, lda, (T*)b, ldb);     \
     return cudaGetLastError() == cudaSuccess ? 0 : -100;                                          \
   }
 LA_AUX_DEV(s, float, float)

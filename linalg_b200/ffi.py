@@ -166,7 +166,7 @@ def declared_symbols():
                   "lantr", "lacpy", "laset"):
             syms.append(f"{l}{r}_")
         for r in ("trsm", "herk", "getrf", "getrs", "potrf", "potrs", "geqrf", "ormqr", "gels",
-                  "trtrs", "laswp", "gemm_stair", "lange", "lacpy", "laset"):
+                  "trtrs", "laswp", "gemm_stair", "lange", "lacpy", "laset", "geadd", "geabs"):
             syms.append(f"la_b200_{l}{r}_dev")
         syms.append(f"la_b200_{l}gemm_dev")
     syms += ["cblas_zhemm", "cblas_ssyrk", "cblas_dsyrk", "cblas_zherk", "sormqr_", "dormqr_",

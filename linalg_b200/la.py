@@ -175,6 +175,137 @@ def _lapack(name, letter, *args):
         raise LinAlgError(f"LAPACK.{letter}{name} returned {info.value}")
 
 
+
+class _DeviceChain:
+    """Resident operands for a chain of products, element-wise steps and one solve (SURVEY.md §8 f3;
+    include/la_b200.h Part 3 + handles): square n x n matrices and n x 1 vectors of one element
+    type live in device handles, every step is one `la_b200_*_dev` call on the default stream,
+    only scalars and the final result cross PCIe."""
+
+    def __init__(self, letter, n, dtype):
+        from ctypes import c_double, c_float, c_int64, c_void_p
+        self.L, self.n, self.dtype = letter, n, np.dtype(dtype)
+        cd = self.cd = backend().cdll
+        if not hasattr(cd, "la_b200_mat_create"):
+            raise RuntimeError("the backend has no device-matrix handles")
+        cd.la_b200_mat_create.restype = c_void_p
+        cd.la_b200_mat_create.argtypes = [c_int, c_int64, c_int64]
+        cd.la_b200_mat_ptr.restype, cd.la_b200_mat_ptr.argtypes = c_void_p, [c_void_p]
+        cd.la_b200_mat_ld.restype, cd.la_b200_mat_ld.argtypes = c_int64, [c_void_p]
+        cd.la_b200_mat_free.restype, cd.la_b200_mat_free.argtypes = None, [c_void_p]
+        cd.la_b200_mat_upload.argtypes = [c_void_p, c_void_p, c_int64]
+        cd.la_b200_mat_download.argtypes = [c_void_p, c_void_p, c_int64]
+        sc = c_void_p if letter == "z" else (c_float if letter == "s" else c_double)
+        f = lambda name: getattr(cd, f"la_b200_{letter}{name}_dev")
+        self._gemm = f("gemm")
+        self._gemm.argtypes = [c_int, c_int, c_int64, c_int64, c_int64, sc, c_void_p, c_int64,
+                               c_void_p, c_int64, sc, c_void_p, c_int64, c_void_p]
+        self._geadd = f("geadd")
+        self._geadd.argtypes = [c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
+                                c_int64, c_void_p]
+        self._geabs = f("geabs")
+        self._geabs.argtypes = [c_int64, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p]
+        self._laset = f("laset")
+        self._laset.argtypes = [c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        self._lange = f("lange")
+        self._lange.argtypes = [c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p]
+        self._getrf = f("getrf")
+        self._getrf.argtypes = [c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]
+        self._getrs = f("getrs")
+        self._getrs.argtypes = [c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p, c_void_p,
+                                c_int64, c_void_p]
+        self._handles = []
+        self._one, self._k1 = ffi.scalar_arg(letter, 1.0)
+        self._zero, self._k0 = ffi.scalar_arg(letter, 0.0)
+        self._scalar = self._handle("d", 1, 1)          # a device double for norms
+        self._ipiv = self._handle("s", n, 1)            # 4-byte slots: the pivots (int32)
+        self._info = self._handle("s", 1, 1)
+
+    def _handle(self, letter, rows, cols):
+        from ctypes import c_void_p
+        h = c_void_p(self.cd.la_b200_mat_create(ord(letter), rows, cols))
+        if h.value is None:
+            self.close()
+            raise MemoryError("la_b200_mat_create failed")
+        self._handles.append(h)
+        return h
+
+    def close(self):
+        for h in self._handles:
+            self.cd.la_b200_mat_free(h)
+        self._handles = []
+
+    def __enter__(self): return self
+    def __exit__(self, *exc): self.close()
+
+    def matrix(self): return self._handle(self.L, self.n, self.n)
+    def vector(self): return self._handle(self.L, self.n, 1)
+    def _p(self, h): return self.cd.la_b200_mat_ptr(h)
+    def _ld(self, h): return self.cd.la_b200_mat_ld(h)
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise LinAlgError(f"la_b200_{self.L}{what}_dev returned {rc}")
+
+    def upload(self, h, a):
+        a = np.asfortranarray(a, dtype=self.dtype)
+        self._check(self.cd.la_b200_mat_upload(h, ffi.ptr(a), a.shape[0]), "mat_upload")
+
+    def download(self, h, rows, cols):
+        out = np.zeros((rows, cols), dtype=self.dtype, order="F")
+        self._check(self.cd.la_b200_mat_download(h, ffi.ptr(out), rows), "mat_download")
+        return out
+
+    def _sc(self, v):
+        buf = np.array([v], dtype=self.dtype)
+        return buf
+
+    def fill(self, h, offdiag, diag, cols=None):
+        a, b = self._sc(offdiag), self._sc(diag)
+        cols = self.n if cols is None else cols
+        self._check(self._laset(ord("A"), self.n, cols, ffi.ptr(a), ffi.ptr(b), self._p(h),
+                                self._ld(h), None), "laset")
+
+    def mul(self, dst, a, b, cols=None, trans_a=False):
+        """dst <- op(a) b: Matrix#* is beta = 1 on a zeroed result (mult.cr:118-120)."""
+        cols = self.n if cols is None else cols
+        self.fill(dst, 0, 0, cols)
+        self._check(self._gemm(ffi.TRANS if trans_a else ffi.NO_TRANS, ffi.NO_TRANS, self.n, cols,
+                               self.n, self._one, self._p(a), self._ld(a), self._p(b), self._ld(b),
+                               self._one, self._p(dst), self._ld(dst), None), "gemm")
+
+    def axpby(self, dst, alpha, a, beta=0.0):
+        """dst <- alpha a + beta dst"""
+        al, be = self._sc(alpha), self._sc(beta)
+        self._check(self._geadd(self.n, self.n, ffi.ptr(al), self._p(a), self._ld(a), ffi.ptr(be),
+                                self._p(dst), self._ld(dst), None), "geadd")
+
+    def absolute(self, dst, a):
+        self._check(self._geabs(self.n, self.n, self._p(a), self._ld(a), self._p(dst), self._ld(dst),
+                                None), "geabs")
+
+    def norm(self, h, kind, cols=None):
+        from ctypes import c_double
+        cols = self.n if cols is None else cols
+        self._check(self._lange(ord(kind), self.n, cols, self._p(h), self._ld(h),
+                                self._p(self._scalar), None), "lange")
+        out = np.zeros(1, dtype=np.float64)
+        self._check(self.cd.la_b200_mat_download(self._scalar, ffi.ptr(out), 1), "mat_download")
+        return float(out[0])
+
+    def solve(self, a, b):
+        """b <- a^-1 b through ?getrf / ?getrs on the resident matrices (a is overwritten)."""
+        n = self.n
+        self._check(self._getrf(n, n, self._p(a), self._ld(a), self._p(self._ipiv),
+                                self._p(self._info), None), "getrf")
+        info = np.zeros(1, dtype=np.float32)
+        self._check(self.cd.la_b200_mat_download(self._info, ffi.ptr(info), 1), "mat_download")
+        if int(info.view(np.int32)[0]) != 0:
+            raise LinAlgError(f"?getrf returned {int(info.view(np.int32)[0])}")
+        self._check(self._getrs(ffi.NO_TRANS, n, n, self._p(a), self._ld(a), self._p(self._ipiv),
+                                self._p(b), self._ld(b), None), "getrs")
+
+
 class GeneralMatrix:
     """Dense column-major matrix (src/matrix/general_matrix.cr:10-27)."""
 
@@ -487,6 +618,297 @@ class GeneralMatrix:
                     cd.la_b200_mat_free(h)
         return out
 
+    # -- matrix functions (expm.cr, matfun.cr) ------------------------------------------------------
+    # expm.cr:4-26, 168-191
+    _EXPM_COEFF = (1.0 / 100800, 1.0 / 10059033600, 1.0 / 4487938430976000,
+                   1.0 / 5914384781877411840000.0, 1.0 / 113250775606021113483283660800000000.0)
+    _EXPM_M = (3, 5, 7, 9, 13)
+    _EXPM_THETA = (1.495585217958292e-002, 2.539398330063230e-001, 9.504178996162932e-001,
+                   2.097847961257068e+000, 4.250000000000000e+000)
+    _EXPM_PADE = {
+        3: (120.0, 60.0, 12.0, 1.0),
+        5: (30240.0, 15120.0, 3360.0, 420.0, 30.0, 1.0),
+        7: (17297280.0, 8648640.0, 1995840.0, 277200.0, 25200.0, 1512.0, 56.0, 1.0),
+        9: (17643225600.0, 8821612800.0, 2075673600.0, 302702400.0, 30270240.0,
+            2162160.0, 110880.0, 3960.0, 90.0, 1.0),
+        13: (64764752532480000.0, 32382376266240000.0, 7771770303897600.0,
+             1187353796428800.0, 129060195264000.0, 10559470521600.0,
+             670442572800.0, 33522128640.0, 1323241920.0,
+             40840800.0, 960960.0, 16380.0, 182.0, 1.0),
+    }
+    EXPM_RESIDENT_FROM = 64     # orders from which expm keeps its operands on the device
+
+    def expm(self, *, schur_fact=False):
+        """expm.cr:37-110 — scaling and squaring with Pade approximants (Al-Mohy & Higham 2009),
+        same degree selection, same 1-norm estimates of powers (`normAm`), same special cases
+        (zero matrix, Diagonal flag, 2 x 2 closed forms).  From order EXPM_RESIDENT_FROM on the
+        whole chain — products, |A|, linear combinations, the final solve and the squarings — runs
+        on device-resident operands (one upload, one download).  Differences from the reference,
+        all at rounding level: (V - U)^-1 (U + V) is a ?getrf / ?getrs solve, not an explicit
+        inverse followed by a product; a matrix flagged (one-sided) triangular takes this general
+        path instead of `expm_sqtri` (expm.cr:232-294); `schur_fact: true` needs the eigenvalue
+        routines, which are outside the hot path, and is refused."""
+        if not self.square:
+            raise ValueError("Matrix must be square for expm")
+        if schur_fact:
+            raise NotImplementedError("expm(schur_fact: true) needs ?gees (outside the hot path)")
+        n = self.nrows
+        if n == 0 or float(np.abs(self.raw).sum(axis=0).max()) == 0.0:   # norm(One) == 0
+            out = GeneralMatrix.identity(n, self.dtype)
+            return out
+        if self.flags.upper_triangular and self.flags.lower_triangular:    # flags.diagonal?
+            return GeneralMatrix(np.diag(np.exp(np.diagonal(self.raw))).astype(self.dtype))
+        if n == 2:
+            return GeneralMatrix(self._expm_2by2())
+        if n >= self.EXPM_RESIDENT_FROM and hasattr(backend().cdll, "la_b200_mat_create"):
+            return GeneralMatrix(self._expm_resident())
+        return GeneralMatrix(self._expm_host())
+
+    def _expm_2by2(self):       # expm.cr:297-357
+        a, b, c, d = (self.raw[0, 0], self.raw[0, 1], self.raw[1, 0], self.raw[1, 1])
+        sinch = lambda x: 1.0 if x == 0 else np.sinh(x) / x
+        if self.flags.upper_triangular:                                    # expmT2by2!
+            ave = ((a + d) / 2).real
+            df = abs(a - d) / 2
+            if max(ave, df) < np.log(np.finfo(self.raw.real.dtype).max):
+                x12 = b * np.exp((a + d) / 2) * sinch((d - a) / 2)
+            else:
+                x12 = b * (np.exp(d) - np.exp(a)) / (d - a)
+            return np.array([[np.exp(a), x12], [0.0, np.exp(d)]], dtype=self.dtype)
+        disc = (a - d) * (a - d) + 4 * b * c
+        delta = np.sqrt(disc + 0j) if (np.iscomplexobj(self.raw) or disc < 0) else np.sqrt(disc)
+        k = np.exp((a + d) / 2)
+        out = np.array([[k * (np.cosh(delta / 2) + (a - d) / 2 * sinch(delta / 2)), k * b * sinch(delta / 2)],
+                        [k * c * sinch(delta / 2), k * (np.cosh(delta / 2) + (d - a) / 2 * sinch(delta / 2))]])
+        return (out if np.iscomplexobj(self.raw) else out.real).astype(self.dtype)
+
+    @staticmethod
+    def _expm_alpha_steps(alpha, eps, m):      # expm.cr:112-117
+        import math
+        if alpha == 0.0:
+            return 0
+        return max(int(math.ceil(math.log2(alpha / (eps / 2)) / (2 * m))), 0)
+
+    def _expm_plan(self, norm_am, norm_am_abs_a, norm1_a):
+        """The degree / scaling decisions of expm.cr:58-98, written once for both paths.
+        `norm_am(which, m)` estimates ||X^m||_1 for X in {"a2", "a4", "a6"} (computing the power
+        on demand), `norm_am_abs_a(m, scale)` does it for |A| / scale.  Returns (degree, s)."""
+        import math
+        eps = float(np.finfo(self.raw.real.dtype).eps)
+        TH, MV, CO = self._EXPM_THETA, self._EXPM_M, self._EXPM_COEFF
+        steps = lambda k, scale=1.0: self._expm_alpha_steps(
+            CO[k - 1] * norm_am_abs_a(2 * MV[k - 1] + 1, scale) / (norm1_a / scale), eps, MV[k - 1])
+        eta1 = max(norm_am("a2", 2) ** (1.0 / 4), norm_am("a2", 3) ** (1.0 / 6))
+        if eta1 <= TH[0] and steps(1) == 0:
+            return 3, 0
+        eta2 = max(norm_am("a4", 1) ** (1.0 / 4), norm_am("a2", 3) ** (1.0 / 6))
+        if eta2 <= TH[1] and steps(2) == 0:
+            return 5, 0
+        eta3 = max(norm_am("a6", 1) ** (1.0 / 6), norm_am("a4", 2) ** (1.0 / 8))
+        for i in (2, 3):
+            if eta3 <= TH[i] and steps(i + 1) == 0:
+                return MV[i], 0
+        eta4 = max(norm_am("a4", 2) ** (1.0 / 8), norm_am("a2", 5) ** (1.0 / 10))
+        eta5 = min(eta3, eta4)
+        s = max(int(math.ceil(math.log2(eta5 / TH[-1]))), 0) if eta5 > 0 else 0
+        s += steps(5, 2.0 ** s)
+        return 13, s
+
+    def _expm_host(self):
+        """The chain with every product through Matrix#* (cblas_?gemm on host pointers), the
+        element-wise steps in host memory as in the reference."""
+        A = self.clone()
+        A.clear_flags()
+        n, dt = self.nrows, self.dtype
+        pw = {}
+
+        def power(which):
+            if which not in pw:
+                if which == "a2":
+                    pw[which] = A * A
+                elif which == "a4":
+                    pw[which] = power("a2") * power("a2")
+                else:
+                    pw[which] = power("a2") * power("a4")
+            return pw[which]
+
+        def norm_am_of(mat, m):          # expm.cr:193-217 (test on the real parts, as written)
+            b = mat if bool(np.all(mat.real >= 0)) else np.abs(mat)
+            e = GeneralMatrix.ones(n, 1, b.dtype)
+            bt = GeneralMatrix(np.asfortranarray(b.T))
+            for _ in range(m):
+                e = bt * e
+            return float(np.abs(e.raw).max())
+
+        absa = np.abs(A.raw)
+        norm1_a = float(absa.sum(axis=0).max())
+        deg, s = self._expm_plan(lambda w, m: norm_am_of(power(w).raw, m),
+                                 lambda m, scale: norm_am_of(absa / scale, m), norm1_a)
+        c = self._EXPM_PADE[deg]
+        eye = np.eye(n, dtype=dt)
+        a = A.raw / 2.0 ** s
+        a2 = power("a2").raw / 2.0 ** (2 * s)
+        G = lambda x: GeneralMatrix(np.asfortranarray(x.astype(dt)))
+        if deg == 13:
+            a4, a6 = power("a4").raw / 2.0 ** (4 * s), power("a6").raw / 2.0 ** (6 * s)
+            u = (G(a) * (G(a6) * G(c[13] * a6 + c[11] * a4 + c[9] * a2) +
+                         G(c[7] * a6 + c[5] * a4 + c[3] * a2 + c[1] * eye))).raw
+            v = (G(a6) * G(c[12] * a6 + c[10] * a4 + c[8] * a2)).raw + \
+                c[6] * a6 + c[4] * a4 + c[2] * a2 + c[0] * eye
+        else:
+            m2 = (deg + 3) // 2
+            pws = [eye, a2]
+            if deg >= 5:
+                pws.append(power("a4").raw)
+            if deg >= 7:
+                pws.append(power("a6").raw)
+            while len(pws) < m2:
+                pws.append((G(pws[-1]) * G(a2)).raw)
+            u = np.zeros((n, n), dtype=dt)
+            v = np.zeros((n, n), dtype=dt)
+            for j in range(deg + 1, 1, -2):
+                u = u + c[j - 1] * pws[j // 2 - 1]
+            u = (G(a) * G(u)).raw
+            for j in range(deg, 0, -2):
+                v = v + c[j - 1] * pws[(j + 1) // 2 - 1]
+        f = G(v - u).solve(G(u + v))
+        for _ in range(s):
+            f = f * f
+        return f.raw
+
+    def _expm_resident(self):
+        """The same chain on device-resident operands (`_DeviceChain`)."""
+        n, dt, L = self.nrows, self.dtype, self.letter
+        cplx = np.iscomplexobj(self.raw)
+        with _DeviceChain(L, n, dt) as dc:
+            A, absA, t1, t2, t3 = (dc.matrix() for _ in range(5))
+            e1, e2 = dc.vector(), dc.vector()
+            dc.upload(A, self.raw)
+            dc.absolute(absA, A)
+            pw = {}
+
+            def power(which):
+                if which not in pw:
+                    h = dc.matrix()
+                    if which == "a2":
+                        dc.mul(h, A, A)
+                    elif which == "a4":
+                        dc.mul(h, power("a2"), power("a2"))
+                    else:
+                        dc.mul(h, power("a2"), power("a4"))
+                    pw[which] = h
+                return pw[which]
+
+            def nonneg(h):               # expm.cr:205: the reference tests the real parts only
+                if cplx:
+                    return bool(np.all(dc.download(h, n, n).real >= 0))
+                dc.absolute(t1, h)
+                dc.axpby(t1, -1.0, h, 1.0)           # |X| - X
+                return dc.norm(t1, "M") == 0.0
+
+            def norm_am_of(h, m, scale=1.0, known_nonneg=False):
+                src = h
+                if not known_nonneg and not nonneg(h):
+                    dc.absolute(t2, h)
+                    src = t2
+                dc.fill(e1, 1.0, 1.0, cols=1)
+                x, y = e1, e2
+                for _ in range(m):
+                    dc.mul(y, src, x, cols=1, trans_a=True)      # e <- X^T e (plain transpose)
+                    x, y = y, x
+                return dc.norm(x, "M", cols=1) / scale ** m
+
+            norm1_a = dc.norm(A, "O")
+            deg, s = self._expm_plan(lambda w, m: norm_am_of(power(w), m),
+                                     lambda m, scale: norm_am_of(absA, m, scale, True), norm1_a)
+            c = self._EXPM_PADE[deg]
+            sc = [1.0 / 2.0 ** (k * s) for k in range(7)]       # a^k is scaled by 2^-(k s)
+            U, V = t1, t2
+            if deg == 13:
+                a2, a4, a6 = power("a2"), power("a4"), power("a6")
+                W = t3
+                dc.axpby(W, c[13] * sc[6], a6)                    # c14 a6 + c12 a4 + c10 a2 (scaled)
+                dc.axpby(W, c[11] * sc[4], a4, 1.0)
+                dc.axpby(W, c[9] * sc[2], a2, 1.0)
+                Sa6 = dc.matrix()
+                dc.axpby(Sa6, sc[6], a6)
+                dc.mul(V, Sa6, W)                                 # V = a6 (...)
+                dc.axpby(V, c[7] * sc[6], a6, 1.0)
+                dc.axpby(V, c[5] * sc[4], a4, 1.0)
+                dc.axpby(V, c[3] * sc[2], a2, 1.0)
+                dc.fill(W, 0.0, c[1])
+                dc.axpby(V, 1.0, W, 1.0)                          # + c2 I
+                dc.axpby(W, sc[1], A)                             # scaled A
+                dc.mul(U, W, V)                                   # U = a (...)
+                dc.axpby(W, c[12] * sc[6], a6)                    # c13 a6 + c11 a4 + c9 a2
+                dc.axpby(W, c[10] * sc[4], a4, 1.0)
+                dc.axpby(W, c[8] * sc[2], a2, 1.0)
+                dc.mul(V, Sa6, W)
+                dc.axpby(V, c[6] * sc[6], a6, 1.0)
+                dc.axpby(V, c[4] * sc[4], a4, 1.0)
+                dc.axpby(V, c[2] * sc[2], a2, 1.0)
+                dc.fill(W, 0.0, c[0])
+                dc.axpby(V, 1.0, W, 1.0)
+            else:
+                m2 = (deg + 3) // 2
+                eye = dc.matrix()
+                dc.fill(eye, 0.0, 1.0)
+                pws = [eye, power("a2")]
+                if deg >= 5:
+                    pws.append(power("a4"))
+                if deg >= 7:
+                    pws.append(power("a6"))
+                while len(pws) < m2:
+                    h = dc.matrix()
+                    dc.mul(h, pws[-1], pws[1])
+                    pws.append(h)
+                W = t3
+                dc.fill(W, 0.0, 0.0)
+                for j in range(deg + 1, 1, -2):
+                    dc.axpby(W, c[j - 1], pws[j // 2 - 1], 1.0)
+                dc.mul(U, A, W)
+                dc.fill(V, 0.0, 0.0)
+                for j in range(deg, 0, -2):
+                    dc.axpby(V, c[j - 1], pws[(j + 1) // 2 - 1], 1.0)
+            D, N = t3, dc.matrix()
+            dc.axpby(D, 1.0, V)
+            dc.axpby(D, -1.0, U, 1.0)                             # V - U
+            dc.axpby(N, 1.0, V)
+            dc.axpby(N, 1.0, U, 1.0)                              # U + V
+            dc.solve(D, N)                                        # F = (V - U)^-1 (U + V)
+            F, G2 = N, t1
+            for _ in range(s):
+                dc.mul(G2, F, F)
+                F, G2 = G2, F
+            return dc.download(F, n, n)
+
+    # matfun.cr:20-56
+    def cosm(self):
+        if np.iscomplexobj(self.raw):
+            return GeneralMatrix(0.5 * (GeneralMatrix(1j * self.raw).expm().raw +
+                                        GeneralMatrix(-1j * self.raw).expm().raw))
+        return GeneralMatrix(np.asfortranarray(
+            GeneralMatrix((1j * self.raw).astype(np.complex128)).expm().raw.real.astype(self.dtype)))
+
+    def sinm(self):
+        if np.iscomplexobj(self.raw):
+            return GeneralMatrix(-0.5j * (GeneralMatrix(1j * self.raw).expm().raw -
+                                          GeneralMatrix(-1j * self.raw).expm().raw))
+        return GeneralMatrix(np.asfortranarray(
+            GeneralMatrix((1j * self.raw).astype(np.complex128)).expm().raw.imag.astype(self.dtype)))
+
+    def tanm(self):
+        return self.sinm() * self.cosm().inv_()
+
+    def coshm(self):
+        return GeneralMatrix(0.5 * (self.expm().raw + GeneralMatrix(-self.raw).expm().raw))
+
+    def sinhm(self):
+        return GeneralMatrix(0.5 * (self.expm().raw - GeneralMatrix(-self.raw).expm().raw))
+
+    def tanhm(self):
+        return self.sinhm() * self.coshm().inv_()
+
     # -- LU (lu.cr) --------------------------------------------------------------------------
     def lu(self, *, overwrite_a=False):
         a = self if overwrite_a else self.clone()
@@ -745,6 +1167,13 @@ def lapack_version():
     return backend().ilaver()
 
 
+def expm(a): return a.expm()
+def cosm(a): return a.cosm()
+def sinm(a): return a.sinm()
+def tanm(a): return a.tanm()
+def coshm(a): return a.coshm()
+def sinhm(a): return a.sinhm()
+def tanhm(a): return a.tanhm()
 def solve(a, b, **kw): return a.solve(b, **kw)
 def inv(a): return a.inv()
 def solvels(a, b, **kw): return a.solvels(b, **kw)

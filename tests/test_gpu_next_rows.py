@@ -203,3 +203,82 @@ def test_handles_report_their_geometry_and_refuse_bad_arguments(product_abi):
     assert cd.la_b200_mat_download(h, ffi.ptr(b), 39) == 0
     assert np.array_equal(b[:37], a[:37]) and not b[37:].any()
     cd.la_b200_mat_free(h)
+
+
+# ---- matrix functions on top of the path (src/linalg/expm.cr, matfun.cr) -------
+from oracle import expm_ref  # noqa: E402
+
+
+def test_expm_reference_spec_vectors(product_abi):
+    """spec/expm_spec.cr and spec/matfun_spec.cr through the product (special cases, the 2 x 2
+    closed forms and the small general path)."""
+    with la.use_backend(product_abi):
+        assert np.array_equal(la.GMat(np.zeros((2, 2))).expm().raw, np.eye(2))
+        assert abs(la.GMat(np.ones((1, 1))).expm().raw[0, 0] - np.e) < 1e-14
+        m = la.GMat([[0, 6, 0, 0], [0, 0, 6, 0], [0, 0, 0, 6], [0, 0, 0, 0]])
+        mres = np.array([[1.0, 6.0, 18.0, 36.0], [0.0, 1.0, 6.0, 18.0], [0.0, 0.0, 1.0, 6.0], [0.0, 0.0, 0.0, 1.0]])
+        assert np.abs(m.expm().raw - mres).max() < 1e-12
+        assert np.abs(la.GMat32(m.raw).expm().raw - mres).max() < 1e-4
+        sym = la.GMat(m.raw + m.raw.T).expm().raw
+        assert abs(sym[0, 0] - 2288.37752914804) < 1e-8 and abs(sym[1, 2] - 5946.76670170141) < 1e-8
+        bad = la.GMat([[1, 1e9], [0, 1]]).expm().raw
+        assert np.allclose(bad, [[np.e, np.e * 1e9], [0, np.e]], rtol=1e-14)
+        z = la.GMatComplex([[0, 1j, 1], [2, 0, -1j], [0, 0, 1]]).expm().raw
+        assert abs(z[0, 0] - (0.83373 + 0.98890j)) < 1e-4 and abs(z[1, 2] - (1.85841 - 1.47252j)) < 1e-4
+        d = la.GeneralMatrix(np.diag([np.pi * 1j, 5, 1]).astype(np.complex128), flags=la.MatrixFlags.Triangular)
+        assert np.allclose(d.expm().raw, np.diag([-1, np.e ** 5, np.e]), rtol=1e-14, atol=1e-14)
+        c = la.GMatComplex([[1.0, 2.0], [-1.0, 3.0]])
+        assert np.abs(la.expm(la.GMatComplex(1j * c.raw)).raw -
+                      np.array([[0.42645930 + 1.89217551j, -2.13721484 - 0.97811252j],
+                                [1.06860742 + 0.48905626j, -1.71075555 + 0.91406299j]])).max() < 1e-5
+        assert np.allclose(la.cosm(c).raw + 1j * la.sinm(c).raw, la.expm(la.GMatComplex(1j * c.raw)).raw, atol=1e-13)
+        a = la.GMat([[1.0, 3.0], [1.0, 4.0]])
+        assert np.abs(la.sinhm(a).raw - np.array([[10.57300653, 39.28826594], [13.09608865, 49.86127247]])).max() < 1e-6
+        assert np.allclose(la.tanhm(a).raw, la.sinhm(a).raw @ np.linalg.inv(la.coshm(a).raw), rtol=1e-11)
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+@pytest.mark.parametrize("n,scale", [(5, 0.05), (9, 0.6), (24, 2.0), (40, 12.0),      # host chain
+                                     (64, 0.02), (100, 1.5), (200, 30.0), (333, 8.0)])  # resident chain
+def test_expm_matches_the_oracle_over_all_pade_degrees(dt, n, scale, product_abi):
+    """The product's expm (host chain below order 64, device-resident chain from there) against
+    the CPU restatement of the reference's algorithm on the same input."""
+    rng = np.random.default_rng(31 + n)
+    a = _rand(rng, (n, n), dt) * (scale / np.sqrt(n))
+    ref = expm_ref.expm(a.astype(np.complex128 if np.iscomplexobj(a) else np.float64))
+    with la.use_backend(product_abi):
+        got = la.GeneralMatrix(a).expm().raw
+    tol = 2e-4 if np.dtype(dt) == np.float32 else 1e-11
+    assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol
+
+
+def test_expm_resident_chain_equals_the_host_chain(product_abi):
+    rng = np.random.default_rng(77)
+    n = 150
+    for dt, scale in ((np.float64, 20.0), (np.complex128, 3.0)):
+        a = la.GeneralMatrix(_rand(rng, (n, n), dt) * (scale / np.sqrt(n)))
+        with la.use_backend(product_abi):
+            host = a._expm_host()
+            res = a._expm_resident()
+        assert np.linalg.norm(host - res) / np.linalg.norm(host) < 1e-12
+
+
+@pytest.mark.parametrize("dt", DTYPES, ids=IDS)
+def test_geadd_and_geabs_on_resident_matrices(dt, product_abi):
+    rng = np.random.default_rng(41)
+    n = 77
+    a, b = _rand(rng, (n, n), dt), _rand(rng, (n, n), dt)
+    with la.use_backend(product_abi):
+        with la._DeviceChain(ffi.LETTER[np.dtype(dt)], n, dt) as dc:
+            ha, hb = dc.matrix(), dc.matrix()
+            dc.upload(ha, a)
+            dc.upload(hb, b)
+            dc.axpby(hb, 2.5, ha, -0.75)
+            got = dc.download(hb, n, n)
+            assert np.allclose(got, 2.5 * a - 0.75 * b, rtol=0, atol=2e-6 if np.dtype(dt) == np.float32 else 1e-15)
+            dc.axpby(hb, -1.0, ha)                     # beta = 0: B is not read (NaN-safe)
+            assert np.array_equal(dc.download(hb, n, n), -a)
+            dc.absolute(hb, ha)
+            absref = np.abs(a).astype(dt)
+            assert np.allclose(dc.download(hb, n, n), absref, rtol=1e-6 if np.dtype(dt) == np.float32 else 1e-15)
+            assert abs(dc.norm(ha, "O") - np.abs(a).sum(axis=0).max()) < 1e-4 * n
