@@ -341,7 +341,28 @@ def time_other_types():
             ((A.conj() @ r).norm() / (A.norm() * r.norm())).item())
         del A, b, W, X
         torch.cuda.empty_cache()
+    out.update(time_expm())
     return out
+
+
+def time_expm(n=4096):
+    """A consumer of the path that is a pure chain of products and one solve:
+    the reference's expm (src/linalg/expm.cr) on device-resident operands, host matrix in, host
+    matrix out; checked through exp(A) exp(-A) = I."""
+    import time
+
+    import numpy as np
+
+    from linalg_b200 import la
+    rng = np.random.default_rng(20261110)
+    A = la.GeneralMatrix(np.asfortranarray((rng.random((n, n)) - 0.5) * (8.0 / np.sqrt(n))))
+    A.expm()                                           # warm-up
+    t0 = time.perf_counter()
+    E = A.expm()
+    ms = (time.perf_counter() - t0) * 1e3
+    Em = la.GeneralMatrix(-A.raw).expm()
+    err = float(np.abs((E * Em).raw - np.eye(n)).max())
+    return {"expm_n": n, "expm_ms_host_in_host_out": ms, "expm_times_expm_of_minus_a_minus_identity": err}
 
 
 def dist_legs(world, rank):
