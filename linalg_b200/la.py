@@ -653,14 +653,15 @@ class GeneralMatrix:
         if schur_fact:
             raise NotImplementedError("expm(schur_fact: true) needs ?gees (outside the hot path)")
         n = self.nrows
-        if n == 0 or float(np.abs(self.raw).sum(axis=0).max()) == 0.0:   # norm(One) == 0
-            out = GeneralMatrix.identity(n, self.dtype)
-            return out
+        resident = n >= self.EXPM_RESIDENT_FROM and hasattr(backend().cdll, "la_b200_mat_create")
+        # norm(One) == 0 (the resident chain takes the norm on the device, after its upload)
+        if n == 0 or (not resident and float(np.abs(self.raw).sum(axis=0).max()) == 0.0):
+            return GeneralMatrix.identity(n, self.dtype)
         if self.flags.upper_triangular and self.flags.lower_triangular:    # flags.diagonal?
             return GeneralMatrix(np.diag(np.exp(np.diagonal(self.raw))).astype(self.dtype))
         if n == 2:
             return GeneralMatrix(self._expm_2by2())
-        if n >= self.EXPM_RESIDENT_FROM and hasattr(backend().cdll, "la_b200_mat_create"):
+        if resident:
             return GeneralMatrix(self._expm_resident())
         return GeneralMatrix(self._expm_host())
 
@@ -819,6 +820,8 @@ class GeneralMatrix:
                 return dc.norm(x, "M", cols=1) / scale ** m
 
             norm1_a = dc.norm(A, "O")
+            if norm1_a == 0.0:
+                return np.asfortranarray(np.eye(n, dtype=dt))
             deg, s = self._expm_plan(lambda w, m: norm_am_of(power(w), m),
                                      lambda m, scale: norm_am_of(absA, m, scale, True), norm1_a)
             c = self._EXPM_PADE[deg]

@@ -214,6 +214,7 @@ def test_expm_reference_spec_vectors(product_abi):
     closed forms and the small general path)."""
     with la.use_backend(product_abi):
         assert np.array_equal(la.GMat(np.zeros((2, 2))).expm().raw, np.eye(2))
+        assert np.array_equal(la.GMat(np.zeros((80, 80))).expm().raw, np.eye(80))     # resident chain
         assert abs(la.GMat(np.ones((1, 1))).expm().raw[0, 0] - np.e) < 1e-14
         m = la.GMat([[0, 6, 0, 0], [0, 0, 6, 0], [0, 0, 0, 6], [0, 0, 0, 0]])
         mres = np.array([[1.0, 6.0, 18.0, 36.0], [0.0, 1.0, 6.0, 18.0], [0.0, 0.0, 1.0, 6.0], [0.0, 0.0, 0.0, 1.0]])
