@@ -257,17 +257,30 @@ constexpr size_t trsm_smem_bytes() {
          sizeof(T) * (size_t)TrsmCfg<T>::NB * (TrsmCfg<T>::NT + 1) + sizeof(T) * TrsmCfg<T>::NB;
 }
 
+// NT vectors per CTA (one solver thread each) and TRSM_LT threads for the loads and stores.  The
+// vectors live in shared memory (Xs[i][v]: conflict free across the solver threads) and are
+// solved by blocked substitution: eight unknowns at a time in registers, first the updates from
+// all finished unknowns (a rolled loop: one load of x_k and eight multiply-adds per step), then
+// the 8 x 8 diagonal block.  The previous form kept the whole vector in registers and unrolled
+// the full substitution — 2016 multiply-adds and as many shared-memory loads of straight-line
+// code per instantiation, executed once per launch, i.e. always from a cold instruction cache:
+// 124 us per launch for a 64 x 64 triangle and 16384 vectors, 56 % of sgetrf at N = 16384.
+constexpr int TRSM_LT = 256;
+constexpr int TRSM_BS = 8;
+
 template <typename T>
-__global__ void __launch_bounds__(TrsmCfg<T>::NT)
+__global__ void __launch_bounds__(TRSM_LT)
 trsm_base_kernel(int right, int a_lower, int op, int unit, int na, int64_t nvec, T alpha,
                  const T* __restrict__ A, int64_t lda, T* __restrict__ B, int64_t ldb) {
   constexpr int NB = TrsmCfg<T>::NB, NT = TrsmCfg<T>::NT, LDM = NB + 1, LDX = NT + 1;
+  constexpr int BS = TRSM_BS;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* Ms = reinterpret_cast<T*>(smem_raw);   // effective matrix M (see below), row pitch LDM
-  T* Xs = Ms + NB * LDM;                    // Left side staging: Xs[i * LDX + v]
+  T* Xs = Ms + NB * LDM;                    // the vectors: Xs[i * LDX + v]
   T* rdiag = Xs + NB * LDX;                 // reciprocals of M's diagonal
   // M = op(A) for Left;  M = op(A)^T for Right (x*op(A) = b  <=>  M x^T = b^T).
-  for (int idx = threadIdx.x; idx < na * na; idx += NT) {
+#pragma unroll 4
+  for (int idx = threadIdx.x; idx < na * na; idx += TRSM_LT) {
     int i = idx % na, j = idx / na;  // stored element A(i,j); only the stored triangle is read
     bool stored = a_lower ? (i >= j) : (i <= j);
     T v = stored ? A[i + (int64_t)j * lda] : zero<T>();
@@ -282,39 +295,75 @@ trsm_base_kernel(int right, int a_lower, int op, int unit, int na, int64_t nvec,
   const int64_t v0 = (int64_t)blockIdx.x * NT;
   const int nv = (int)((nvec - v0) < NT ? (nvec - v0) : NT);
   const int t = threadIdx.x;
-  T x[NB];
-  if (right) {
-#pragma unroll
-    for (int i = 0; i < NB; i++)
-      x[i] = (i < na && t < nv) ? B[v0 + t + (int64_t)i * ldb] : zero<T>();
-    __syncthreads();
-    if (t < na && !unit) rdiag[t] = recip(Ms[t * LDM + t]);
-    __syncthreads();
-  } else {
-    for (int idx = t; idx < na * nv; idx += NT) {
-      int i = idx % na, v = idx / na;
-      Xs[i * LDX + v] = B[i + (v0 + v) * ldb];
-    }
-    __syncthreads();
-    if (t < na && !unit) rdiag[t] = recip(Ms[t * LDM + t]);
-#pragma unroll
-    for (int i = 0; i < NB; i++) x[i] = (i < na && t < nv) ? Xs[i * LDX + t] : zero<T>();
-    __syncthreads();
+  const bool scale = !is_one(alpha);
+  // ---- stage alpha * b (coalesced along the contiguous direction of B)
+#pragma unroll 4
+  for (int idx = t; idx < na * nv; idx += TRSM_LT) {
+    int i, v;
+    T b;
+    if (right) { v = idx % nv; i = idx / nv; b = B[v0 + v + (int64_t)i * ldb]; }
+    else       { i = idx % na; v = idx / na; b = B[i + (v0 + v) * ldb]; }
+    Xs[i * LDX + v] = scale ? mul(alpha, b) : b;
   }
-  if (t < nv) solve_vec_regs<T, NB, LDM>(Ms, rdiag, na, eff_lower, unit != 0, alpha, x);
-  if (right) {
+  __syncthreads();
+  if (t < na && !unit) rdiag[t] = recip(Ms[t * LDM + t]);
+  __syncthreads();
+  if (t < NT && t < nv) {
+    T* xv = Xs + t;                        // this thread's vector: xv[i * LDX]
+    if (eff_lower) {
+      for (int jb = 0; jb < na; jb += BS) {
+        T xr[BS];
 #pragma unroll
-    for (int i = 0; i < NB; i++)
-      if (i < na && t < nv) B[v0 + t + (int64_t)i * ldb] = x[i];
-  } else {
+        for (int r = 0; r < BS; r++) xr[r] = jb + r < na ? xv[(jb + r) * LDX] : zero<T>();
+        for (int k = 0; k < jb; k++) {
+          const T xk = xv[k * LDX];
 #pragma unroll
-    for (int i = 0; i < NB; i++)
-      if (i < na && t < nv) Xs[i * LDX + t] = x[i];
-    __syncthreads();
-    for (int idx = t; idx < na * nv; idx += NT) {
-      int i = idx % na, v = idx / na;
-      B[i + (v0 + v) * ldb] = Xs[i * LDX + v];
+          for (int r = 0; r < BS; r++) xr[r] = fnma_(Ms[(jb + r) * LDM + k], xk, xr[r]);
+        }
+#pragma unroll
+        for (int c = 0; c < BS; c++) {
+          if (jb + c < na) {
+            if (!unit) xr[c] = mul(xr[c], rdiag[jb + c]);
+#pragma unroll
+            for (int r = c + 1; r < BS; r++)
+              if (jb + r < na) xr[r] = fnma_(Ms[(jb + r) * LDM + jb + c], xr[c], xr[r]);
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < BS; r++)
+          if (jb + r < na) xv[(jb + r) * LDX] = xr[r];
+      }
+    } else {
+      for (int jb = ((na - 1) / BS) * BS; jb >= 0; jb -= BS) {
+        T xr[BS];
+#pragma unroll
+        for (int r = 0; r < BS; r++) xr[r] = jb + r < na ? xv[(jb + r) * LDX] : zero<T>();
+        for (int k = jb + BS; k < na; k++) {
+          const T xk = xv[k * LDX];
+#pragma unroll
+          for (int r = 0; r < BS; r++)
+            if (jb + r < na) xr[r] = fnma_(Ms[(jb + r) * LDM + k], xk, xr[r]);
+        }
+#pragma unroll
+        for (int cc = 0; cc < BS; cc++) {
+          const int c = BS - 1 - cc;
+          if (jb + c < na) {
+            if (!unit) xr[c] = mul(xr[c], rdiag[jb + c]);
+#pragma unroll
+            for (int r = 0; r < c; r++) xr[r] = fnma_(Ms[(jb + r) * LDM + jb + c], xr[c], xr[r]);
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < BS; r++)
+          if (jb + r < na) xv[(jb + r) * LDX] = xr[r];
+      }
     }
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int idx = t; idx < na * nv; idx += TRSM_LT) {
+    if (right) { const int v = idx % nv, i = idx / nv; B[v0 + v + (int64_t)i * ldb] = Xs[i * LDX + v]; }
+    else       { const int i = idx % na, v = idx / na; B[i + (v0 + v) * ldb] = Xs[i * LDX + v]; }
   }
 }
 
@@ -343,7 +392,7 @@ void trsm_rec(Context& ctx, Side side, Uplo uplo, Op op, Diag diag, int64_t m, i
       attr.mark(ctx.device);
     }
     unsigned g = (unsigned)ceil_div(nvec, TRSM_NT);
-    trsm_base_kernel<T><<<g, TRSM_NT, trsm_smem_bytes<T>(), ctx.stream>>>(side == Right, uplo == Lower, (int)op,
+    trsm_base_kernel<T><<<g, TRSM_LT, trsm_smem_bytes<T>(), ctx.stream>>>(side == Right, uplo == Lower, (int)op,
                                                        diag == Unit, (int)na, nvec, alpha, A, lda,
                                                        B, ldb);
     LA_CUDA_CHECK(cudaGetLastError());
