@@ -413,8 +413,14 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   // stable set of free SMs, and the leaf's CTAs then wait for one another forever.
   const bool dmma_ok = std::is_same<T, double>::value && (lda % 2 == 0) &&
                        (((uintptr_t)A & 15) == 0);
+  // FP32: the update is the persistent 3xTF32 kernel behind two short packing launches, which
+  // hold the leaf up for a few microseconds at most (LA_B200_LU_LOOKAHEAD_F32=0 turns it off)
+  static const bool f32_la = !(getenv("LA_B200_LU_LOOKAHEAD_F32") && atoi(getenv("LA_B200_LU_LOOKAHEAD_F32")) == 0);
+  const bool tf32_ok = f32_la && std::is_same<T, float>::value && (lda % 4 == 0) &&
+                       (((uintptr_t)A & 15) == 0);
+  const double gemm_flop_per_ms = std::is_same<T, float>::value ? 230.0e9 : 33.0e9;
   static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
-  const bool lookahead = !la_disabled && ctx.allow_side_stream && dmma_ok && k >= 8192 &&
+  const bool lookahead = !la_disabled && ctx.allow_side_stream && (dmma_ok || tf32_ok) && k >= 8192 &&
                          leaf_ctas <= 96 && k > NB;
   Context* side = lookahead ? side_context(ctx) : nullptr;
   if (side) {
@@ -452,7 +458,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
     static const double model_scale = getenv("LA_B200_LU_MODEL") ? atof(getenv("LA_B200_LU_MODEL")) : 1.1;
     static const bool split_env = !(getenv("LA_B200_LU_SPLIT") && atoi(getenv("LA_B200_LU_SPLIT")) == 0);
     const double h = (double)(m - j1) / 16384.0;
-    const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / 33.0e9;
+    const double upd_ms = 2.0 * (double)(m - j1) * (double)(nr - jb1) * (double)jb / gemm_flop_per_ms;
     const double pan_free_ms = 1.5 + 0.3 * h;
     const double pan_tight_ms = model_scale * (1.6 + 0.9 * h);
     // Steps whose update is shorter than the next panel are bound by the chain
@@ -524,7 +530,7 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
         if (ctx.on_block_final) ctx.on_block_final(j0, j0 + jb);
       }
       const double panel_ms = side_sms > ctas1 + 16 ? pan_free_ms : pan_tight_ms;
-      const double flop_per_ms = 33.0e9 * (double)(ctx.sm_count - side_sms) / 148.0;
+      const double flop_per_ms = gemm_flop_per_ms * (double)(ctx.sm_count - side_sms) / 148.0;
       int64_t c1 = (int64_t)(panel_ms * flop_per_ms / (2.0 * (double)mr * (double)jb));
       c1 = round_up(c1 > 0 ? c1 : 1, (int64_t)128);
       if (c1 + 1024 >= rest) c1 = rest;

@@ -110,6 +110,32 @@ def test_getrf_probe_residual_at_scale(n):
     assert torch.tril(M, -1).abs().max().item() <= 1.0 + 1e-14     # partial pivoting: |l_ij| <= 1
 
 
+@pytest.mark.parametrize("m,n", [(8192, 8192), (16384, 16384), (12000, 9000), (9000, 12000)])
+def test_sgetrf_probe_residual_at_scale(m, n):
+    # FP32 LU with look-ahead (the 3xTF32 trailing update beside the next panel on a side stream)
+    g = torch.Generator(device="cuda").manual_seed(60 + m % 7)
+    A0 = torch.rand((n, m), dtype=torch.float32, device="cuda", generator=g)     # torch view of m x n
+    W = A0.clone()
+    k = min(m, n)
+    ipiv = torch.zeros(k, dtype=torch.int32, device="cuda")
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    dev.getrf(m, n, W, m, ipiv, info)
+    assert info.item() == 0
+    piv = ipiv.cpu().numpy().astype(np.int64) - 1
+    assert piv.min() >= 0 and piv.max() < m and np.all(piv >= np.arange(k))
+    perm = np.arange(m)
+    for i, p in enumerate(piv):
+        perm[i], perm[p] = perm[p], perm[i]
+    X = torch.rand((n, 8), dtype=torch.float64, device="cuda", generator=g) - 0.5
+    M = W.T.double()                                   # math view of the factors (m x n)
+    L = torch.tril(M[:, :k], -1) + torch.eye(m, k, dtype=torch.float64, device="cuda")
+    U = torch.triu(M[:k, :])
+    PAx = (A0.T.double() @ X)[torch.from_numpy(perm).cuda()]
+    rel = ((PAx - L @ (U @ X)).abs().max() / (A0.abs().max().double() * X.abs().sum(dim=0).max())).item()
+    assert rel < 2e-5, rel
+    assert torch.tril(M[:, :k], -1).abs().max().item() <= 1.0 + 1e-6
+
+
 @pytest.mark.parametrize("n", [8192, 16384])
 def test_potrf_probe_residual_at_scale(n):
     G = _rand((n, n), 8)
