@@ -418,6 +418,8 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   static const bool f32_la = !(getenv("LA_B200_LU_LOOKAHEAD_F32") && atoi(getenv("LA_B200_LU_LOOKAHEAD_F32")) == 0);
   const bool tf32_ok = f32_la && std::is_same<T, float>::value && (lda % 4 == 0) &&
                        (((uintptr_t)A & 15) == 0);
+  // (complex128 was measured with the same arrangement and did not gain: 95.9 against 93.0 ms at
+  // N = 8192, 470 against 456 ms at 16384; it stays on the main stream)
   const double gemm_flop_per_ms = std::is_same<T, float>::value ? 230.0e9 : 33.0e9;
   static const bool la_disabled = getenv("LA_B200_NO_LOOKAHEAD") != nullptr;
   const bool lookahead = !la_disabled && ctx.allow_side_stream && (dmma_ok || tf32_ok) && k >= 8192 &&
