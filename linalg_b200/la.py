@@ -415,13 +415,31 @@ class GeneralMatrix:
             eps = max(self.tolerance(), ot)
         return bool(np.all(np.abs(self.raw - o) <= eps))
 
+    def _clear_triangle(self, upper):
+        """Zero the strictly upper / lower triangle in place through ?laset_ (the
+        reference's `tril!` / `triu!` are scalar-callback loops, matrix.cr:650-663): ?laset on
+        the sub-matrix shifted by one column / row sets exactly the strict triangle."""
+        m, n = self.raw.shape
+        if m == 0 or n == 0 or (upper and n < 2) or (not upper and m < 2):
+            return
+        zero = np.zeros(1, dtype=self.dtype)
+        fn = backend().lapack("laset", self.letter)
+        item = self.raw.itemsize
+        base = self.raw.ctypes.data
+        if upper:   # strictly upper part of A = upper triangle (with diagonal) of A[:, 1:]
+            sub = base + m * item
+            fn(b"U", _ci(min(m, n - 1)), _ci(n - 1), ffi.ptr(zero), ffi.ptr(zero), sub, _ci(m))
+        else:       # strictly lower part of A = lower triangle (with diagonal) of A[1:, :]
+            sub = base + item
+            fn(b"L", _ci(m - 1), _ci(min(n, m - 1)), ffi.ptr(zero), ffi.ptr(zero), sub, _ci(m))
+
     def tril_(self):  # matrix.cr:650-663
-        self.raw[:] = np.tril(self.raw)
+        self._clear_triangle(upper=True)
         self.flags = MatrixFlags.LowerTriangular
         return self
 
     def triu_(self):
-        self.raw[:] = np.triu(self.raw)
+        self._clear_triangle(upper=False)
         self.flags = MatrixFlags.UpperTriangular
         return self
 
@@ -969,9 +987,15 @@ class GeneralMatrix:
             uplo = b"U"
             _lapack("potrf", L, uplo, n, self.raw, n)
             _lapack("potri", L, uplo, n, self.raw, n)
-            # adjust_symmetric: mirror the computed triangle
-            iu = np.triu_indices(n, 1)
-            self.raw.T[iu] = self.raw[iu].conj()
+            # adjust_symmetric: mirror the computed (upper) triangle, block by block (plain slices:
+            # index arrays over the whole triangle cost more than the inversion itself)
+            bs = 512
+            for j0 in range(0, n, bs):
+                j1 = min(n, j0 + bs)
+                d = self.raw[j0:j1, j0:j1]
+                d[:] = np.triu(d) + np.triu(d, 1).conj().T
+                if j1 < n:
+                    self.raw[j1:, j0:j1] = self.raw[j0:j1, j1:].conj().T
         else:
             ipiv = np.zeros(n, dtype=np.int32)
             _lapack("getrf", L, n, n, self.raw, n, ipiv)
