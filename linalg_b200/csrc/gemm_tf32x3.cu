@@ -33,7 +33,6 @@ constexpr int S_STAGES = 2;
 constexpr int S_A_BYTES = SM_ * SK_ * 4;               // 16 KB per (hi or lo)
 constexpr int S_B_BYTES = SN_ * SK_ * 4;               // 32 KB per (hi or lo)
 constexpr int S_STAGE_BYTES = 2 * S_A_BYTES + 2 * S_B_BYTES;  // 96 KB
-constexpr int S_SMEM_BYTES = S_STAGES * S_STAGE_BYTES + 1024 + 256;
 constexpr int S_THREADS = 384;                         // 4 control warps + 8 epilogue warps
 constexpr int S_TMEM_COLS = 512;                       // two 256-column accumulators
 // The tensor core truncates when it adds into its FP32 accumulator; on same-signed data that is a

@@ -88,27 +88,6 @@ template <> __device__ __forceinline__ void ll_put<zcomplex>(LLPacket* p, zcompl
   ll_store(p, (unsigned long long)__double_as_longlong(v.x), (unsigned long long)seq << 32);
   ll_store(p + 1, (unsigned long long)__double_as_longlong(v.y), (unsigned long long)seq << 32);
 }
-template <typename T> __device__ __forceinline__ T ll_get(const LLPacket* p, unsigned seq);
-template <> __device__ __forceinline__ double ll_get<double>(const LLPacket* p, unsigned seq) {
-  unsigned long long d, t;
-  ll_wait(p, seq, d, t);
-  return __longlong_as_double((long long)d);
-}
-template <> __device__ __forceinline__ float ll_get<float>(const LLPacket* p, unsigned seq) {
-  unsigned long long d, t;
-  ll_wait(p, seq, d, t);
-  return __uint_as_float((unsigned)d);
-}
-template <> __device__ __forceinline__ zcomplex ll_get<zcomplex>(const LLPacket* p, unsigned seq) {
-  unsigned long long d, t;
-  zcomplex v;
-  ll_wait(p, seq, d, t);
-  v.x = __longlong_as_double((long long)d);
-  ll_wait(p + 1, seq, d, t);
-  v.y = __longlong_as_double((long long)d);
-  return v;
-}
-
 template <typename T> __device__ __forceinline__ T from_words(const unsigned long long* d);
 template <> __device__ __forceinline__ double from_words<double>(const unsigned long long* d) {
   return __longlong_as_double((long long)d[0]);
@@ -177,17 +156,6 @@ typedef unsigned long long ukey;
 __device__ __forceinline__ ukey key_of(double absval) {
   const ukey k = (ukey)__double_as_longlong(absval);
   return k > 0x7ff0000000000000ull ? 0ull : k;
-}
-__device__ __forceinline__ void argmax_combine(ukey& v, int& i, ukey ov, int oi) {
-  if (oi != 0x7fffffff && (i == 0x7fffffff || ov > v || (ov == v && oi < i))) { v = ov; i = oi; }
-}
-__device__ __forceinline__ void warp_argmax(ukey& v, int& i) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const ukey ov = __shfl_xor_sync(0xffffffffu, v, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, i, o);
-    argmax_combine(v, i, ov, oi);
-  }
 }
 
 #ifdef LA_PANEL_TRACE
