@@ -292,3 +292,35 @@ def test_tall_gram_products_match_a_double_precision_reference(dtype, p, q, m):
     assert float((S.to(hi) - ref).abs().max()) <= tol * float(ref.abs().max())
     if not (dtype.is_complex and max(p, q) > 32):
         assert path == 4, "the tall-gram kernel was not taken"
+
+
+@pytest.mark.parametrize("dt", [torch.float64, torch.float32, torch.complex128], ids=["d", "s", "z"])
+@pytest.mark.parametrize("m,n,pad", [(300, 64, 8), (1500, 96, 3), (9000, 40, 8), (20000, 33, 5), (4100, 700, 16)])
+def test_getrf_leaves_padding_rows_alone(dt, m, n, pad):
+    # the LU leaf writes every row to its final position once, at the end of the launch (rows do
+    # not move in between): with lda > m the rows between m and lda must come back untouched, and
+    # the factors must reproduce P A (all leaf forms: one CTA, 512-thread and 256-thread CTAs,
+    # several rows per thread)
+    lda = m + pad
+    g = torch.Generator(device="cuda").manual_seed(m + n)
+    full = torch.rand((n, lda), dtype=dt, device="cuda", generator=g) - 0.5     # torch view: n x lda
+    full[:, m:] = float("nan")
+    A0 = full[:, :m].clone()
+    W = full.clone()
+    k = min(m, n)
+    ipiv = torch.zeros(k, dtype=torch.int32, device="cuda")
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    dev.getrf(m, n, W, lda, ipiv, info)
+    assert info.item() == 0
+    assert torch.isnan(W[:, m:].real).all() and not torch.isnan(W[:, :m].real).any()
+    piv = ipiv.cpu().numpy().astype(np.int64) - 1
+    perm = np.arange(m)
+    for i, p in enumerate(piv):
+        perm[i], perm[p] = perm[p], perm[i]
+    hp = torch.complex128 if dt == torch.complex128 else torch.float64
+    M = W[:, :m].T.to(hp)                                                        # m x n factors
+    L = torch.tril(M[:, :k], -1) + torch.eye(m, k, dtype=hp, device="cuda")
+    U = torch.triu(M[:k, :])
+    PA = A0.T.to(hp)[torch.from_numpy(perm).cuda()]
+    tol = 5e-5 if dt == torch.float32 else 1e-12
+    assert ((PA - L @ U).abs().max() / A0.abs().max()).item() < tol * max(1, n // 50)
