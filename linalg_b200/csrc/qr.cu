@@ -25,6 +25,11 @@ constexpr int QR_MAX_JB = 32;
 constexpr int QR_MAX_CTAS = 640;
 constexpr size_t QR_SMEM_BUDGET = 200 * 1024;
 
+struct __align__(16) QrLL {
+  unsigned long long data;
+  unsigned long long tag;
+};
+
 template <typename T>
 struct QrExchange {
   unsigned int barrier;
@@ -34,6 +39,11 @@ struct QrExchange {
   // streamed panels that take two reflectors per pass: the sums against column j+1 and row j+1
   T part2[2][QR_MAX_CTAS][QR_MAX_JB];
   T rowj2[2][QR_MAX_JB];
+  // shared-memory panels: the same sums and row j as 16-byte (payload, tag) packets that the
+  // readers poll — no grid barrier between a column's sums and their reduction (two words per
+  // value: complex); cleared once per factorisation, tags grow from launch to launch
+  QrLL pll[2][QR_MAX_CTAS][QR_MAX_JB * 2];
+  QrLL rowll[2][QR_MAX_JB * 2];
 };
 
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
@@ -50,6 +60,46 @@ __device__ __forceinline__ void grid_barrier(unsigned* counter, unsigned target)
     __threadfence();
   }
   __syncthreads();
+}
+
+// tagged packets (the protocol of lu_panel.cu): a packet is valid when the upper half of its tag
+// is the step's sequence number; one vector store, polled with volatile loads
+__device__ __forceinline__ void qll_store(QrLL* p, unsigned long long data, unsigned seq) {
+  asm volatile("st.global.cg.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(data),
+               "l"((unsigned long long)seq << 32) : "memory");
+}
+__device__ __forceinline__ unsigned long long qll_wait(const QrLL* p, unsigned seq) {
+  unsigned long long d, t;
+  do {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(d), "=l"(t) : "l"(p) : "memory");
+  } while ((unsigned)(t >> 32) != seq);
+  return d;
+}
+template <typename T> struct QllWords { static constexpr int N = 1; };
+template <> struct QllWords<zcomplex> { static constexpr int N = 2; };
+template <typename T> __device__ __forceinline__ void qll_put(QrLL* p, T v, unsigned seq);
+template <> __device__ __forceinline__ void qll_put<double>(QrLL* p, double v, unsigned seq) {
+  qll_store(p, (unsigned long long)__double_as_longlong(v), seq);
+}
+template <> __device__ __forceinline__ void qll_put<float>(QrLL* p, float v, unsigned seq) {
+  qll_store(p, (unsigned long long)__float_as_uint(v), seq);
+}
+template <> __device__ __forceinline__ void qll_put<zcomplex>(QrLL* p, zcomplex v, unsigned seq) {
+  qll_store(p, (unsigned long long)__double_as_longlong(v.x), seq);
+  qll_store(p + 1, (unsigned long long)__double_as_longlong(v.y), seq);
+}
+template <typename T> __device__ __forceinline__ T qll_get(const QrLL* p, unsigned seq);
+template <> __device__ __forceinline__ double qll_get<double>(const QrLL* p, unsigned seq) {
+  return __longlong_as_double((long long)qll_wait(p, seq));
+}
+template <> __device__ __forceinline__ float qll_get<float>(const QrLL* p, unsigned seq) {
+  return __uint_as_float((unsigned)qll_wait(p, seq));
+}
+template <> __device__ __forceinline__ zcomplex qll_get<zcomplex>(const QrLL* p, unsigned seq) {
+  zcomplex v;
+  v.x = __longlong_as_double((long long)qll_wait(p, seq));
+  v.y = __longlong_as_double((long long)qll_wait(p + 1, seq));
+  return v;
 }
 
 template <typename T> __device__ __forceinline__ void st_cg(T* p, T v) { __stcg(p, v); }
@@ -109,7 +159,7 @@ __device__ __forceinline__ void householder(T alpha, double xnorm2, T& beta_out,
 template <typename T>
 __global__ void __launch_bounds__(QR_NT)
 qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
-                QrExchange<T>* xch, int64_t rpc, int use_smem) {
+                QrExchange<T>* xch, int64_t rpc, int use_smem, unsigned seq_base) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ T s_f[QR_MAX_JB];       // f_c = conj(tau) * w_c
   __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
@@ -128,8 +178,17 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
   if (use_smem) {
     base = reinterpret_cast<T*>(smem_raw);
     pitch = rpc;
-    for (int c = 0; c < jb; c++)
-      for (int64_t r = tid; r < nr; r += QR_NT) base[c * pitch + r] = A[rs + r + (int64_t)c * lda];
+    // (eight columns per trip, all loads of a trip in flight before the first store: column by
+    // column this loop was up to 64 dependent rounds of global-memory latency per launch)
+    for (int64_t r = tid; r < nr; r += QR_NT)
+      for (int c0 = 0; c0 < jb; c0 += 8) {
+        T v[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = c0 + i < jb ? A[rs + r + (int64_t)(c0 + i) * lda] : zero<T>();
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          if (c0 + i < jb) base[(c0 + i) * pitch + r] = v[i];
+      }
     __syncthreads();
   } else {
     base = A + rs;
@@ -137,28 +196,29 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
   }
 
   const int kmax = (int)(mp < jb ? mp : jb);
-  unsigned target = 0;
+  constexpr int QW = QllWords<T>::N;
   for (int j = 0; j < kmax; j++) {
     const int par = j & 1;
-    // ---- partial sums s_c over owned rows r > j, one warp per column
+    const unsigned seq = seq_base + (unsigned)j + 1u;
+    // ---- partial sums s_c over owned rows r > j, one warp per column, published as packets
     for (int c = j + warp; c < jb; c += QR_NT / 32) {
       T acc = zero<T>();
       int64_t rbeg = j + 1 - rs; if (rbeg < 0) rbeg = 0;
       for (int64_t r = rbeg + lane; r < nr; r += 32)
         acc = fma_(conj_(base[j * pitch + r]), base[c * pitch + r], acc);
       acc = warp_sum<T>(acc);
-      if (lane == 0) st_cg<T>(&xch->part[par][blockIdx.x][c], acc);
+      if (lane == 0) qll_put<T>(&xch->pll[par][blockIdx.x][c * QW], acc, seq);
     }
     if (j >= rs && j < rs + nr && tid >= j && tid < jb)
-      st_cg<T>(&xch->rowj[par][tid], base[tid * pitch + (j - rs)]);
-    target += (unsigned)G;
-    grid_barrier(&xch->barrier, target);
-    // ---- reduce the partials: 8 groups x 32 columns
+      qll_put<T>(&xch->rowll[par][tid * QW], base[tid * pitch + (j - rs)], seq);
+    // ---- reduce the partials of all CTAs as they arrive: 8 groups x 32 columns.  (A CTA can be
+    // two columns ahead of no other: it publishes column j+1 only after it has read every CTA's
+    // column j, so the two buffers of a parity never hold live data of different columns.)
     {
       const int c = tid & 31, grp = tid >> 5;
       T s = zero<T>();
       if (c >= j && c < jb)
-        for (int g = grp; g < G; g += QR_NT / 32) s = add(s, ld_cg<T>(&xch->part[par][g][c]));
+        for (int g = grp; g < G; g += QR_NT / 32) s = add(s, qll_get<T>(&xch->pll[par][g][c * QW], seq));
       s_red[grp][c] = s;
     }
     __syncthreads();
@@ -168,7 +228,7 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
       if (c >= j && c < jb)
         for (int g = 0; g < QR_NT / 32; g++) s = add(s, s_red[g][c]);
       // every lane needs alpha, s_j
-      T rj = (c >= j && c < jb) ? ld_cg<T>(&xch->rowj[par][c]) : zero<T>();
+      T rj = (c >= j && c < jb) ? qll_get<T>(&xch->rowll[par][c * QW], seq) : zero<T>();
       T alpha, sj;
       if constexpr (Traits<T>::is_complex) {
         alpha.x = __shfl_sync(0xffffffffu, rj.x, j); alpha.y = __shfl_sync(0xffffffffu, rj.y, j);
@@ -211,8 +271,12 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
     __syncthreads();
   }
   if (use_smem) {
-    for (int c = 0; c < jb; c++)
-      for (int64_t r = tid; r < nr; r += QR_NT) A[rs + r + (int64_t)c * lda] = base[c * pitch + r];
+    for (int64_t r = tid; r < nr; r += QR_NT)
+      for (int c0 = 0; c0 < jb; c0 += 8) {
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+          if (c0 + i < jb) A[rs + r + (int64_t)(c0 + i) * lda] = base[(c0 + i) * pitch + r];
+      }
   }
 }
 
@@ -648,7 +712,7 @@ bool qr_panel_is_tall(Context& ctx, int64_t mp) {
 // factor in Tout (streamed 8-column panels); otherwise the caller builds them.
 template <typename T>
 bool qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExchange<T>* xch,
-              T* Vc = nullptr, int64_t ldv = 0, T* Tout = nullptr, int64_t ldt = 0) {
+              unsigned& seq, T* Vc = nullptr, int64_t ldv = 0, T* Tout = nullptr, int64_t ldt = 0) {
   int64_t G = ceil_div(mp, 512);
   if (G > ctx.sm_count) G = ctx.sm_count;
   if (G < 1) G = 1;
@@ -682,7 +746,9 @@ bool qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
     }
     return false;
   }
-  void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem};
+  unsigned seq_base = seq;
+  seq += 64;
+  void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem, &seq_base};
   LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_kernel<T>, dim3((unsigned)G),
                                             dim3(QR_NT), args, smem, ctx.stream));
   return false;
@@ -767,6 +833,7 @@ struct QrBlock {
   T* W; T* W2; int64_t ldw;  // (columns to update) x QR_NB
   int64_t b0;              // first column (= first row) of the block
   int leaf;                // leaf panel width
+  unsigned seq;            // packet sequence of the shared-memory panel launches (this call)
 };
 
 // C <- H^H C with H = I - V T V^H (V: mrows x jb, unit lower trapezoidal, clean; T: jb x jb).
@@ -804,7 +871,7 @@ void qr_rec(Context& ctx, int64_t m, T* A, int64_t lda, T* tau, int64_t j0, int6
   const int64_t mp = m - j0;
   if (jn <= w.leaf) {
     T* P = A + j0 + j0 * lda;
-    if (qr_panel<T>(ctx, mp, (int)jn, P, lda, tau + j0, w.xch, Vn, w.ldv, Tn, QR_NB)) return;
+    if (qr_panel<T>(ctx, mp, (int)jn, P, lda, tau + j0, w.xch, w.seq, Vn, w.ldv, Tn, QR_NB)) return;
     const int64_t kk = mp < jn ? mp : jn;      // reflectors actually produced
     copy_triangle<T>(ctx, Lower, true, mp, jn, P, lda, Vn, w.ldv);
     gemm<T>(ctx, OpC, OpN, kk, kk, mp, one<T>(), Vn, w.ldv, Vn, w.ldv, zero<T>(), w.G, QR_MAX_JB);
@@ -851,6 +918,11 @@ void geqrf_ex(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, T* d_tau, i
   Arena::Mark mk = ctx.arena.mark();
   QrBlock<T> w;
   w.xch = (QrExchange<T>*)ctx.arena.alloc(sizeof(QrExchange<T>));
+  // the packet area comes out of the arena with whatever was there: cleared in stream order, and
+  // the tags of this call start above every cleared value
+  LA_CUDA_CHECK(cudaMemsetAsync(&w.xch->pll[0][0][0], 0,
+                                sizeof(w.xch->pll) + sizeof(w.xch->rowll), ctx.stream));
+  w.seq = 64;
   w.ldv = round_up(m, 16);
   w.Vc = ctx.alloc<T>(w.ldv * QR_NB);
   w.Tb = ctx.alloc<T>(QR_NB * QR_NB);
