@@ -66,3 +66,52 @@ def test_expm_matches_scipy_over_all_pade_degrees(n, scale, kind):
         a = a + 1j * (rng.random((n, n)) - 0.5) * scale / np.sqrt(n)
     got, ref = R.expm(a), sl.expm(a)
     assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < 1e-12
+
+
+# ---- the host mirror (linalg_b200/la.py) through the ORACLE library: the degree selection, the
+# norm estimates and the Pade sums of la.py are host logic and are checked here without a GPU
+from linalg_b200 import la  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def cpu_abi():
+    from oracle import openblas_ref
+    return openblas_ref.abi()
+
+
+@pytest.mark.parametrize("n,scale", [(3, 0.01), (5, 0.2), (8, 1.0), (12, 3.0), (20, 10.0), (70, 25.0)])
+@pytest.mark.parametrize("kind", ["real", "complex", "single"])
+def test_la_expm_host_chain_follows_the_reference_algorithm(n, scale, kind, cpu_abi):
+    rng = np.random.default_rng(200 + n)
+    a = (rng.random((n, n)) - 0.5) * scale / np.sqrt(n)
+    if kind == "complex":
+        a = a + 1j * (rng.random((n, n)) - 0.5) * scale / np.sqrt(n)
+    if kind == "single":
+        a = a.astype(np.float32)
+    ref = R.expm(a.astype(np.complex128 if np.iscomplexobj(a) else np.float64))
+    with la.use_backend(cpu_abi):
+        got = la.GeneralMatrix(a).expm().raw
+    tol = 5e-4 if kind == "single" else 1e-11
+    assert got.dtype == a.dtype
+    assert np.linalg.norm(got - ref) / np.linalg.norm(ref) < tol
+
+
+def test_la_expm_special_cases_and_matfun(cpu_abi):
+    with la.use_backend(cpu_abi):
+        assert np.array_equal(la.GMat(np.zeros((5, 5))).expm().raw, np.eye(5))
+        assert _close(la.GMat(M4).expm().raw, M4_EXP, 1e-13)
+        assert _close(la.GMat(M4 + M4.T).expm().raw, SYM_EXP, 1e-12)
+        assert _close(la.GMat([[1, 1e9], [0, 1]]).expm().raw, [[np.e, np.e * 1e9], [0, np.e]], 1e-14)
+        up = la.GeneralMatrix(np.array([[1.0, 2.0], [0.0, 3.0]]), flags=la.MatrixFlags.UpperTriangular)
+        assert _close(up.expm().raw, R.expm(up.raw), 1e-14)                  # expmT2by2
+        d = la.GeneralMatrix(np.diag([0.5, -1.0, 2.0]), flags=la.MatrixFlags.Triangular)
+        assert _close(d.expm().raw, np.diag(np.exp([0.5, -1.0, 2.0])), 1e-15)
+        with pytest.raises(NotImplementedError):
+            la.GMat(M4).expm(schur_fact=True)
+        with pytest.raises(ValueError):
+            la.GMat(np.ones((2, 3))).expm()
+        m = la.GMatComplex([[1.0, 2.0], [-1.0, 3.0]])
+        assert _close(la.cosm(m).raw + 1j * la.sinm(m).raw, R.expm(1j * m.raw), 1e-13)
+        a = la.GMat([[1.0, 3.0, 0.5], [1.0, 4.0, -1.0], [0.2, 0.1, 0.3]])
+        for f in ("cosm", "sinm", "tanm", "coshm", "sinhm", "tanhm"):
+            assert _close(getattr(la, f)(a).raw, getattr(R, f)(a.raw), 1e-11), f
