@@ -156,10 +156,13 @@ __device__ __forceinline__ void householder(T alpha, double xnorm2, T& beta_out,
 }
 
 // QR of an mp x jb panel (mp >= 1, jb <= 32), reflectors left in place, tau[0..kmax).
-template <typename T>
+// SMEM: the CTA's row slice is held in shared memory for the whole launch (a compile-time switch,
+// so that the panel is addressed with shared-memory loads and stores, not generic ones)
+template <typename T, bool SMEM>
 __global__ void __launch_bounds__(QR_NT)
 qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restrict__ tau,
-                QrExchange<T>* xch, int64_t rpc, int use_smem, unsigned seq_base) {
+                QrExchange<T>* xch, int64_t rpc, unsigned seq_base) {
+  constexpr int use_smem = SMEM ? 1 : 0;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ T s_f[QR_MAX_JB];       // f_c = conj(tau) * w_c
   __shared__ T s_red[QR_NT / 32][QR_MAX_JB];
@@ -757,8 +760,8 @@ bool qr_panel(Context& ctx, int64_t mp, int jb, T* A, int64_t lda, T* tau, QrExc
   }
   unsigned seq_base = seq;
   seq += 64;
-  void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &use_smem, &seq_base};
-  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_kernel<T>, dim3((unsigned)G),
+  void* args[] = {&mp, &jb, &A, &lda, &tau, &xch, &rpc, &seq_base};
+  LA_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)qr_panel_kernel<T, true>, dim3((unsigned)G),
                                             dim3(QR_NT), args, smem, ctx.stream));
   return false;
 }
@@ -767,7 +770,7 @@ template <typename T>
 void ensure_attrs(Context& ctx) {
   static DeviceOnce done;
   if (done.pending(ctx.device)) {
-    LA_CUDA_CHECK(cudaFuncSetAttribute(qr_panel_kernel<T>,
+    LA_CUDA_CHECK(cudaFuncSetAttribute(qr_panel_kernel<T, true>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)QR_SMEM_BUDGET));
     done.mark(ctx.device);
