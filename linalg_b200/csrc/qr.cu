@@ -155,6 +155,13 @@ __device__ __forceinline__ void householder(T alpha, double xnorm2, T& beta_out,
   }
 }
 
+#ifdef LA_PANEL_TRACE
+__device__ long long g_qr_trace[64 * 8];
+#define QTRACE(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0 && j < 64) g_qr_trace[j * 8 + (slot)] = clock64(); } while (0)
+#else
+#define QTRACE(slot) do { } while (0)
+#endif
+
 // QR of an mp x jb panel (mp >= 1, jb <= 32), reflectors left in place, tau[0..kmax).
 // SMEM: the CTA's row slice is held in shared memory for the whole launch (a compile-time switch,
 // so that the panel is addressed with shared-memory loads and stores, not generic ones)
@@ -203,17 +210,36 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
   for (int j = 0; j < kmax; j++) {
     const int par = j & 1;
     const unsigned seq = seq_base + (unsigned)j + 1u;
+    QTRACE(0);
     // ---- partial sums s_c over owned rows r > j, one warp per column, published as packets
-    for (int c = j + warp; c < jb; c += QR_NT / 32) {
-      T acc = zero<T>();
+    // (a warp's up to four columns c0, c0+8, ... are summed together: the element of column j is
+    // loaded once per row and the four chains of multiply-adds and their shuffle reductions
+    // overlap — one column after the other this phase was 40 % of a step)
+    {
+      constexpr int NWQ = QR_NT / 32, CPW = QR_MAX_JB / NWQ;
+      const int c0 = j + warp;
+      T acc[CPW];
+#pragma unroll
+      for (int q = 0; q < CPW; q++) acc[q] = zero<T>();
       int64_t rbeg = j + 1 - rs; if (rbeg < 0) rbeg = 0;
-      for (int64_t r = rbeg + lane; r < nr; r += 32)
-        acc = fma_(conj_(base[j * pitch + r]), base[c * pitch + r], acc);
-      acc = warp_sum<T>(acc);
-      if (lane == 0) qll_put<T>(&xch->pll[par][blockIdx.x][c * QW], acc, seq);
+#pragma unroll 4
+      for (int64_t r = rbeg + lane; r < nr; r += 32) {
+        const T x = conj_(base[j * pitch + r]);
+#pragma unroll
+        for (int q = 0; q < CPW; q++)
+          if (c0 + q * NWQ < jb) acc[q] = fma_(x, base[(c0 + q * NWQ) * pitch + r], acc[q]);
+      }
+#pragma unroll
+      for (int q = 0; q < CPW; q++) acc[q] = warp_sum<T>(acc[q]);
+      if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < CPW; q++)
+          if (c0 + q * NWQ < jb) qll_put<T>(&xch->pll[par][blockIdx.x][(c0 + q * NWQ) * QW], acc[q], seq);
+      }
     }
     if (j >= rs && j < rs + nr && tid >= j && tid < jb)
       qll_put<T>(&xch->rowll[par][tid * QW], base[tid * pitch + (j - rs)], seq);
+    QTRACE(1);
     // ---- reduce the partials of all CTAs as they arrive: 8 groups x 32 columns.  (A CTA can be
     // two columns ahead of no other: it publishes column j+1 only after it has read every CTA's
     // column j, so the two buffers of a parity never hold live data of different columns.)
@@ -224,7 +250,9 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
         for (int g = grp; g < G; g += QR_NT / 32) s = add(s, qll_get<T>(&xch->pll[par][g][c * QW], seq));
       s_red[grp][c] = s;
     }
+    QTRACE(2);
     __syncthreads();
+    QTRACE(3);
     if (tid < 32) {
       const int c = tid;
       T s = zero<T>();
@@ -252,6 +280,7 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
       }
     }
     __syncthreads();
+    QTRACE(4);
     // ---- apply: rows r > j: v_r = x_r*scale, a(r,c) -= v_r f_c; row j: a(j,j)=beta, a(j,c) -= f_c
     {
       const T scale = s_scale;
@@ -272,6 +301,7 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
       }
     }
     __syncthreads();
+    QTRACE(5);
   }
   if (use_smem) {
     for (int64_t r = tid; r < nr; r += QR_NT)
@@ -1400,3 +1430,10 @@ LA_INST_QR(double)
 LA_INST_QR(zcomplex)
 
 }  // namespace la
+
+#ifdef LA_PANEL_TRACE
+extern "C" void la_b200_debug_qr_trace(long long* out) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, la::g_qr_trace, sizeof(long long) * 64 * 8);
+}
+#endif
