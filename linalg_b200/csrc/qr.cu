@@ -290,6 +290,8 @@ qr_panel_kernel(int64_t mp, int jb, T* __restrict__ A, int64_t lda, T* __restric
         for (int64_t r = rbeg + tid; r < nr; r += QR_NT) {
           T v = mul(base[j * pitch + r], scale);
           base[j * pitch + r] = v;
+          // (eight independent load / multiply-add / store chains in flight)
+#pragma unroll 8
           for (int c = j + 1; c < jb; c++)
             base[c * pitch + r] = fnma_(v, s_f[c], base[c * pitch + r]);
         }
