@@ -4,7 +4,10 @@
 // src/linalg/mult.cr:6-15 (`blas` macro: always COL_MAJOR, NoTrans).  Row-major calls are
 // mapped onto the column-major kernels by the usual transposition identities.
 #include "shim_common.h"
+#include <cstdlib>
+#include <thread>
 #include <utility>
+#include <vector>
 
 namespace la {
 
@@ -13,6 +16,20 @@ static void cblas_error(const char* name, int arg) {
   // the reference); report and leave the output untouched, as the reference BLAS does.
   fprintf(stderr, "la_b200: %s: parameter %d had an illegal value\n", name, arg);
 }
+
+// GPUs one drop-in product may use: LA_B200_GPUS (default 1 — the reference's host calls one
+// library, and a process normally owns one GPU; set it to let the big products of an unchanged
+// host spread over the GPUs of the box).  Clamped to the number of visible devices.
+static int gemm_gpu_count() {
+  static const int n = [] {
+    const char* e = getenv("LA_B200_GPUS");
+    int want = e ? atoi(e) : 1, have = 0;
+    if (want <= 1 || cudaGetDeviceCount(&have) != cudaSuccess) return 1;
+    return want < have ? want : have;
+  }();
+  return n;
+}
+static thread_local bool tl_gemm_worker = false;   // set in the per-GPU threads of a split product
 
 template <typename T>
 static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, int k, T alpha,
@@ -33,6 +50,32 @@ static void h_gemm(const char* name, int order, int ta, int tb, int m, int n, in
   if (ldc < (m > 1 ? m : 1)) return cblas_error(name, 14);
   if (m == 0 || n == 0) return;
   if ((is_zero(alpha) || k == 0) && is_one(beta)) return;
+  // Several GPUs (LA_B200_GPUS > 1): the columns of C and of op(B) are dealt in contiguous blocks
+  // to one host thread per GPU, each of which runs the single-GPU path below on its block (its
+  // own PCIe link for its share of B and C and for A; no data-path exchange between the GPUs).
+  if (!tl_gemm_worker && gemm_gpu_count() > 1 && !is_zero(alpha) && k > 0 &&
+      (double)m * (double)n * (double)k >= 6.4e10 && n >= 1024 * gemm_gpu_count()) {
+    const int ng = gemm_gpu_count();
+    int cur = 0;
+    LA_CUDA_CHECK(cudaGetDevice(&cur));
+    const int64_t nb = round_up(ceil_div((int64_t)n, (int64_t)ng), 128);
+    std::vector<std::thread> workers;
+    for (int d = 0; d < ng; d++) {
+      const int64_t c0 = (int64_t)d * nb;
+      if (c0 >= n) break;
+      const int cn = (int)(nb < n - c0 ? nb : n - c0);
+      const T* Bd = tb == OpN ? B + c0 * (int64_t)ldb : B + c0;
+      T* Cd = C + c0 * (int64_t)ldc;
+      workers.emplace_back([=] {
+        LA_CUDA_CHECK(cudaSetDevice(d));
+        tl_gemm_worker = true;
+        h_gemm<T>(name, LA_COL_MAJOR_, ta, tb, m, cn, k, alpha, A, lda, Bd, ldb, beta, Cd, ldc);
+      });
+    }
+    for (auto& w : workers) w.join();
+    LA_CUDA_CHECK(cudaSetDevice(cur));
+    return;
+  }
   ContextLease ctx;
   Arena::Mark mk = ctx->arena.mark();
   const bool need_ab = !is_zero(alpha) && k > 0;

@@ -101,3 +101,19 @@ def test_concurrent_callers_with_staged_transfers(product_abi, oracle_abi):
         ref = np.zeros((n, n), order="F")
         _dgemm(oracle_abi, A, B, ref, n, n, n, n, n, n)
         assert checks.rel(C - ref, ref) < 1e-13
+
+
+def test_drop_in_dgemm_split_over_the_visible_gpus():
+    """LA_B200_GPUS > 1: the columns of a big cblas_dgemm are dealt to one host thread per GPU
+    (shim_cblas.cu).  The switch is read when the library is loaded, so the call runs in a child
+    process; with one visible GPU the request is clamped and the ordinary path is checked."""
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    env = dict(os.environ, LA_B200_GPUS="2")
+    r = subprocess.run([sys.executable, str(root / "tools" / "multi_gpu_gemm_check.py"), "4096"],
+                       cwd=str(root), env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "max relative error on sampled columns" in r.stdout
