@@ -407,10 +407,10 @@ void getrf(Context& ctx, int64_t m, int64_t n, T* A, int64_t lda, int* d_ipiv, i
   // factored on a side stream (a chain of latency-bound leaf launches that needs only a few
   // SMs) while the main stream finishes the trailing update on the remaining SMs.
   const int64_t leaf_ctas = ceil_div(m, 512);
-  // Only when the overlapped trailing update is exactly ONE persistent kernel with a capped
-  // grid (the FP64 DMMA GEMM on TMA-legal operands): a trailing update made of many ordinary
-  // launches (SIMT GEMM, complex packing passes) gives the side stream's cooperative leaf no
-  // stable set of free SMs, and the leaf's CTAs then wait for one another forever.
+  // Only when the overlapped trailing update is essentially ONE persistent kernel with a capped
+  // grid (the FP64 DMMA GEMM on TMA-legal operands; FP32 below): the cooperative leaf needs its
+  // SMs whole and all at once, and a trailing update made of many ordinary launches (SIMT GEMM)
+  // keeps taking them away between two leaves.
   const bool dmma_ok = std::is_same<T, double>::value && (lda % 2 == 0) &&
                        (((uintptr_t)A & 15) == 0);
   // FP32: the update is the persistent 3xTF32 kernel behind two short packing launches, which
