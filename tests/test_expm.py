@@ -106,6 +106,9 @@ def test_la_expm_special_cases_and_matfun(cpu_abi):
         assert _close(up.expm().raw, R.expm(up.raw), 1e-14)                  # expmT2by2
         d = la.GeneralMatrix(np.diag([0.5, -1.0, 2.0]), flags=la.MatrixFlags.Triangular)
         assert _close(d.expm().raw, np.diag(np.exp([0.5, -1.0, 2.0])), 1e-15)
+        tri = la.GMat(M4)
+        tri.detect(la.MatrixFlags.Triangular)                               # spec/expm_spec.cr:31-32
+        assert tri.flags.upper_triangular and _close(tri.expm().raw, M4_EXP, 1e-13)
         with pytest.raises(NotImplementedError):
             la.GMat(M4).expm(schur_fact=True)
         with pytest.raises(ValueError):
